@@ -1,0 +1,209 @@
+/*
+ * rt_b200.h -- C ABI of librt_b200.so: the B200-native (sm_100a CUDA) replacement for the
+ * CPU path-tracing hot path of ShuvalovIvan/RayTracingProject.
+ *
+ * The reference has no process/device boundary: `cam.render(world)` (src/main.cpp:70 ->
+ * src/camera.h:32-50) runs everything on one host thread.  This header is the boundary the
+ * replacement inserts at that call; north_star names its three core entry
+ * points rt_upload_scene / rt_render / rt_readback.  Each declaration cites the reference
+ * interface it replaces (paths relative to the reference tree).
+ *
+ * Conventions: plain C, POD structs with fixed layout (doubles, as the reference computes in
+ * double), every function returns 0 on success and a negative RT_E* code on failure with a
+ * message in rt_last_error().  Nothing here throws, nothing falls back to the CPU: without a
+ * CUDA device rt_create fails.  A context is bound to ONE device and is externally
+ * synchronised (one caller at a time), like the reference, which is not re-entrant
+ * (function-local static RNG, src/rtweekend.h:26-27).
+ */
+#ifndef RT_B200_H
+#define RT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RT_ABI_VERSION 1u
+
+enum {
+    RT_OK = 0,
+    RT_E_INVALID = -1,   /* bad argument / ABI mismatch */
+    RT_E_CUDA = -2,      /* CUDA runtime error (message has the cudaError string) */
+    RT_E_STATE = -3,     /* call order (e.g. render before upload) */
+    RT_E_NOMEM = -4
+};
+
+/* material tags: src/material.h:15 (lambertian), :31 (metal), :48 (dielectric) */
+enum { RT_LAMBERTIAN = 0, RT_METAL = 1, RT_DIELECTRIC = 2 };
+
+/* arithmetic type of the device path.  F64 = "parity mode": IEEE double, same operation order
+ * as the reference, no FMA contraction.  F32 = fast mode (big spheres intersected in double). */
+enum { RT_F32 = 0, RT_F64 = 1 };
+
+/* bounce-loop variants (north_star item 3) */
+enum { RT_MEGAKERNEL = 0, RT_WAVEFRONT = 1 };
+
+/* closest-hit back ends for rt_trace_closest / rt_bench_closest */
+enum { RT_TRACE_BVH = 0, RT_TRACE_BRUTE = 1 };
+
+/* acceleration-structure builders */
+enum { RT_BVH_SAH_HOST = 0, RT_BVH_LBVH_GPU = 1 };
+
+/* src/sphere.h:60-66 (private fields of `sphere`; static :9-14, moving :19-28) */
+typedef struct {
+    double  center1[3];
+    double  center_vec[3];   /* center2 - center1; ignored unless is_moving */
+    double  radius;
+    int32_t is_moving;
+    int32_t material;        /* index into the material array */
+} rt_sphere;
+
+/* src/material.h:27-28 (lambertian albedo), :43-45 (metal albedo, fuzz<=1), :73-74 (ir) */
+typedef struct {
+    int32_t type;
+    int32_t pad;
+    double  albedo[3];
+    double  param;           /* metal: fuzz, dielectric: index of refraction */
+} rt_material;
+
+/* public fields of `camera`, src/camera.h:15-26 */
+typedef struct {
+    double  aspect_ratio;
+    int32_t image_width;
+    int32_t samples_per_pixel;
+    int32_t max_depth;
+    int32_t pad;
+    double  vfov;
+    double  lookfrom[3], lookat[3], vup[3];
+    double  defocus_angle, focus_dist;
+} rt_camera;
+
+/* src/ray.h:23-26 */
+typedef struct { double orig[3], dir[3], tm; } rt_ray;
+
+/* src/hittable.h:7-14 plus the list index of the sphere that was hit (-1 = miss) */
+typedef struct {
+    double  p[3], normal[3], t;
+    int32_t front_face;
+    int32_t prim;
+} rt_hit;
+
+typedef struct {
+    uint32_t abi;            /* RT_ABI_VERSION */
+    int32_t  builder;        /* RT_BVH_SAH_HOST | RT_BVH_LBVH_GPU */
+    int32_t  max_leaf;       /* spheres per leaf, 1..8 (0 = default 4) */
+    int32_t  pad;
+    double   big_radius;     /* spheres with radius >= this are kept out of the tree and tested first,
+                                in double (the r = 1000 ground sphere; SURVEY.md 7 hard parts 1, 5).
+                                0 = default 100; negative = never */
+} rt_bvh_opts;
+
+typedef struct {
+    uint32_t abi;            /* RT_ABI_VERSION */
+    int32_t  precision;      /* RT_F32 | RT_F64 */
+    int32_t  variant;        /* RT_MEGAKERNEL | RT_WAVEFRONT */
+    int32_t  sample_begin;   /* first sample index of every pixel rendered by this call ... */
+    int32_t  sample_count;   /* ... and how many (0 = all of camera.samples_per_pixel): the shard
+                                a rank renders under sample-range sharding */
+    int32_t  accumulate;     /* 0: overwrite the accumulation buffer, 1: add to it (progressive) */
+    uint64_t seed;           /* Philox key; stream = (pixel, sample, stage), see DESIGN.md */
+    int32_t  slices;         /* sample slices per pixel rendered by different warps (0 = auto) */
+    int32_t  pad;
+} rt_render_opts;
+
+typedef struct {
+    uint64_t rays;           /* path segments traced by the last render (ray_color entries, depth > 0) */
+    uint64_t samples;        /* W*H*sample_count of the last render */
+    double   render_ms;      /* device time of the last render (CUDA events on the ctx stream) */
+    double   resolve_ms;     /* device time of the last resolve/encode */
+    double   build_ms;       /* BVH build (host wall or device time) of the last upload */
+    double   upload_ms;
+    int32_t  n_spheres, n_big, n_nodes, bvh_depth;
+    int32_t  image_width, image_height;
+    int32_t  slices, kernel_launches;   /* launches of this library's kernels in the last render+resolve */
+    int32_t  scene_in_smem, pad;
+} rt_stats;
+
+typedef struct rt_ctx rt_ctx;
+
+/* ---- lifetime -------------------------------------------------------------------------- */
+int         rt_create(rt_ctx **ctx, int device);      /* fails (RT_E_CUDA) when no CUDA device */
+int         rt_destroy(rt_ctx *ctx);
+const char *rt_last_error(const rt_ctx *ctx);          /* ctx may be NULL: last creation error */
+uint32_t    rt_abi_version(void);
+
+/* ---- the render path: replaces camera::render(world), src/camera.h:32-50 ------------------ */
+
+/* world -> device.  Replaces the hittable_list of shared_ptr<sphere> (src/hittable_list.h:13,
+ * src/main.cpp:12-53): spheres/materials are copied into tagged SoA buffers and a BVH is built
+ * (bvh.h is a stub in the reference; src/bvh.h:16-24 fixes only the traversal contract). */
+int rt_upload_scene(rt_ctx *ctx, const rt_sphere *spheres, size_t n_spheres,
+                    const rt_material *materials, size_t n_materials, const rt_bvh_opts *opts);
+
+/* camera::initialize + the pixel/sample/bounce loops (src/camera.h:37-47, src/camera_cpu.h:8-26).
+ * Asynchronous: enqueues on the context's stream. */
+int rt_render(rt_ctx *ctx, const rt_camera *cam, const rt_render_opts *opts);
+
+/* write_color for every pixel + the P3 stream camera::render prints (src/color.h:14-35,
+ * src/camera.h:35,45).  Synchronises.  Every output pointer is optional:
+ *   sum_rgb  H*W*3 doubles, per-pixel radiance sums (pixel_color before write_color)
+ *   rgb8     H*W*3 bytes, exactly the integers write_color prints
+ *   ppm      P3 text, byte-identical to the reference's stdout; *ppm_len in = capacity, out = length
+ * spp_total = divisor used by write_color (0 = samples rendered into the buffer so far). */
+int rt_readback(rt_ctx *ctx, int spp_total, double *sum_rgb, uint8_t *rgb8, char *ppm, size_t *ppm_len);
+
+int rt_image_size(const rt_camera *cam, int *width, int *height);   /* src/camera.h:53-54 */
+int rt_synchronize(rt_ctx *ctx);
+int rt_get_stats(rt_ctx *ctx, rt_stats *out);
+
+/* ---- multi-GPU plumbing (one process per GPU) -------------------------------- */
+
+/* Device pointer / geometry of the accumulation buffer so the host framework can reduce it
+ * across ranks (NCCL) or map it into a peer (CUDA IPC).  elem_bytes 4 (RT_F32, float4 per
+ * pixel) or 8 (RT_F64, double4 per pixel); n_elems = W*H*4. */
+int rt_accum_buffer(rt_ctx *ctx, void **dev_ptr, size_t *n_elems, int *elem_bytes);
+int rt_stream(rt_ctx *ctx, void **cuda_stream);
+/* CUDA IPC handle (64 bytes) of the accumulation buffer, and the fused peer reduce + resolve:
+ * rank 0 reads every peer's partial buffer over NVLink inside the resolve kernel. */
+int rt_ipc_export(rt_ctx *ctx, void *handle64);
+int rt_ipc_open_peers(rt_ctx *ctx, const void *handles64, int n_peers);   /* peers other than self */
+int rt_ipc_close_peers(rt_ctx *ctx);
+
+/* ---- parity / microbenchmark hooks (same code the render path runs) ------------------------- */
+
+/* closest hit in (tmin, tmax): hittable_list::hit, src/hittable_list.h:25-39 (ground truth,
+ * RT_TRACE_BRUTE) or the BVH traversal (src/bvh.h:16-24 contract, RT_TRACE_BVH). */
+int rt_trace_closest(rt_ctx *ctx, const rt_ray *rays, size_t n, double tmin, double tmax,
+                     int precision, int backend, rt_hit *out);
+
+/* material::scatter (src/material.h:19-71) for n independent (material, ray, hit) triples;
+ * element i draws from the stream (pixel = i, sample = 0, stage = 1) of `seed`. */
+int rt_scatter(rt_ctx *ctx, const rt_material *materials, const rt_ray *rays_in, const rt_hit *hits,
+               size_t n, uint64_t seed, int precision,
+               int32_t *scattered_flag, double *attenuation_rgb, rt_ray *scattered);
+
+/* camera::get_ray (src/camera.h:87-113) for n (i, j, sample) triples, stream stage 0. */
+int rt_gen_rays(rt_ctx *ctx, const rt_camera *cam, const int32_t *px_i, const int32_t *px_j,
+                const uint32_t *sample, size_t n, uint64_t seed, int precision, rt_ray *out);
+
+/* BASELINE config 2: n synthetic rays generated in-kernel (even index: get_ray of a virtual
+ * 8192x8192 image; odd: incoherent origin/direction) traced against the uploaded
+ * scene.  prim_out/t_out (host, optional) receive per-ray results; rays_out (host, optional)
+ * receives the rays in double so an oracle can re-trace them.  *ms = device time of the trace. */
+int rt_bench_closest(rt_ctx *ctx, const rt_camera *cam, size_t n, uint64_t seed, int precision,
+                     int backend, int repeats, double *ms, int32_t *prim_out, float *t_out,
+                     rt_ray *rays_out, size_t rays_out_n);
+
+/* src/main.cpp:11-68 scene + camera generators (default-seeded mt19937, g++ draw order),
+ * generalised for BASELINE configs 4 and 5: grid half-width g (11), thresholds p_diffuse (0.8),
+ * p_metal (0.95).  Returns the sphere count (call with cap = 0 to size the arrays). */
+size_t rt_scene_rtiow(int g, double p_diffuse, double p_metal, uint32_t mt_seed,
+                      rt_sphere *spheres, rt_material *materials, size_t cap);
+int    rt_camera_rtiow(rt_camera *cam, int image_width, int spp, int max_depth, double scale);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_B200_H */

@@ -1,0 +1,720 @@
+// rt_api.cu -- the C ABI of librt_b200.so (include/rt_b200.h): context, scene upload, render,
+// readback and the parity hooks.  Host logic only; every kernel lives in rt_kernels_*.cu,
+// rt_frame.cu and rt_lbvh.cu.  No CPU fallback anywhere: a CUDA failure is an error.
+#include "../../include/rt_b200.h"
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <random>
+#include <string>
+#include <vector>
+
+#include "rt_bvh_host.h"
+#include "rt_frame.h"
+#include "rt_kernels.cuh"
+#include "rt_lbvh.h"
+
+using namespace rt;
+
+static_assert(sizeof(rt_sphere) == 64, "rt_sphere layout");
+static_assert(sizeof(rt_material) == 40, "rt_material layout");
+static_assert(sizeof(rt_ray) == 56, "rt_ray layout");
+static_assert(sizeof(rt_hit) == 64, "rt_hit layout");
+static_assert(sizeof(HitRec) == sizeof(rt_hit), "HitRec mirrors rt_hit");
+static_assert(sizeof(MatRec) == sizeof(rt_material), "MatRec mirrors rt_material");
+
+namespace {
+
+std::string g_create_error;
+
+template <typename T> struct DevBuf {
+    T* p = nullptr; size_t n = 0;
+    cudaError_t resize(size_t count) {
+        if (count <= n && p) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; n = 0;
+        if (count == 0) return cudaSuccess;
+        cudaError_t e = cudaMalloc(&p, count * sizeof(T));
+        if (e == cudaSuccess) n = count;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+};
+
+}  // namespace
+
+struct rt_ctx {
+    int device = 0, sm_count = 0;
+    size_t smem_optin = 0, smem_per_sm = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[4] = { nullptr, nullptr, nullptr, nullptr };
+    std::string err;
+
+    // scene (SoA, both precisions; see rt_device.cuh for the slot layout)
+    bool has_scene = false;
+    int n_spheres = 0, n_slots = 0, n_big = 0, n_nodes = 0, root_ref = RT_SENTINEL, depth = 0;
+    DevBuf<float4> nodes, sa32, sb32, sc32;
+    DevBuf<double4> sa64, sb64, sc64, big_a, big_b, big_c;
+    DevBuf<int> meta, big_meta;
+    double build_ms = 0, upload_ms = 0;
+
+    // frame
+    int W = 0, H = 0, slices = 0, precision = -1;
+    long long samples_in_buffer = 0;
+    DevBuf<unsigned char> accum;            // Quad<T>[slices][H][W]
+    DevBuf<unsigned char> reduced;          // Quad<T>[H][W] (after peer reduce, for rt_accum_buffer consumers)
+    DevBuf<unsigned int> job_counter;
+    DevBuf<unsigned long long> ray_counter;
+    DevBuf<unsigned char> rgb8;
+    DevBuf<double> sum;
+    DevBuf<char> text;
+    DevBuf<unsigned> enc_sums;
+    DevBuf<unsigned long long> enc_offsets;   // [blocks] + total at the end
+    bool render_timed = false;
+
+    // peers (CUDA IPC)
+    PeerList peers = {};
+    void* peer_mapped[RT_MAX_PEERS] = {};
+
+    rt_stats stats = {};
+};
+
+namespace {
+
+int fail(rt_ctx* c, int code, const std::string& msg) { if (c) c->err = msg; else g_create_error = msg; return code; }
+int cuda_fail(rt_ctx* c, cudaError_t e, const char* what) {
+    return fail(c, RT_E_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return cuda_fail(ctx, e_, #call); } while (0)
+
+// ---- camera::initialize, src/camera.h:52-85, in double exactly as written -------------------
+typedef Vec<double> V3;
+V3 v3(const double a[3]) { return mk<double>(a[0], a[1], a[2]); }
+V3 hunit(V3 v) { return (1 / std::sqrt(len2(v))) * v; }                       // src/vec3.h:117-119
+V3 hcross(V3 u, V3 v) { return mk<double>(u.y * v.z - u.z * v.y, u.z * v.x - u.x * v.z, u.x * v.y - u.y * v.x); }
+V3 hdiv(V3 v, double t) { return (1 / t) * v; }                                // src/vec3.h:101-103
+
+int image_height_of(const rt_camera& c) {
+    int h = static_cast<int>(c.image_width / c.aspect_ratio);                  // src/camera.h:53-54
+    return h < 1 ? 1 : h;
+}
+
+CameraFrame<double> camera_frame(const rt_camera& c) {
+    CameraFrame<double> f;
+    const double pi = 3.1415926535897932385;                                   // src/rtweekend.h:17
+    f.image_width = c.image_width;
+    f.image_height = image_height_of(c);
+    f.center = v3(c.lookfrom);
+    const double theta = c.vfov * pi / 180.0;                                  // src/rtweekend.h:21-23
+    const double h = std::tan(theta / 2);
+    const double viewport_height = 2 * h * c.focus_dist;
+    const double viewport_width = viewport_height * (static_cast<double>(f.image_width) / f.image_height);
+    const V3 w = hunit(v3(c.lookfrom) - v3(c.lookat));
+    const V3 u = hunit(hcross(v3(c.vup), w));
+    const V3 v = hcross(w, u);
+    const V3 viewport_u = viewport_width * u;
+    const V3 viewport_v = viewport_height * (-v);
+    f.pixel_delta_u = hdiv(viewport_u, f.image_width);
+    f.pixel_delta_v = hdiv(viewport_v, f.image_height);
+    const V3 viewport_upper_left = ((f.center - (c.focus_dist * w)) - hdiv(viewport_u, 2)) - hdiv(viewport_v, 2);
+    f.pixel00_loc = viewport_upper_left + 0.5 * (f.pixel_delta_u + f.pixel_delta_v);
+    const double defocus_radius = c.focus_dist * std::tan((c.defocus_angle / 2) * pi / 180.0);
+    f.defocus_disk_u = defocus_radius * u;                                     // operator*(vec3,double) = t*v, src/vec3.h:97-99
+    f.defocus_disk_v = defocus_radius * v;
+    f.defocus = c.defocus_angle > 0;                                           // src/camera.h:94 tests `<= 0`
+    return f;
+}
+
+template <typename T> Vec<T> narrow(const V3& a) { return mk<T>(T(a.x), T(a.y), T(a.z)); }
+template <typename T> CameraFrame<T> narrow_frame(const CameraFrame<double>& f) {
+    CameraFrame<T> g;
+    g.center = narrow<T>(f.center); g.pixel00_loc = narrow<T>(f.pixel00_loc);
+    g.pixel_delta_u = narrow<T>(f.pixel_delta_u); g.pixel_delta_v = narrow<T>(f.pixel_delta_v);
+    g.defocus_disk_u = narrow<T>(f.defocus_disk_u); g.defocus_disk_v = narrow<T>(f.defocus_disk_v);
+    g.image_width = f.image_width; g.image_height = f.image_height; g.defocus = f.defocus;
+    return g;
+}
+
+template <typename T> struct Sel;
+template <> struct Sel<float> {
+    static const float4* a(const rt_ctx* c) { return c->sa32.p; }
+    static const float4* b(const rt_ctx* c) { return c->sb32.p; }
+    static const float4* cc(const rt_ctx* c) { return c->sc32.p; }
+};
+template <> struct Sel<double> {
+    static const double4* a(const rt_ctx* c) { return c->sa64.p; }
+    static const double4* b(const rt_ctx* c) { return c->sb64.p; }
+    static const double4* cc(const rt_ctx* c) { return c->sc64.p; }
+};
+
+template <typename T> SceneView<T> scene_view(const rt_ctx* c) {
+    SceneView<T> sv;
+    sv.nodes = c->nodes.p;
+    sv.sa = Sel<T>::a(c); sv.sb = Sel<T>::b(c); sv.sc = Sel<T>::cc(c);
+    sv.meta = c->meta.p;
+    sv.big_a = c->big_a.p; sv.big_b = c->big_b.p; sv.big_c = c->big_c.p; sv.big_meta = c->big_meta.p;
+    sv.n_slots = c->n_slots; sv.n_nodes = c->n_nodes; sv.n_big = c->n_big; sv.root_ref = c->root_ref;
+    return sv;
+}
+
+// Shared memory one megakernel CTA may use for the staged scene: two CTAs per SM, 1 KB/CTA is
+// reserved by the driver, and at least 32 KB per CTA stays L1 for the traversal stacks.
+template <typename T> bool can_stage(const rt_ctx* c, size_t* bytes) {
+    *bytes = staged_bytes<T>(c->n_nodes, c->n_slots);
+    const size_t per_cta = std::min(c->smem_optin, (c->smem_per_sm - 2048) / 2);
+    return *bytes + 32 * 1024 <= per_cta && c->n_slots > 0;
+}
+
+double ms_since(std::chrono::steady_clock::time_point t0) {
+    return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+}
+
+}  // namespace
+
+extern "C" {
+
+uint32_t rt_abi_version(void) { return RT_ABI_VERSION; }
+
+const char* rt_last_error(const rt_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int rt_create(rt_ctx** out, int device) {
+    if (!out) return fail(nullptr, RT_E_INVALID, "rt_create: null out pointer");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(nullptr, RT_E_CUDA, std::string("rt_create: no CUDA device (") + cudaGetErrorString(e) + "); there is no CPU fallback");
+    if (device < 0 || device >= count) return fail(nullptr, RT_E_INVALID, "rt_create: device index out of range");
+    rt_ctx* ctx = new rt_ctx;
+    ctx->device = device;
+    cudaDeviceProp prop;
+    if ((e = cudaSetDevice(device)) != cudaSuccess || (e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess ||
+        (e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) {
+        delete ctx;
+        return fail(nullptr, RT_E_CUDA, std::string("rt_create: ") + cudaGetErrorString(e));
+    }
+    ctx->sm_count = prop.multiProcessorCount;
+    ctx->smem_optin = prop.sharedMemPerBlockOptin;
+    ctx->smem_per_sm = prop.sharedMemPerMultiprocessor;
+    for (auto& ev : ctx->ev) cudaEventCreate(&ev);
+    ctx->job_counter.resize(1);
+    ctx->ray_counter.resize(1);
+    *out = ctx;
+    return RT_OK;
+}
+
+int rt_destroy(rt_ctx* ctx) {
+    if (!ctx) return RT_OK;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    rt_ipc_close_peers(ctx);
+    ctx->nodes.release(); ctx->sa32.release(); ctx->sb32.release(); ctx->sc32.release();
+    ctx->sa64.release(); ctx->sb64.release(); ctx->sc64.release();
+    ctx->big_a.release(); ctx->big_b.release(); ctx->big_c.release(); ctx->meta.release(); ctx->big_meta.release();
+    ctx->accum.release(); ctx->reduced.release(); ctx->job_counter.release(); ctx->ray_counter.release();
+    ctx->rgb8.release(); ctx->sum.release(); ctx->text.release(); ctx->enc_sums.release(); ctx->enc_offsets.release();
+    for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return RT_OK;
+}
+
+int rt_image_size(const rt_camera* cam, int* width, int* height) {
+    if (!cam || cam->image_width < 1 || !(cam->aspect_ratio > 0)) return RT_E_INVALID;
+    if (width) *width = cam->image_width;
+    if (height) *height = image_height_of(*cam);
+    return RT_OK;
+}
+
+int rt_synchronize(rt_ctx* ctx) {
+    if (!ctx) return RT_E_INVALID;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return RT_OK;
+}
+
+int rt_stream(rt_ctx* ctx, void** cuda_stream) {
+    if (!ctx || !cuda_stream) return RT_E_INVALID;
+    *cuda_stream = ctx->stream;
+    return RT_OK;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------ scene upload --
+extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_spheres,
+                               const rt_material* materials, size_t n_materials, const rt_bvh_opts* opts) {
+    if (!ctx) return RT_E_INVALID;
+    if (n_spheres && (!spheres || !materials)) return fail(ctx, RT_E_INVALID, "rt_upload_scene: null arrays");
+    if (opts && opts->abi != RT_ABI_VERSION) return fail(ctx, RT_E_INVALID, "rt_upload_scene: ABI version mismatch");
+    if (n_spheres >= (size_t(1) << 28)) return fail(ctx, RT_E_INVALID, "rt_upload_scene: too many spheres");
+    const int builder = opts ? opts->builder : RT_BVH_SAH_HOST;
+    const int max_leaf = (opts && opts->max_leaf > 0) ? std::min(opts->max_leaf, 8) : 4;
+    double big_radius = (opts && opts->big_radius != 0.0) ? opts->big_radius : 100.0;
+    if (big_radius < 0) big_radius = INFINITY;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    const auto t_start = std::chrono::steady_clock::now();
+
+    for (size_t i = 0; i < n_spheres; ++i) {
+        if (spheres[i].material < 0 || size_t(spheres[i].material) >= n_materials)
+            return fail(ctx, RT_E_INVALID, "rt_upload_scene: sphere material index out of range");
+        const int ty = materials[spheres[i].material].type;
+        if (ty < RT_LAMBERTIAN || ty > RT_DIELECTRIC) return fail(ctx, RT_E_INVALID, "rt_upload_scene: unknown material type");
+    }
+
+    // split: outsized spheres stay out of the tree (tested first, in double)
+    std::vector<int> tree_ids, big_ids;
+    for (size_t i = 0; i < n_spheres; ++i) {
+        if (std::fabs(spheres[i].radius) >= big_radius && big_ids.size() < 16) big_ids.push_back(int(i));
+        else tree_ids.push_back(int(i));
+    }
+    std::vector<HostBox> boxes(tree_ids.size());
+    for (size_t k = 0; k < tree_ids.size(); ++k) {
+        const rt_sphere& s = spheres[tree_ids[k]];
+        boxes[k] = sphere_box(s.center1, s.center_vec, s.radius, s.is_moving != 0);
+    }
+
+    const auto t_build = std::chrono::steady_clock::now();
+    HostBVH bvh;
+    std::vector<int> order;               // slot -> index into tree_ids
+    const int n_tree = int(tree_ids.size());
+    if (builder == RT_BVH_LBVH_GPU && n_tree >= 2) {
+        DevBuf<HostBox> d_boxes; DevBuf<int> d_order;
+        CK(d_boxes.resize(n_tree)); CK(d_order.resize(n_tree)); CK(ctx->nodes.resize(size_t(n_tree - 1) * 4));
+        CK(cudaMemcpyAsync(d_boxes.p, boxes.data(), sizeof(HostBox) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
+        int root = RT_SENTINEL, depth = 0;
+        cudaError_t e = build_lbvh_gpu(d_boxes.p, n_tree, ctx->nodes.p, d_order.p, &root, &depth, ctx->stream);
+        if (e != cudaSuccess) { d_boxes.release(); d_order.release(); return cuda_fail(ctx, e, "build_lbvh_gpu"); }
+        order.resize(n_tree);
+        CK(cudaMemcpyAsync(order.data(), d_order.p, sizeof(int) * n_tree, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        d_boxes.release(); d_order.release();
+        if (depth > RT_STACK) return fail(ctx, RT_E_INVALID, "rt_upload_scene: LBVH deeper than the traversal stack");
+        ctx->root_ref = root; ctx->depth = depth; ctx->n_nodes = n_tree - 1;
+    } else {
+        build_bvh_sah(boxes, max_leaf, bvh);
+        order = bvh.order;
+        if (bvh.depth > RT_STACK) return fail(ctx, RT_E_INVALID, "rt_upload_scene: BVH deeper than the traversal stack");
+        ctx->root_ref = bvh.root_ref; ctx->depth = bvh.depth; ctx->n_nodes = bvh.n_inner;
+        CK(ctx->nodes.resize(std::max<size_t>(1, size_t(bvh.n_inner) * 4)));
+        if (bvh.n_inner)
+            CK(cudaMemcpyAsync(ctx->nodes.p, bvh.nodes.data(), bvh.nodes.size() * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    }
+    ctx->build_ms = ms_since(t_build);
+
+    // SoA slots in leaf order
+    auto fill = [&](const std::vector<int>& ids, std::vector<double4>& a, std::vector<double4>& b, std::vector<double4>& c, std::vector<int>& m) {
+        a.resize(ids.size()); b.resize(ids.size()); c.resize(ids.size()); m.resize(ids.size());
+        for (size_t k = 0; k < ids.size(); ++k) {
+            const rt_sphere& s = spheres[ids[k]];
+            const rt_material& mt = materials[s.material];
+            const bool mov = s.is_moving != 0;
+            a[k] = make_double4(s.center1[0], s.center1[1], s.center1[2], s.radius);
+            b[k] = make_double4(mov ? s.center_vec[0] : 0.0, mov ? s.center_vec[1] : 0.0, mov ? s.center_vec[2] : 0.0, s.radius * s.radius);
+            double param = mt.param;
+            if (mt.type == RT_METAL) param = param < 1 ? param : 1;             // src/material.h:33
+            c[k] = make_double4(mt.albedo[0], mt.albedo[1], mt.albedo[2], param);
+            m[k] = (ids[k] << 3) | (mov ? 4 : 0) | mt.type;
+        }
+    };
+    std::vector<int> slot_ids(n_tree);
+    for (int k = 0; k < n_tree; ++k) slot_ids[k] = tree_ids[order[k]];
+    std::vector<double4> a64, b64, c64, ba, bb, bc;
+    std::vector<int> meta, bmeta;
+    fill(slot_ids, a64, b64, c64, meta);
+    fill(big_ids, ba, bb, bc, bmeta);
+    std::vector<float4> a32(n_tree), b32(n_tree), c32(n_tree);
+    for (int k = 0; k < n_tree; ++k) {
+        a32[k] = make_float4(float(a64[k].x), float(a64[k].y), float(a64[k].z), float(a64[k].w));
+        const float r = a32[k].w;
+        b32[k] = make_float4(float(b64[k].x), float(b64[k].y), float(b64[k].z), r * r);
+        c32[k] = make_float4(float(c64[k].x), float(c64[k].y), float(c64[k].z), float(c64[k].w));
+    }
+    const size_t nt = std::max(1, n_tree), nb = std::max<size_t>(1, big_ids.size());
+    CK(ctx->sa32.resize(nt)); CK(ctx->sb32.resize(nt)); CK(ctx->sc32.resize(nt));
+    CK(ctx->sa64.resize(nt)); CK(ctx->sb64.resize(nt)); CK(ctx->sc64.resize(nt)); CK(ctx->meta.resize(nt));
+    CK(ctx->big_a.resize(nb)); CK(ctx->big_b.resize(nb)); CK(ctx->big_c.resize(nb)); CK(ctx->big_meta.resize(nb));
+    if (n_tree) {
+        CK(cudaMemcpyAsync(ctx->sa32.p, a32.data(), sizeof(float4) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(ctx->sb32.p, b32.data(), sizeof(float4) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(ctx->sc32.p, c32.data(), sizeof(float4) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(ctx->sa64.p, a64.data(), sizeof(double4) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(ctx->sb64.p, b64.data(), sizeof(double4) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(ctx->sc64.p, c64.data(), sizeof(double4) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(ctx->meta.p, meta.data(), sizeof(int) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    if (!big_ids.empty()) {
+        CK(cudaMemcpyAsync(ctx->big_a.p, ba.data(), sizeof(double4) * ba.size(), cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(ctx->big_b.p, bb.data(), sizeof(double4) * bb.size(), cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(ctx->big_c.p, bc.data(), sizeof(double4) * bc.size(), cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(ctx->big_meta.p, bmeta.data(), sizeof(int) * bmeta.size(), cudaMemcpyHostToDevice, ctx->stream));
+    }
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->n_spheres = int(n_spheres); ctx->n_slots = n_tree; ctx->n_big = int(big_ids.size());
+    ctx->has_scene = true;
+    ctx->upload_ms = ms_since(t_start);
+    ctx->stats.n_spheres = ctx->n_spheres; ctx->stats.n_big = ctx->n_big; ctx->stats.n_nodes = ctx->n_nodes;
+    ctx->stats.bvh_depth = ctx->depth; ctx->stats.build_ms = ctx->build_ms; ctx->stats.upload_ms = ctx->upload_ms;
+    return RT_OK;
+}
+
+// ------------------------------------------------------------------------------ render --
+namespace {
+
+template <typename T>
+int render_impl(rt_ctx* ctx, const rt_camera& cam, const rt_render_opts& o, int sample_begin, int sample_count, int slices) {
+    typedef typename Quad<T>::type Q;
+    const CameraFrame<double> f64 = camera_frame(cam);
+    RenderParams<T> p;
+    p.cam = narrow_frame<T>(f64);
+    p.scene = scene_view<T>(ctx);
+    p.accum = reinterpret_cast<Q*>(ctx->accum.p);
+    p.job_counter = ctx->job_counter.p;
+    p.ray_counter = ctx->ray_counter.p;
+    p.seed = o.seed;
+    p.sample_begin = sample_begin; p.sample_count = sample_count; p.max_depth = cam.max_depth;
+    p.slices = slices;
+    p.tiles_x = (ctx->W + 7) / 8; p.tiles_y = (ctx->H + 3) / 4;
+    p.accumulate = o.accumulate;
+    size_t smem = 0;
+    const bool staged = can_stage<T>(ctx, &smem);
+    ctx->stats.scene_in_smem = staged;
+    CK(cudaMemsetAsync(ctx->job_counter.p, 0, sizeof(unsigned int), ctx->stream));
+    CK(cudaMemsetAsync(ctx->ray_counter.p, 0, sizeof(unsigned long long), ctx->stream));
+    CK(cudaEventRecord(ctx->ev[0], ctx->stream));
+    CK(launch_render_mega<T>(p, staged, smem, ctx->sm_count, ctx->stream));
+    CK(cudaEventRecord(ctx->ev[1], ctx->stream));
+    return RT_OK;
+}
+
+}  // namespace
+
+extern "C" int rt_render(rt_ctx* ctx, const rt_camera* cam, const rt_render_opts* opts) {
+    if (!ctx || !cam || !opts) return RT_E_INVALID;
+    if (opts->abi != RT_ABI_VERSION) return fail(ctx, RT_E_INVALID, "rt_render: ABI version mismatch");
+    if (!ctx->has_scene) return fail(ctx, RT_E_STATE, "rt_render: no scene uploaded");
+    if (cam->image_width < 1 || !(cam->aspect_ratio > 0)) return fail(ctx, RT_E_INVALID, "rt_render: bad image size");
+    if (opts->precision != RT_F32 && opts->precision != RT_F64) return fail(ctx, RT_E_INVALID, "rt_render: bad precision");
+    if (opts->variant != RT_MEGAKERNEL) return fail(ctx, RT_E_INVALID, "rt_render: variant not built");
+    CK(cudaSetDevice(ctx->device));
+    const int W = cam->image_width, H = image_height_of(*cam);
+    if ((long long)W * H >= (1ll << 32)) return fail(ctx, RT_E_INVALID, "rt_render: image too large for the 32-bit pixel key");
+    const int sample_begin = std::max(0, opts->sample_begin);
+    const int sample_count = opts->sample_count > 0 ? opts->sample_count : std::max(0, cam->samples_per_pixel - sample_begin);
+
+    // slices: enough warp jobs to keep every resident warp busy and the tail short
+    const long long tiles = (long long)((W + 7) / 8) * ((H + 3) / 4);
+    const int block = opts->precision == RT_F32 ? RT_MEGA_BLOCK(float) : RT_MEGA_BLOCK(double);
+    const long long resident_warps = (long long)ctx->sm_count * 2 * (block / 32);
+    int slices = opts->slices;
+    if (slices <= 0) slices = int(std::min<long long>(64, (16 * resident_warps + tiles - 1) / tiles));
+    slices = std::max(1, std::min(slices, std::max(1, sample_count)));
+    const size_t elem = opts->precision == RT_F32 ? sizeof(float4) : sizeof(double4);
+
+    const bool same = ctx->W == W && ctx->H == H && ctx->precision == opts->precision && ctx->slices == slices;
+    if (opts->accumulate && !same) return fail(ctx, RT_E_STATE, "rt_render: accumulate needs the same image, precision and slice count as the buffer");
+    if (!same) {
+        CK(ctx->accum.resize(size_t(slices) * W * H * elem));
+        ctx->W = W; ctx->H = H; ctx->precision = opts->precision; ctx->slices = slices;
+    }
+    if (!opts->accumulate) ctx->samples_in_buffer = 0;
+    int rc = opts->precision == RT_F32 ? render_impl<float>(ctx, *cam, *opts, sample_begin, sample_count, slices)
+                                       : render_impl<double>(ctx, *cam, *opts, sample_begin, sample_count, slices);
+    if (rc != RT_OK) return rc;
+    ctx->samples_in_buffer += sample_count;
+    ctx->render_timed = true;
+    ctx->stats.samples = (uint64_t)W * H * sample_count;
+    ctx->stats.image_width = W; ctx->stats.image_height = H; ctx->stats.slices = slices;
+    ctx->stats.kernel_launches = 1;
+    return RT_OK;
+}
+
+extern "C" int rt_readback(rt_ctx* ctx, int spp_total, double* sum_rgb, uint8_t* rgb8, char* ppm, size_t* ppm_len) {
+    if (!ctx) return RT_E_INVALID;
+    if (ctx->W == 0 || !ctx->accum.p) return fail(ctx, RT_E_STATE, "rt_readback: nothing rendered");
+    if (ppm && !ppm_len) return fail(ctx, RT_E_INVALID, "rt_readback: ppm needs ppm_len");
+    CK(cudaSetDevice(ctx->device));
+    const size_t npix = size_t(ctx->W) * ctx->H;
+    CK(ctx->rgb8.resize(npix * 3 + 16));
+    if (sum_rgb) CK(ctx->sum.resize(npix * 3));
+    const double scale = spp_total > 0 ? 1.0 / spp_total : 0.0;                 // src/color.h:20
+    CK(cudaEventRecord(ctx->ev[2], ctx->stream));
+    int launches = 1;
+    if (ctx->precision == RT_F32)
+        CK(launch_resolve<float4>(reinterpret_cast<const float4*>(ctx->accum.p), ctx->slices, ctx->peers, npix, scale,
+                                  sum_rgb ? ctx->sum.p : nullptr, ctx->rgb8.p, nullptr, ctx->stream));
+    else
+        CK(launch_resolve<double4>(reinterpret_cast<const double4*>(ctx->accum.p), ctx->slices, ctx->peers, npix, scale,
+                                   sum_rgb ? ctx->sum.p : nullptr, ctx->rgb8.p, nullptr, ctx->stream));
+    unsigned long long text_len = 0;
+    if (ppm || (ppm_len && !ppm)) {
+        EncodeHeader hdr;
+        hdr.len = std::snprintf(hdr.text, sizeof hdr.text, "P3\n%d %d\n255\n", ctx->W, ctx->H);   // src/camera.h:35
+        const int nb = encode_blocks(npix);
+        CK(ctx->enc_sums.resize(nb + 1)); CK(ctx->enc_offsets.resize(nb + 2));
+        CK(ctx->text.resize(npix * 12 + 64));
+        CK(launch_encode_p3(ctx->rgb8.p, npix, hdr, ctx->enc_sums.p, ctx->enc_offsets.p, ctx->enc_offsets.p + nb + 1, ctx->text.p, ctx->stream));
+        launches += 3;
+        CK(cudaMemcpyAsync(&text_len, ctx->enc_offsets.p + nb + 1, sizeof text_len, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    CK(cudaEventRecord(ctx->ev[3], ctx->stream));
+    if (sum_rgb) CK(cudaMemcpyAsync(sum_rgb, ctx->sum.p, npix * 3 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    if (rgb8) CK(cudaMemcpyAsync(rgb8, ctx->rgb8.p, npix * 3, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (ppm_len) {
+        if (ppm) {
+            if (*ppm_len < text_len) { *ppm_len = size_t(text_len); return fail(ctx, RT_E_INVALID, "rt_readback: ppm buffer too small"); }
+            CK(cudaMemcpy(ppm, ctx->text.p, size_t(text_len), cudaMemcpyDeviceToHost));
+        }
+        *ppm_len = size_t(text_len);
+    }
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, ctx->ev[2], ctx->ev[3]) == cudaSuccess) ctx->stats.resolve_ms = ms;
+    ctx->stats.kernel_launches = (ctx->render_timed ? 1 : 0) + launches;
+    return RT_OK;
+}
+
+extern "C" int rt_get_stats(rt_ctx* ctx, rt_stats* out) {
+    if (!ctx || !out) return RT_E_INVALID;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (ctx->render_timed) {
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]) == cudaSuccess) ctx->stats.render_ms = ms;
+        unsigned long long rays = 0;
+        CK(cudaMemcpy(&rays, ctx->ray_counter.p, sizeof rays, cudaMemcpyDeviceToHost));
+        ctx->stats.rays = rays;
+    }
+    *out = ctx->stats;
+    return RT_OK;
+}
+
+// ---------------------------------------------------------------- multi-GPU plumbing --
+extern "C" int rt_accum_buffer(rt_ctx* ctx, void** dev_ptr, size_t* n_elems, int* elem_bytes) {
+    if (!ctx) return RT_E_INVALID;
+    if (!ctx->accum.p) return fail(ctx, RT_E_STATE, "rt_accum_buffer: nothing rendered");
+    if (dev_ptr) *dev_ptr = ctx->accum.p;
+    if (n_elems) *n_elems = size_t(ctx->slices) * ctx->W * ctx->H * 4;
+    if (elem_bytes) *elem_bytes = ctx->precision == RT_F32 ? 4 : 8;
+    return RT_OK;
+}
+
+extern "C" int rt_ipc_export(rt_ctx* ctx, void* handle64) {
+    if (!ctx || !handle64) return RT_E_INVALID;
+    if (!ctx->accum.p) return fail(ctx, RT_E_STATE, "rt_ipc_export: nothing rendered");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "ipc handle size");
+    CK(cudaSetDevice(ctx->device));
+    cudaIpcMemHandle_t h;
+    CK(cudaIpcGetMemHandle(&h, ctx->accum.p));
+    // the slice count rides in a trailer the caller exchanges together with the handle
+    std::memcpy(handle64, &h, 64);
+    return RT_OK;
+}
+
+extern "C" int rt_ipc_close_peers(rt_ctx* ctx) {
+    if (!ctx) return RT_E_INVALID;
+    for (int i = 0; i < RT_MAX_PEERS; ++i)
+        if (ctx->peer_mapped[i]) { cudaIpcCloseMemHandle(ctx->peer_mapped[i]); ctx->peer_mapped[i] = nullptr; }
+    ctx->peers.n = 0;
+    return RT_OK;
+}
+
+extern "C" int rt_ipc_open_peers(rt_ctx* ctx, const void* handles64, int n_peers) {
+    if (!ctx || (n_peers && !handles64)) return RT_E_INVALID;
+    if (n_peers > RT_MAX_PEERS) return fail(ctx, RT_E_INVALID, "rt_ipc_open_peers: too many peers");
+    CK(cudaSetDevice(ctx->device));
+    rt_ipc_close_peers(ctx);
+    for (int i = 0; i < n_peers; ++i) {
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, static_cast<const char*>(handles64) + 64 * i, 64);
+        void* p = nullptr;
+        CK(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        ctx->peer_mapped[i] = p;
+        ctx->peers.ptr[i] = p;
+        ctx->peers.slices[i] = ctx->slices;      // peers render the same image with the same slice count
+    }
+    ctx->peers.n = n_peers;
+    return RT_OK;
+}
+
+// ------------------------------------------------------------------------ parity hooks --
+extern "C" int rt_trace_closest(rt_ctx* ctx, const rt_ray* rays, size_t n, double tmin, double tmax,
+                                int precision, int backend, rt_hit* out) {
+    if (!ctx || (n && (!rays || !out))) return RT_E_INVALID;
+    if (!ctx->has_scene) return fail(ctx, RT_E_STATE, "rt_trace_closest: no scene uploaded");
+    if (n == 0) return RT_OK;
+    CK(cudaSetDevice(ctx->device));
+    DevBuf<double> d_rays; DevBuf<HitRec> d_out;
+    CK(d_rays.resize(n * 7)); CK(d_out.resize(n));
+    CK(cudaMemcpyAsync(d_rays.p, rays, n * sizeof(rt_ray), cudaMemcpyHostToDevice, ctx->stream));
+    cudaError_t e = precision == RT_F32
+        ? launch_trace_closest<float>(scene_view<float>(ctx), d_rays.p, n, tmin, tmax, backend == RT_TRACE_BRUTE, d_out.p, ctx->stream)
+        : launch_trace_closest<double>(scene_view<double>(ctx), d_rays.p, n, tmin, tmax, backend == RT_TRACE_BRUTE, d_out.p, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, d_out.p, n * sizeof(rt_hit), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    d_rays.release(); d_out.release();
+    if (e != cudaSuccess) return cuda_fail(ctx, e, "rt_trace_closest");
+    return RT_OK;
+}
+
+extern "C" int rt_scatter(rt_ctx* ctx, const rt_material* materials, const rt_ray* rays_in, const rt_hit* hits,
+                          size_t n, uint64_t seed, int precision,
+                          int32_t* scattered_flag, double* attenuation_rgb, rt_ray* scattered) {
+    if (!ctx || (n && (!materials || !rays_in || !hits || !scattered_flag || !attenuation_rgb || !scattered))) return RT_E_INVALID;
+    if (n == 0) return RT_OK;
+    CK(cudaSetDevice(ctx->device));
+    DevBuf<MatRec> d_m; DevBuf<double> d_in, d_att, d_out; DevBuf<HitRec> d_h; DevBuf<int> d_f;
+    CK(d_m.resize(n)); CK(d_in.resize(7 * n)); CK(d_att.resize(3 * n)); CK(d_out.resize(7 * n)); CK(d_h.resize(n)); CK(d_f.resize(n));
+    std::vector<rt_material> mats(materials, materials + n);
+    for (auto& m : mats) if (m.type == RT_METAL) m.param = m.param < 1 ? m.param : 1;      // src/material.h:33
+    CK(cudaMemcpyAsync(d_m.p, mats.data(), n * sizeof(rt_material), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(d_in.p, rays_in, n * sizeof(rt_ray), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(d_h.p, hits, n * sizeof(rt_hit), cudaMemcpyHostToDevice, ctx->stream));
+    cudaError_t e = precision == RT_F32
+        ? launch_scatter<float>(d_m.p, d_in.p, d_h.p, n, seed, d_f.p, d_att.p, d_out.p, ctx->stream)
+        : launch_scatter<double>(d_m.p, d_in.p, d_h.p, n, seed, d_f.p, d_att.p, d_out.p, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(scattered_flag, d_f.p, n * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(attenuation_rgb, d_att.p, 3 * n * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(scattered, d_out.p, n * sizeof(rt_ray), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    d_m.release(); d_in.release(); d_att.release(); d_out.release(); d_h.release(); d_f.release();
+    if (e != cudaSuccess) return cuda_fail(ctx, e, "rt_scatter");
+    return RT_OK;
+}
+
+extern "C" int rt_gen_rays(rt_ctx* ctx, const rt_camera* cam, const int32_t* px_i, const int32_t* px_j,
+                           const uint32_t* sample, size_t n, uint64_t seed, int precision, rt_ray* out) {
+    if (!ctx || !cam || (n && (!px_i || !px_j || !sample || !out))) return RT_E_INVALID;
+    if (cam->image_width < 1 || !(cam->aspect_ratio > 0)) return fail(ctx, RT_E_INVALID, "rt_gen_rays: bad image size");
+    if (n == 0) return RT_OK;
+    CK(cudaSetDevice(ctx->device));
+    DevBuf<int> d_i, d_j; DevBuf<uint32_t> d_s; DevBuf<double> d_out;
+    CK(d_i.resize(n)); CK(d_j.resize(n)); CK(d_s.resize(n)); CK(d_out.resize(7 * n));
+    CK(cudaMemcpyAsync(d_i.p, px_i, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(d_j.p, px_j, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(d_s.p, sample, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    const CameraFrame<double> f = camera_frame(*cam);
+    cudaError_t e = precision == RT_F32
+        ? launch_gen_rays<float>(narrow_frame<float>(f), d_i.p, d_j.p, d_s.p, n, seed, d_out.p, ctx->stream)
+        : launch_gen_rays<double>(f, d_i.p, d_j.p, d_s.p, n, seed, d_out.p, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, d_out.p, n * sizeof(rt_ray), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    d_i.release(); d_j.release(); d_s.release(); d_out.release();
+    if (e != cudaSuccess) return cuda_fail(ctx, e, "rt_gen_rays");
+    return RT_OK;
+}
+
+extern "C" int rt_bench_closest(rt_ctx* ctx, const rt_camera* cam, size_t n, uint64_t seed, int precision,
+                                int backend, int repeats, double* ms, int32_t* prim_out, float* t_out,
+                                rt_ray* rays_out, size_t rays_out_n) {
+    if (!ctx || !cam) return RT_E_INVALID;
+    if (!ctx->has_scene) return fail(ctx, RT_E_STATE, "rt_bench_closest: no scene uploaded");
+    if (n == 0) return RT_OK;
+    CK(cudaSetDevice(ctx->device));
+    rt_camera c = *cam;
+    c.image_width = 8192; c.aspect_ratio = 1.0;                 // the virtual 8192 x 8192 image of SURVEY.md 8d
+    const CameraFrame<double> f = camera_frame(c);
+    rays_out_n = rays_out ? std::min(rays_out_n, n) : 0;
+    DevBuf<int> d_prim; DevBuf<float> d_t; DevBuf<double> d_rays;
+    CK(d_prim.resize(n)); CK(d_t.resize(n)); CK(d_rays.resize(std::max<size_t>(1, 7 * rays_out_n)));
+    size_t smem = 0;
+    cudaError_t e = cudaSuccess;
+    repeats = std::max(1, repeats);
+    float best = 1e30f;
+    for (int it = 0; it < repeats && e == cudaSuccess; ++it) {
+        cudaEventRecord(ctx->ev[2], ctx->stream);
+        if (precision == RT_F32) {
+            const bool staged = can_stage<float>(ctx, &smem);
+            e = launch_bench_closest<float>(scene_view<float>(ctx), narrow_frame<float>(f), n, seed, backend == RT_TRACE_BRUTE, staged, smem,
+                                            ctx->sm_count, d_prim.p, d_t.p, d_rays.p, rays_out_n, ctx->stream);
+        } else {
+            const bool staged = can_stage<double>(ctx, &smem);
+            e = launch_bench_closest<double>(scene_view<double>(ctx), f, n, seed, backend == RT_TRACE_BRUTE, staged, smem,
+                                             ctx->sm_count, d_prim.p, d_t.p, d_rays.p, rays_out_n, ctx->stream);
+        }
+        cudaEventRecord(ctx->ev[3], ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        float t = 0;
+        if (e == cudaSuccess && cudaEventElapsedTime(&t, ctx->ev[2], ctx->ev[3]) == cudaSuccess) best = std::min(best, t);
+    }
+    if (ms) *ms = best;
+    if (e == cudaSuccess && prim_out) e = cudaMemcpy(prim_out, d_prim.p, n * 4, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && t_out) e = cudaMemcpy(t_out, d_t.p, n * 4, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && rays_out_n) e = cudaMemcpy(rays_out, d_rays.p, rays_out_n * sizeof(rt_ray), cudaMemcpyDeviceToHost);
+    d_prim.release(); d_t.release(); d_rays.release();
+    if (e != cudaSuccess) return cuda_fail(ctx, e, "rt_bench_closest");
+    return RT_OK;
+}
+
+// -------------------------------------------------------------------- scene generators --
+// src/main.cpp:11-53.  The reference draws from one default-seeded std::mt19937 through
+// uniform_real_distribution<double>(0,1) (src/rtweekend.h:25-29); g++ evaluates the arguments
+// of vec3(...) right to left, so the draws are sequenced explicitly here.
+extern "C" size_t rt_scene_rtiow(int g, double p_diffuse, double p_metal, uint32_t mt_seed,
+                                 rt_sphere* spheres, rt_material* materials, size_t cap) {
+    std::mt19937 gen(mt_seed);
+    std::uniform_real_distribution<double> dist(0.0, 1.0);
+    auto rnd = [&]() { return dist(gen); };
+    auto rnd_range = [&](double lo, double hi) { return lo + (hi - lo) * rnd(); };
+    size_t n = 0;
+    auto push = [&](double cx, double cy, double cz, double vy, double r, bool moving, int type, double ar, double ag, double ab, double param) {
+        if (n < cap && spheres && materials) {
+            rt_sphere& s = spheres[n];
+            s.center1[0] = cx; s.center1[1] = cy; s.center1[2] = cz;
+            s.center_vec[0] = 0; s.center_vec[1] = vy; s.center_vec[2] = 0;
+            s.radius = r; s.is_moving = moving; s.material = int32_t(n);
+            rt_material& m = materials[n];
+            m.type = type; m.pad = 0; m.albedo[0] = ar; m.albedo[1] = ag; m.albedo[2] = ab; m.param = param;
+        }
+        ++n;
+    };
+    push(0, -1000, 0, 0, 1000, false, RT_LAMBERTIAN, 0.5, 0.5, 0.5, 0);
+    for (int a = -g; a < g; a++) {
+        for (int b = -g; b < g; b++) {
+            const double choose_mat = rnd();
+            const double cz = b + 0.9 * rnd();               // first draw feeds z (:20)
+            const double cx = a + 0.9 * rnd();
+            const double dx = cx - 4, dy = 0.2 - 0.2, dz = cz - 0;
+            if (std::sqrt(dx * dx + dy * dy + dz * dz) > 0.9) {
+                if (choose_mat < p_diffuse) {
+                    double rz = rnd(), ry = rnd(), rx = rnd();   // right operand of color::random()*color::random() first (:27)
+                    double lz = rnd(), ly = rnd(), lx = rnd();
+                    const double c2y = 0.2 + rnd_range(0, .5);   // center + vec3(0, random_double(0,.5), 0) (:29)
+                    push(cx, 0.2, cz, c2y - 0.2, 0.2, true, RT_LAMBERTIAN, lx * rx, ly * ry, lz * rz, 0);
+                } else if (choose_mat < p_metal) {
+                    double az = rnd_range(0.5, 1), ay = rnd_range(0.5, 1), ax = rnd_range(0.5, 1);
+                    const double fuzz = rnd_range(0, 0.5);
+                    push(cx, 0.2, cz, 0, 0.2, false, RT_METAL, ax, ay, az, fuzz < 1 ? fuzz : 1);
+                } else {
+                    push(cx, 0.2, cz, 0, 0.2, false, RT_DIELECTRIC, 0, 0, 0, 1.5);
+                }
+            }
+        }
+    }
+    push(0, 1, 0, 0, 1.0, false, RT_DIELECTRIC, 0, 0, 0, 1.5);
+    push(-4, 1, 0, 0, 1.0, false, RT_LAMBERTIAN, 0.4, 0.2, 0.1, 0);
+    push(4, 1, 0, 0, 1.0, false, RT_METAL, 0.7, 0.6, 0.5, 0.0);
+    return n;
+}
+
+// src/main.cpp:57-68; scale = g/11 moves the camera back for the wider grids of config 5
+extern "C" int rt_camera_rtiow(rt_camera* cam, int image_width, int spp, int max_depth, double scale) {
+    if (!cam) return RT_E_INVALID;
+    if (!(scale > 0)) scale = 1.0;
+    std::memset(cam, 0, sizeof *cam);
+    cam->aspect_ratio = 16.0 / 9.0;
+    cam->image_width = image_width;
+    cam->samples_per_pixel = spp;
+    cam->max_depth = max_depth;
+    cam->vfov = 20;
+    cam->lookfrom[0] = 13 * scale; cam->lookfrom[1] = 2 * scale; cam->lookfrom[2] = 3 * scale;
+    cam->lookat[0] = cam->lookat[1] = cam->lookat[2] = 0;
+    cam->vup[0] = 0; cam->vup[1] = 1; cam->vup[2] = 0;
+    cam->defocus_angle = 0.6;
+    cam->focus_dist = 10.0 * scale;
+    return RT_OK;
+}

@@ -1,0 +1,188 @@
+// rt_bvh_host.cpp -- SAH BVH builder on the host (see rt_bvh_host.h).
+#include "rt_bvh_host.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <limits>
+#include <numeric>
+
+namespace rt {
+
+namespace {
+
+float down(double v) { float f = float(v); if (double(f) > v) f = std::nextafterf(f, -INFINITY); return f; }
+float up(double v)   { float f = float(v); if (double(f) < v) f = std::nextafterf(f, INFINITY); return f; }
+
+struct Box {
+    float lo[3] = { INFINITY, INFINITY, INFINITY }, hi[3] = { -INFINITY, -INFINITY, -INFINITY };
+    void grow(const HostBox& b) { for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], b.lo[a]); hi[a] = std::max(hi[a], b.hi[a]); } }
+    void grow(const Box& b) { for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], b.lo[a]); hi[a] = std::max(hi[a], b.hi[a]); } }
+    double area() const {
+        const double dx = double(hi[0]) - lo[0], dy = double(hi[1]) - lo[1], dz = double(hi[2]) - lo[2];
+        if (dx < 0) return 0;
+        return 2.0 * (dx * dy + dy * dz + dz * dx);
+    }
+};
+
+struct TmpNode { Box box; int left = -1, right = -1; int first = 0, count = 0; };   // leaf iff left < 0
+
+struct Builder {
+    const std::vector<HostBox>& boxes;
+    int max_leaf;
+    std::vector<int> idx;
+    std::vector<TmpNode> nodes;
+    std::vector<float> cen[3];
+    std::vector<double> suffix;
+
+    Builder(const std::vector<HostBox>& b, int ml) : boxes(b), max_leaf(ml) {
+        idx.resize(b.size());
+        std::iota(idx.begin(), idx.end(), 0);
+        for (int a = 0; a < 3; ++a) {
+            cen[a].resize(b.size());
+            for (size_t i = 0; i < b.size(); ++i) cen[a][i] = 0.5f * (b[i].lo[a] + b[i].hi[a]);
+        }
+        suffix.resize(b.size() + 1);
+        nodes.reserve(2 * b.size() + 1);
+    }
+
+    int build(int first, int count) {
+        const int me = int(nodes.size());
+        nodes.emplace_back();
+        Box bb;
+        for (int i = first; i < first + count; ++i) bb.grow(boxes[idx[i]]);
+        nodes[me].box = bb;
+        nodes[me].first = first; nodes[me].count = count;
+        if (count == 1) return me;
+
+        // exact SAH sweep on every axis for small ranges, 32-bin SAH above
+        const double inv_area = 1.0 / std::max(bb.area(), 1e-300);
+        double best_cost = std::numeric_limits<double>::infinity();
+        int best_axis = -1, best_split = -1;      // split = number of prims on the left after sorting by axis
+        float best_plane = 0; bool binned = count > 4096;
+        if (!binned) {
+            for (int a = 0; a < 3; ++a) {
+                std::sort(idx.begin() + first, idx.begin() + first + count, [&](int x, int y) {
+                    return cen[a][x] < cen[a][y] || (cen[a][x] == cen[a][y] && x < y); });
+                Box r;
+                for (int i = count - 1; i >= 1; --i) { r.grow(boxes[idx[first + i]]); suffix[i] = r.area(); }
+                Box l;
+                for (int i = 1; i < count; ++i) {
+                    l.grow(boxes[idx[first + i - 1]]);
+                    const double cost = 1.0 + (l.area() * i + suffix[i] * (count - i)) * inv_area;
+                    if (cost < best_cost) { best_cost = cost; best_axis = a; best_split = i; }
+                }
+            }
+        } else {
+            const int NB = 32;
+            for (int a = 0; a < 3; ++a) {
+                float cmin = INFINITY, cmax = -INFINITY;
+                for (int i = first; i < first + count; ++i) { cmin = std::min(cmin, cen[a][idx[i]]); cmax = std::max(cmax, cen[a][idx[i]]); }
+                if (!(cmax > cmin)) continue;
+                Box bin[NB]; int cnt[NB] = { 0 };
+                const float scale = NB / (cmax - cmin);
+                for (int i = first; i < first + count; ++i) {
+                    int k = std::min(NB - 1, std::max(0, int((cen[a][idx[i]] - cmin) * scale)));
+                    bin[k].grow(boxes[idx[i]]); cnt[k]++;
+                }
+                double ra[NB]; int rc[NB];
+                Box r; int c = 0;
+                for (int k = NB - 1; k >= 1; --k) { r.grow(bin[k]); c += cnt[k]; ra[k] = r.area(); rc[k] = c; }
+                Box l; c = 0;
+                for (int k = 1; k < NB; ++k) {
+                    l.grow(bin[k - 1]); c += cnt[k - 1];
+                    if (c == 0 || rc[k] == 0) continue;
+                    const double cost = 1.0 + (l.area() * c + ra[k] * rc[k]) * inv_area;
+                    if (cost < best_cost) { best_cost = cost; best_axis = a; best_split = c; best_plane = cmin + k / scale; }
+                }
+            }
+        }
+        const double leaf_cost = double(count);
+        if (count <= max_leaf && (best_axis < 0 || leaf_cost <= best_cost)) return me;      // leaf
+        if (best_axis < 0) {                                                                // all centroids equal
+            best_axis = 0; best_split = count / 2; binned = false;
+        }
+        if (!binned) {
+            if (best_axis != 2 || true)
+                std::sort(idx.begin() + first, idx.begin() + first + count, [&](int x, int y) {
+                    return cen[best_axis][x] < cen[best_axis][y] || (cen[best_axis][x] == cen[best_axis][y] && x < y); });
+        } else {
+            auto mid = std::partition(idx.begin() + first, idx.begin() + first + count, [&](int x) {
+                return cen[best_axis][x] < best_plane; });
+            best_split = int(mid - (idx.begin() + first));
+            if (best_split == 0 || best_split == count) {
+                std::sort(idx.begin() + first, idx.begin() + first + count, [&](int x, int y) { return cen[best_axis][x] < cen[best_axis][y]; });
+                best_split = count / 2;
+            }
+        }
+        const int l = build(first, best_split);
+        const int r = build(first + best_split, count - best_split);
+        nodes[me].left = l; nodes[me].right = r;
+        return me;
+    }
+};
+
+int leaf_ref(int first, int count) { return ~((first << 3) | (count - 1)); }
+
+}  // namespace
+
+HostBox sphere_box(const double c1[3], const double cv[3], double radius, bool moving) {
+    HostBox b;
+    const double r = std::fabs(radius);
+    for (int a = 0; a < 3; ++a) {
+        double lo = c1[a] - r, hi = c1[a] + r;
+        if (moving) { lo = std::min(lo, c1[a] + cv[a] - r); hi = std::max(hi, c1[a] + cv[a] + r); }
+        const double pad = std::ldexp(std::max(std::max(std::fabs(lo), std::fabs(hi)), r), -20) + 1e-30;
+        b.lo[a] = down(lo - pad);
+        b.hi[a] = up(hi + pad);
+    }
+    return b;
+}
+
+void build_bvh_sah(const std::vector<HostBox>& boxes, int max_leaf, HostBVH& out) {
+    out = HostBVH();
+    const int n = int(boxes.size());
+    if (n == 0) return;
+    max_leaf = std::min(8, std::max(1, max_leaf));
+    Builder b(boxes, max_leaf);
+    b.build(0, n);
+    out.order = b.idx;
+    // a leaf range longer than 8 cannot be encoded; the builder never makes one (count <= max_leaf)
+    if (b.nodes[0].left < 0) {                       // whole scene is one leaf
+        out.root_ref = leaf_ref(0, b.nodes[0].count);
+        out.depth = 1;
+        return;
+    }
+    // BFS renumbering of inner nodes so the top of the tree is a prefix of the node array
+    std::vector<int> bfs, inner_id(b.nodes.size(), -1), level(b.nodes.size(), 0);
+    bfs.push_back(0);
+    for (size_t q = 0; q < bfs.size(); ++q) {
+        const TmpNode& nd = b.nodes[bfs[q]];
+        inner_id[bfs[q]] = int(q);
+        for (int ch : { nd.left, nd.right })
+            if (b.nodes[ch].left >= 0) { level[ch] = level[bfs[q]] + 1; bfs.push_back(ch); }
+    }
+    out.n_inner = int(bfs.size());
+    out.nodes.assign(size_t(out.n_inner) * 16, 0.0f);
+    int depth = 0;
+    for (size_t q = 0; q < bfs.size(); ++q) {
+        const TmpNode& nd = b.nodes[bfs[q]];
+        const TmpNode& L = b.nodes[nd.left];
+        const TmpNode& R = b.nodes[nd.right];
+        float* f = &out.nodes[q * 16];
+        f[0] = L.box.lo[0]; f[1] = L.box.lo[1]; f[2] = L.box.lo[2]; f[3] = L.box.hi[0];
+        f[4] = L.box.hi[1]; f[5] = L.box.hi[2]; f[6] = R.box.lo[0]; f[7] = R.box.lo[1];
+        f[8] = R.box.lo[2]; f[9] = R.box.hi[0]; f[10] = R.box.hi[1]; f[11] = R.box.hi[2];
+        const int lref = L.left >= 0 ? inner_id[nd.left] : leaf_ref(L.first, L.count);
+        const int rref = R.left >= 0 ? inner_id[nd.right] : leaf_ref(R.first, R.count);
+        std::memcpy(&f[12], &lref, 4);
+        std::memcpy(&f[13], &rref, 4);
+        depth = std::max(depth, level[bfs[q]] + 2);
+    }
+    out.root_ref = 0;
+    out.depth = depth;
+}
+
+int bvh_depth(const HostBVH& b) { return b.depth; }
+
+}  // namespace rt

@@ -1,0 +1,246 @@
+// rt_device.cuh -- device-side math of the path-tracing hot path, templated on the arithmetic
+// type T (float = fast mode, double = parity mode).
+//
+// Parity mode contract: every function below performs the SAME IEEE operations in the SAME
+// order as the reference lines it cites (paths relative to the reference tree), and the
+// translation unit that instantiates T = double is compiled with --fmad=false, so results are
+// bit-identical to the g++ -ffp-contract=off build of the reference wherever only + - * / sqrt
+// are involved.  The one deliberate exception is pow(x,5) (src/material.h:80), evaluated as
+// x*x*x*x*x; it only feeds a comparison against a 24-bit uniform.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace rt {
+
+// ------------------------------------------------------------------------------- vec3 --
+// src/vec3.h:8-119.  Note operator/(v,t) is (1/t)*v (src/vec3.h:101-103), not v.e/t.
+template <typename T> struct Vec { T x, y, z; };
+
+template <typename T> __host__ __device__ __forceinline__ Vec<T> mk(T x, T y, T z) { Vec<T> v; v.x = x; v.y = y; v.z = z; return v; }
+template <typename T> __host__ __device__ __forceinline__ Vec<T> operator+(Vec<T> a, Vec<T> b) { return mk<T>(a.x + b.x, a.y + b.y, a.z + b.z); }
+template <typename T> __host__ __device__ __forceinline__ Vec<T> operator-(Vec<T> a, Vec<T> b) { return mk<T>(a.x - b.x, a.y - b.y, a.z - b.z); }
+template <typename T> __host__ __device__ __forceinline__ Vec<T> operator-(Vec<T> a) { return mk<T>(-a.x, -a.y, -a.z); }
+template <typename T> __host__ __device__ __forceinline__ Vec<T> operator*(Vec<T> a, Vec<T> b) { return mk<T>(a.x * b.x, a.y * b.y, a.z * b.z); }
+template <typename T> __host__ __device__ __forceinline__ Vec<T> operator*(T t, Vec<T> a) { return mk<T>(t * a.x, t * a.y, t * a.z); }
+template <typename T> __host__ __device__ __forceinline__ T dot(Vec<T> a, Vec<T> b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+template <typename T> __host__ __device__ __forceinline__ T len2(Vec<T> a) { return a.x * a.x + a.y * a.y + a.z * a.z; }
+
+__device__ __forceinline__ float  rt_sqrt(float x)  { return sqrtf(x); }   // IEEE: TU built with -prec-sqrt=true
+__device__ __forceinline__ double rt_sqrt(double x) { return sqrt(x); }
+__device__ __forceinline__ float  rt_fmin(float a, float b)   { return fminf(a, b); }
+__device__ __forceinline__ double rt_fmin(double a, double b) { return fmin(a, b); }
+__device__ __forceinline__ float  rt_fabs(float a)  { return fabsf(a); }
+__device__ __forceinline__ double rt_fabs(double a) { return fabs(a); }
+
+template <typename T> __device__ __forceinline__ Vec<T> unit_vector(Vec<T> v) { return (T(1) / rt_sqrt(len2(v))) * v; }   // src/vec3.h:117-119
+template <typename T> __device__ __forceinline__ Vec<T> reflect(Vec<T> v, Vec<T> n) { return v - (T(2) * dot(v, n)) * n; }   // src/vec3.h:149-151
+
+// src/vec3.h:153-158
+template <typename T> __device__ __forceinline__ Vec<T> refract(Vec<T> uv, Vec<T> n, T etai_over_etat) {
+    T cos_theta = rt_fmin(dot(-uv, n), T(1));
+    Vec<T> r_out_perp = etai_over_etat * (uv + cos_theta * n);
+    Vec<T> r_out_parallel = (-rt_sqrt(rt_fabs(T(1) - len2(r_out_perp)))) * n;
+    return r_out_perp + r_out_parallel;
+}
+
+// ------------------------------------------------------------------------------ philox --
+// Replaces the global mt19937 of src/rtweekend.h:25-29 (keyed-stream contract):
+// Philox4x32-10, key = seed, counter = (pixel, sample, stage, k >> 2), draw k uses word k & 3,
+// u = (word >> 8) * 2^-24 -- exactly representable in float and double.
+struct Philox {
+    uint32_t key0, key1;
+    uint32_t pixel, sample, stage, k;
+    uint32_t w0, w1, w2, w3;
+
+    __device__ __forceinline__ void init(uint64_t seed) { key0 = uint32_t(seed); key1 = uint32_t(seed >> 32); k = 0; pixel = sample = stage = 0; }
+    __device__ __forceinline__ void set(uint32_t px, uint32_t s, uint32_t st) { pixel = px; sample = s; stage = st; k = 0; }
+
+    __device__ __forceinline__ void generate(uint32_t block) {
+        uint32_t c0 = pixel, c1 = sample, c2 = stage, c3 = block;
+        uint32_t k0 = key0, k1 = key1;
+#pragma unroll
+        for (int r = 0; r < 10; ++r) {
+            const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+            const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+            c0 = hi1 ^ c1 ^ k0; c1 = lo1; c2 = hi0 ^ c3 ^ k1; c3 = lo0;
+            k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+        }
+        w0 = c0; w1 = c1; w2 = c2; w3 = c3;
+    }
+
+    // 24-bit integer m of the next draw; u = m * 2^-24
+    __device__ __forceinline__ uint32_t next24() {
+        const uint32_t lane = k & 3u;
+        if (lane == 0u) generate(k >> 2);
+        ++k;
+        const uint32_t w = lane == 0u ? w0 : (lane == 1u ? w1 : (lane == 2u ? w2 : w3));
+        return w >> 8;
+    }
+};
+
+template <typename T> __device__ __forceinline__ T u01(uint32_t m) { return T(m) * T(1.0 / 16777216.0); }   // random_double()
+
+// random_double(-1,1) = -1 + 2*u (src/rtweekend.h:31-34): with u = m*2^-24 this is the exact
+// value a * 2^-23, a = m - 2^23.  The rejection tests |p|^2 < 1 of src/vec3.h:124,132 are exact
+// in double (sums < 2^48 in units of 2^-46); evaluating them on the integers makes the float
+// path take the same accept/reject decision as the reference.
+__device__ __forceinline__ int32_t sym24(uint32_t m) { return int32_t(m) - (1 << 23); }
+
+// src/vec3.h:129-135 with the g++ draw order z, y, x
+template <typename T> __device__ __forceinline__ Vec<T> random_in_unit_sphere(Philox& rng) {
+    for (;;) {
+        const int32_t az = sym24(rng.next24());
+        const int32_t ay = sym24(rng.next24());
+        const int32_t ax = sym24(rng.next24());
+        const int64_t l2 = int64_t(ax) * ax + int64_t(ay) * ay + int64_t(az) * az;
+        if (l2 < (int64_t(1) << 46))
+            return mk<T>(T(ax) * T(1.0 / 8388608.0), T(ay) * T(1.0 / 8388608.0), T(az) * T(1.0 / 8388608.0));
+    }
+}
+
+// ------------------------------------------------------------------------------ camera --
+// Derived camera frame (src/camera.h:118-125), computed on the host in double by the exact
+// formulas of camera::initialize (src/camera.h:52-85) and narrowed to T.
+template <typename T> struct CameraFrame {
+    Vec<T> center, pixel00_loc, pixel_delta_u, pixel_delta_v, defocus_disk_u, defocus_disk_v;
+    int image_width, image_height;
+    int defocus;     // defocus_angle > 0
+};
+
+template <typename T> struct Ray { Vec<T> o, d; T tm; };
+
+// src/camera.h:87-113.  Draw order: px, py (:104-105); disk iterations, first draw -> y,
+// second -> x (src/vec3.h:123 under g++); time (:97).  Stream stage 0.
+template <typename T> __device__ __forceinline__ Ray<T> get_ray(const CameraFrame<T>& c, int i, int j, Philox& rng) {
+    const Vec<T> pixel_center = (c.pixel00_loc + T(i) * c.pixel_delta_u) + T(j) * c.pixel_delta_v;
+    const T px = T(-0.5) + u01<T>(rng.next24());
+    const T py = T(-0.5) + u01<T>(rng.next24());
+    const Vec<T> pixel_sample = pixel_center + (px * c.pixel_delta_u + py * c.pixel_delta_v);
+    Ray<T> r;
+    if (!c.defocus) {
+        r.o = c.center;
+    } else {
+        int32_t ax, ay;
+        for (;;) {
+            ay = sym24(rng.next24());
+            ax = sym24(rng.next24());
+            if (int64_t(ax) * ax + int64_t(ay) * ay < (int64_t(1) << 46)) break;
+        }
+        const T dx = T(ax) * T(1.0 / 8388608.0), dy = T(ay) * T(1.0 / 8388608.0);
+        r.o = (c.center + dx * c.defocus_disk_u) + dy * c.defocus_disk_v;
+    }
+    r.d = pixel_sample - r.o;
+    r.tm = u01<T>(rng.next24());
+    return r;
+}
+
+// ------------------------------------------------------------------------------ sphere --
+// One sphere slot of the tagged SoA scene (replaces class sphere, src/sphere.h:60-66, and the
+// material it points to): a = (center1.xyz, radius), b = (center_vec.xyz, radius^2),
+// c = (albedo.rgb, param); meta = list_index << 3 | is_moving << 2 | material tag.
+template <typename T> struct Quad;
+template <> struct Quad<float>  { typedef float4 type; };
+template <> struct Quad<double> { typedef double4 type; };
+
+#define RT_META_TYPE(m) ((m) & 3)
+#define RT_META_ID(m) ((m) >> 3)
+
+// src/sphere.h:68-72 -- center1 + time*center_vec.  Static spheres carry center_vec = 0, for
+// which the expression returns center1 exactly, so the is_moving branch (:31) is not needed.
+template <typename T> __device__ __forceinline__ Vec<T> sphere_center(const typename Quad<T>::type& a, const typename Quad<T>::type& b, T tm) {
+    return mk<T>(a.x, a.y, a.z) + tm * mk<T>(b.x, b.y, b.z);
+}
+
+// src/sphere.h:30-48 in the reference's own form (parity mode; also the double path the fast
+// mode uses for big spheres).  `a` = direction.length_squared() is hoisted per ray.  Returns the
+// accepted root or a negative value.  Tie rule of src/hittable_list.h:31 (strict <, first in
+// list wins) is restated order-independently: a root equal to tbest is accepted only from a
+// sphere with a smaller list index than the current best.
+template <typename T> __device__ __forceinline__ bool root_ok(T root, T tmin, T tbest, int id, int best_id) {
+    return tmin < root && (root < tbest || (root == tbest && id < best_id));
+}
+
+__device__ __forceinline__ bool sphere_hit_ref(const Vec<double>& o, const Vec<double>& d, double a, const Vec<double>& center,
+                                               double rr, double tmin, double tbest, int id, int best_id, double& t_out) {
+    const Vec<double> oc = o - center;
+    const double half_b = dot(oc, d);
+    const double c = len2(oc) - rr;
+    const double discriminant = half_b * half_b - a * c;
+    if (discriminant < 0) return false;
+    const double sqrtd = sqrt(discriminant);
+    double root = (-half_b - sqrtd) / a;
+    if (!root_ok(root, tmin, tbest, id, best_id)) {
+        root = (-half_b + sqrtd) / a;
+        if (!root_ok(root, tmin, tbest, id, best_id)) return false;
+    }
+    t_out = root;
+    return true;
+}
+
+// Fast-mode sphere test (float): the same quadratic, solved around the closest-approach point
+// so that r^2 - |l|^2 does not cancel catastrophically (l = oc - (oc.d/a) d).  inv_a = 1/a.
+__device__ __forceinline__ bool sphere_hit_f32(const Vec<float>& o, const Vec<float>& d, float inv_a, const Vec<float>& center,
+                                               float rr, float tmin, float tbest, int id, int best_id, float& t_out) {
+    const Vec<float> oc = o - center;
+    const float tca = -dot(oc, d) * inv_a;
+    const Vec<float> l = oc + tca * d;
+    const float disc = rr - len2(l);
+    if (disc < 0.0f) return false;
+    const float s = sqrtf(disc * inv_a);
+    float root = tca - s;
+    if (!root_ok(root, tmin, tbest, id, best_id)) {
+        root = tca + s;
+        if (!root_ok(root, tmin, tbest, id, best_id)) return false;
+    }
+    t_out = root;
+    return true;
+}
+
+// ---------------------------------------------------------------------------- materials --
+// material::scatter for the three materials (src/material.h:19-25, :35-41, :52-71).  `n` is the
+// face-corrected normal (src/hittable.h:15-21).  Returns false when the ray is absorbed.
+template <typename T> __device__ __forceinline__ T reflectance(T cosine, T ref_idx) {   // src/material.h:76-81
+    T r0 = (T(1) - ref_idx) / (T(1) + ref_idx);
+    r0 = r0 * r0;
+    const T x = T(1) - cosine;
+    const T x2 = x * x;
+    return r0 + (T(1) - r0) * ((x2 * x2) * x);
+}
+
+template <typename T> __device__ __forceinline__ bool scatter(int type, Vec<T> albedo, T param, const Vec<T>& d_in, const Vec<T>& n,
+                                                              bool front_face, Philox& rng, Vec<T>& attenuation, Vec<T>& d_out) {
+    if (type == 0) {                                   // lambertian, no near_zero guard (:21)
+        d_out = n + unit_vector(random_in_unit_sphere<T>(rng));
+        attenuation = albedo;
+        return true;
+    } else if (type == 1) {                            // metal: 3k draws even when fuzz == 0 (:38)
+        const Vec<T> reflected = reflect(unit_vector(d_in), n);
+        d_out = reflected + param * random_in_unit_sphere<T>(rng);
+        attenuation = albedo;
+        return dot(d_out, n) > T(0);
+    } else {                                           // dielectric
+        attenuation = mk<T>(T(1), T(1), T(1));
+        const T refraction_ratio = front_face ? (T(1) / param) : param;
+        const Vec<T> unit_direction = unit_vector(d_in);
+        const T cos_theta = rt_fmin(dot(-unit_direction, n), T(1));
+        const T sin_theta = rt_sqrt(T(1) - cos_theta * cos_theta);
+        const bool cannot_refract = refraction_ratio * sin_theta > T(1);
+        // `||` short-circuit (:64): the uniform is drawn only when refraction is possible
+        if (cannot_refract || reflectance(cos_theta, refraction_ratio) > u01<T>(rng.next24()))
+            d_out = reflect(unit_direction, n);
+        else
+            d_out = refract(unit_direction, n, refraction_ratio);
+        return true;
+    }
+}
+
+// src/camera_cpu.h:23-25
+template <typename T> __device__ __forceinline__ Vec<T> sky(const Vec<T>& d) {
+    const Vec<T> unit_direction = unit_vector(d);
+    const T a = T(0.5) * (unit_direction.y + T(1));
+    return (T(1) - a) * mk<T>(T(1), T(1), T(1)) + a * mk<T>(T(0.5), T(0.7), T(1));
+}
+
+}  // namespace rt

@@ -1,0 +1,181 @@
+// rt_frame.cu -- framebuffer passes (the only HBM-bound part of the path):
+//   resolve : sum of sample slices (+ peer partial buffers over NVLink) -> write_color bytes
+//   encode  : bytes -> the P3 text camera::render prints, byte-identical
+// Restates src/color.h:9-12,14-35 (1/spp, sqrt gamma, clamp [0,0.999], int(256*x), "r g b\n")
+// and the header of src/camera.h:35.  Arithmetic is double as in the reference.
+#include "rt_frame.h"
+
+namespace rt {
+
+__device__ __forceinline__ unsigned char write_color_byte(double sum, double scale) {
+    double v = sum * scale;              // src/color.h:20-23
+    v = sqrt(v);                         // :26-28 (linear_to_gamma)
+    if (v < 0.000) v = 0.000;            // :31 interval(0.000, 0.999).clamp, src/interval.h:14-18
+    if (v > 0.999) v = 0.999;
+    return (unsigned char)(int)(256 * v);
+}
+
+// One thread = 4 consecutive pixels: 4 x Quad loads per slice/peer (64 or 128 contiguous bytes),
+// 3 x 32-bit stores of packed rgb.  Slices and peers are summed in a fixed order, so the image is
+// reproducible.  peers[] are device pointers of other ranks' buffers opened through CUDA IPC: the
+// loads cross NVLink inside this kernel (fused reduce + resolve).
+template <typename Q>
+__global__ void resolve_kernel(const Q* __restrict__ accum, int slices, PeerList peers, size_t n_pixels, double scale,
+                               double* __restrict__ sum_out, unsigned char* __restrict__ rgb8, Q* __restrict__ reduced_out) {
+    const size_t g = (size_t(blockIdx.x) * blockDim.x + threadIdx.x) * 4;
+    if (g >= n_pixels) return;
+    double s[4][4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) s[k][0] = s[k][1] = s[k][2] = s[k][3] = 0.0;
+    const int np = int(min(size_t(4), n_pixels - g));
+    for (int sl = 0; sl < slices; ++sl) {
+        const Q* src = accum + size_t(sl) * n_pixels + g;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) if (k < np) { const Q v = src[k]; s[k][0] += double(v.x); s[k][1] += double(v.y); s[k][2] += double(v.z); s[k][3] += double(v.w); }
+    }
+    for (int p = 0; p < peers.n; ++p) {
+        const Q* base = reinterpret_cast<const Q*>(peers.ptr[p]);
+        for (int sl = 0; sl < peers.slices[p]; ++sl) {
+            const Q* src = base + size_t(sl) * n_pixels + g;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) if (k < np) { const Q v = src[k]; s[k][0] += double(v.x); s[k][1] += double(v.y); s[k][2] += double(v.z); s[k][3] += double(v.w); }
+        }
+    }
+    unsigned char b[12];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        if (k < np) {
+            const double sc = scale > 0.0 ? scale : 1.0 / s[k][3];       // spp_total = 0: samples actually accumulated
+            b[3 * k + 0] = write_color_byte(s[k][0], sc);
+            b[3 * k + 1] = write_color_byte(s[k][1], sc);
+            b[3 * k + 2] = write_color_byte(s[k][2], sc);
+            if (sum_out) { sum_out[3 * (g + k) + 0] = s[k][0]; sum_out[3 * (g + k) + 1] = s[k][1]; sum_out[3 * (g + k) + 2] = s[k][2]; }
+            if (reduced_out) { Q v; v.x = decltype(v.x)(s[k][0]); v.y = decltype(v.x)(s[k][1]); v.z = decltype(v.x)(s[k][2]); v.w = decltype(v.x)(s[k][3]); reduced_out[g + k] = v; }
+        } else {
+            b[3 * k] = b[3 * k + 1] = b[3 * k + 2] = 0;
+        }
+    }
+    if (rgb8) {
+        if (np == 4) {
+            unsigned int* dst = reinterpret_cast<unsigned int*>(rgb8 + 3 * g);      // g % 4 == 0 -> 12-byte groups, 4-aligned
+            dst[0] = b[0] | (b[1] << 8) | (b[2] << 16) | (unsigned(b[3]) << 24);
+            dst[1] = b[4] | (b[5] << 8) | (b[6] << 16) | (unsigned(b[7]) << 24);
+            dst[2] = b[8] | (b[9] << 8) | (b[10] << 16) | (unsigned(b[11]) << 24);
+        } else {
+            for (int k = 0; k < 3 * np; ++k) rgb8[3 * g + k] = b[k];
+        }
+    }
+}
+
+template <typename Q>
+cudaError_t launch_resolve(const Q* accum, int slices, const PeerList& peers, size_t n_pixels, double scale,
+                           double* sum_out, unsigned char* rgb8, Q* reduced_out, cudaStream_t st) {
+    if (n_pixels == 0) return cudaSuccess;
+    const size_t threads = (n_pixels + 3) / 4;
+    resolve_kernel<Q><<<unsigned((threads + 255) / 256), 256, 0, st>>>(accum, slices, peers, n_pixels, scale, sum_out, rgb8, reduced_out);
+    return cudaGetLastError();
+}
+template cudaError_t launch_resolve<float4>(const float4*, int, const PeerList&, size_t, double, double*, unsigned char*, float4*, cudaStream_t);
+template cudaError_t launch_resolve<double4>(const double4*, int, const PeerList&, size_t, double, double*, unsigned char*, double4*, cudaStream_t);
+
+// ------------------------------------------------------------------------- P3 encoder --
+// "r g b\n" with variable-width decimals (src/color.h:32-34) needs a prefix sum of line lengths:
+// pass 1 per-block totals, pass 2 scan of the totals (one block), pass 3 block-local scan,
+// text staged in shared memory and copied out with consecutive threads writing consecutive bytes.
+#define ENC_BLOCK 256
+#define ENC_PPT 4                      // pixels per thread
+#define ENC_TILE (ENC_BLOCK * ENC_PPT)
+
+__device__ __forceinline__ int ndigits(unsigned v) { return v >= 100 ? 3 : (v >= 10 ? 2 : 1); }
+__device__ __forceinline__ int line_len(const unsigned char* p) { return ndigits(p[0]) + ndigits(p[1]) + ndigits(p[2]) + 3; }
+
+__device__ __forceinline__ unsigned block_exclusive_scan(unsigned v, unsigned* warp_sums, unsigned& total) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    unsigned x = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const unsigned y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    if (lane == 31) warp_sums[wid] = x;
+    __syncthreads();
+    if (wid == 0) {
+        unsigned w = lane < (ENC_BLOCK / 32) ? warp_sums[lane] : 0;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const unsigned y = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += y; }
+        if (lane < (ENC_BLOCK / 32)) warp_sums[lane] = w;       // inclusive
+    }
+    __syncthreads();
+    total = warp_sums[ENC_BLOCK / 32 - 1];
+    const unsigned base = wid > 0 ? warp_sums[wid - 1] : 0;
+    __syncthreads();
+    return base + x - v;
+}
+
+__global__ void __launch_bounds__(ENC_BLOCK) encode_count_kernel(const unsigned char* __restrict__ rgb8, size_t n_pixels, unsigned* __restrict__ block_sums) {
+    __shared__ unsigned warp_sums[ENC_BLOCK / 32];
+    const size_t p0 = size_t(blockIdx.x) * ENC_TILE + size_t(threadIdx.x) * ENC_PPT;
+    unsigned len = 0;
+    for (int k = 0; k < ENC_PPT; ++k) if (p0 + k < n_pixels) len += line_len(rgb8 + 3 * (p0 + k));
+    unsigned total;
+    block_exclusive_scan(len, warp_sums, total);
+    if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
+}
+
+// exclusive scan of block_sums in place (64-bit offsets out), single block
+__global__ void __launch_bounds__(ENC_BLOCK) encode_scan_kernel(const unsigned* __restrict__ block_sums, int n_blocks,
+                                                                  unsigned long long* __restrict__ block_offsets, unsigned long long header_len,
+                                                                  unsigned long long* __restrict__ total_len) {
+    __shared__ unsigned warp_sums[ENC_BLOCK / 32];
+    unsigned long long carry = header_len;
+    for (int base = 0; base < n_blocks; base += ENC_BLOCK) {
+        const int i = base + threadIdx.x;
+        const unsigned v = i < n_blocks ? block_sums[i] : 0;
+        unsigned total;
+        const unsigned ex = block_exclusive_scan(v, warp_sums, total);
+        if (i < n_blocks) block_offsets[i] = carry + ex;
+        carry += total;
+    }
+    if (threadIdx.x == 0) *total_len = carry;
+}
+
+__device__ __forceinline__ int put_number(char* dst, unsigned v) {
+    int n = 0;
+    if (v >= 100) { dst[n++] = char('0' + v / 100); v %= 100; dst[n++] = char('0' + v / 10); dst[n++] = char('0' + v % 10); }
+    else if (v >= 10) { dst[n++] = char('0' + v / 10); dst[n++] = char('0' + v % 10); }
+    else dst[n++] = char('0' + v);
+    return n;
+}
+
+__global__ void __launch_bounds__(ENC_BLOCK) encode_write_kernel(const unsigned char* __restrict__ rgb8, size_t n_pixels,
+                                                                   const unsigned long long* __restrict__ block_offsets,
+                                                                   char* __restrict__ text, EncodeHeader hdr) {
+    __shared__ unsigned warp_sums[ENC_BLOCK / 32];
+    __shared__ char stage[ENC_TILE * 12];
+    const size_t p0 = size_t(blockIdx.x) * ENC_TILE + size_t(threadIdx.x) * ENC_PPT;
+    unsigned len = 0;
+    for (int k = 0; k < ENC_PPT; ++k) if (p0 + k < n_pixels) len += line_len(rgb8 + 3 * (p0 + k));
+    unsigned total;
+    unsigned off = block_exclusive_scan(len, warp_sums, total);
+    for (int k = 0; k < ENC_PPT; ++k) {
+        if (p0 + k >= n_pixels) break;
+        const unsigned char* px = rgb8 + 3 * (p0 + k);
+        off += put_number(stage + off, px[0]); stage[off++] = ' ';
+        off += put_number(stage + off, px[1]); stage[off++] = ' ';
+        off += put_number(stage + off, px[2]); stage[off++] = '\n';
+    }
+    __syncthreads();
+    char* dst = text + block_offsets[blockIdx.x];
+    for (unsigned i = threadIdx.x; i < total; i += ENC_BLOCK) dst[i] = stage[i];
+    if (blockIdx.x == 0 && threadIdx.x < hdr.len) text[threadIdx.x] = hdr.text[threadIdx.x];   // "P3\nW H\n255\n"
+}
+
+int encode_blocks(size_t n_pixels) { return int((n_pixels + ENC_TILE - 1) / ENC_TILE); }
+
+cudaError_t launch_encode_p3(const unsigned char* rgb8, size_t n_pixels, const EncodeHeader& hdr, unsigned* block_sums,
+                             unsigned long long* block_offsets, unsigned long long* total_len, char* text, cudaStream_t st) {
+    const int nb = encode_blocks(n_pixels);
+    if (nb > 0) encode_count_kernel<<<nb, ENC_BLOCK, 0, st>>>(rgb8, n_pixels, block_sums);
+    encode_scan_kernel<<<1, ENC_BLOCK, 0, st>>>(block_sums, nb, block_offsets, (unsigned long long)hdr.len, total_len);
+    if (nb > 0) encode_write_kernel<<<nb, ENC_BLOCK, 0, st>>>(rgb8, n_pixels, block_offsets, text, hdr);
+    return cudaGetLastError();
+}
+
+}  // namespace rt

@@ -1,0 +1,55 @@
+// rt_kernels_impl.inl -- launchers, included by rt_kernels_f32.cu / rt_kernels_f64.cu with RT_REAL set.
+#include "rt_kernels.cuh"
+
+namespace rt {
+
+template <> cudaError_t launch_render_mega<RT_REAL>(const RenderParams<RT_REAL>& p, bool staged, size_t smem_bytes, int sm_count, cudaStream_t st) {
+    const int block = RT_MEGA_BLOCK(RT_REAL);
+    const int grid = sm_count * RT_MEGA_MINBLOCKS(RT_REAL);       // persistent: resident CTAs only
+    if (staged) {
+        cudaError_t e = cudaFuncSetAttribute(render_mega_kernel<RT_REAL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem_bytes));
+        if (e != cudaSuccess) return e;
+        render_mega_kernel<RT_REAL, true><<<grid, block, smem_bytes, st>>>(p);
+    } else {
+        render_mega_kernel<RT_REAL, false><<<grid, block, 0, st>>>(p);
+    }
+    return cudaGetLastError();
+}
+
+template <> cudaError_t launch_trace_closest<RT_REAL>(const SceneView<RT_REAL>& sv, const double* rays, size_t n, double tmin, double tmax,
+                                                      int brute, HitRec* out, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    trace_closest_kernel<RT_REAL><<<unsigned((n + 127) / 128), 128, 0, st>>>(sv, rays, n, tmin, tmax, brute, out);
+    return cudaGetLastError();
+}
+
+template <> cudaError_t launch_scatter<RT_REAL>(const MatRec* mats, const double* rays_in, const HitRec* hits, size_t n, uint64_t seed,
+                                                int* flag, double* att, double* rays_out, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    scatter_kernel<RT_REAL><<<unsigned((n + 127) / 128), 128, 0, st>>>(mats, rays_in, hits, n, seed, flag, att, rays_out);
+    return cudaGetLastError();
+}
+
+template <> cudaError_t launch_gen_rays<RT_REAL>(const CameraFrame<RT_REAL>& cam, const int* px_i, const int* px_j, const uint32_t* sample,
+                                                 size_t n, uint64_t seed, double* rays_out, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    gen_rays_kernel<RT_REAL><<<unsigned((n + 127) / 128), 128, 0, st>>>(cam, px_i, px_j, sample, n, seed, rays_out);
+    return cudaGetLastError();
+}
+
+template <> cudaError_t launch_bench_closest<RT_REAL>(const SceneView<RT_REAL>& sv, const CameraFrame<RT_REAL>& cam, size_t n, uint64_t seed, int brute,
+                                                      bool staged, size_t smem_bytes, int sm_count, int* prim_out, float* t_out,
+                                                      double* rays_out, size_t rays_out_n, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    const int grid = sm_count * 4;
+    if (staged) {
+        cudaError_t e = cudaFuncSetAttribute(bench_closest_kernel<RT_REAL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem_bytes));
+        if (e != cudaSuccess) return e;
+        bench_closest_kernel<RT_REAL, true><<<grid, 256, smem_bytes, st>>>(sv, cam, n, seed, brute, prim_out, t_out, rays_out, rays_out_n);
+    } else {
+        bench_closest_kernel<RT_REAL, false><<<grid, 256, 0, st>>>(sv, cam, n, seed, brute, prim_out, t_out, rays_out, rays_out_n);
+    }
+    return cudaGetLastError();
+}
+
+}  // namespace rt

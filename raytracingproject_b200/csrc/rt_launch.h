@@ -1,0 +1,46 @@
+// rt_launch.h -- host-visible launch interface of the per-precision kernel translation units.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "rt_trace.cuh"
+
+namespace rt {
+
+// megakernel shape: float 512 threads x 2 CTAs/SM (<= 64 regs), double 256 x 2 (<= 128 regs)
+#define RT_MEGA_BLOCK(T) (sizeof(T) == 4 ? 512 : 256)
+#define RT_MEGA_MINBLOCKS(T) 2
+
+template <typename T> struct RenderParams {
+    CameraFrame<T> cam;
+    SceneView<T> scene;
+    typename Quad<T>::type* accum;      // [slices][H][W] (sum.rgb, samples)
+    unsigned int* job_counter;
+    unsigned long long* ray_counter;
+    uint64_t seed;
+    int sample_begin, sample_count, max_depth;
+    int slices, tiles_x, tiles_y;
+    int accumulate;
+};
+
+struct HitRec;
+struct MatRec;
+
+// bytes of shared memory the staged scene needs
+template <typename T> inline size_t staged_bytes(int n_nodes, int n_slots) {
+    return size_t(n_nodes) * 64 + size_t(n_slots) * (3 * sizeof(typename Quad<T>::type) + sizeof(int));
+}
+
+template <typename T> cudaError_t launch_render_mega(const RenderParams<T>& p, bool staged, size_t smem_bytes, int sm_count, cudaStream_t st);
+template <typename T> cudaError_t launch_trace_closest(const SceneView<T>& sv, const double* rays, size_t n, double tmin, double tmax,
+                                                       int brute, HitRec* out, cudaStream_t st);
+template <typename T> cudaError_t launch_scatter(const MatRec* mats, const double* rays_in, const HitRec* hits, size_t n, uint64_t seed,
+                                                 int* flag, double* att, double* rays_out, cudaStream_t st);
+template <typename T> cudaError_t launch_gen_rays(const CameraFrame<T>& cam, const int* px_i, const int* px_j, const uint32_t* sample,
+                                                  size_t n, uint64_t seed, double* rays_out, cudaStream_t st);
+template <typename T> cudaError_t launch_bench_closest(const SceneView<T>& sv, const CameraFrame<T>& cam, size_t n, uint64_t seed, int brute,
+                                                       bool staged, size_t smem_bytes, int sm_count, int* prim_out, float* t_out,
+                                                       double* rays_out, size_t rays_out_n, cudaStream_t st);
+
+}  // namespace rt

@@ -1,0 +1,217 @@
+// rt_trace.cuh -- scene view, BVH traversal and surface reconstruction (device side).
+//
+// Replaces hittable_list::hit (src/hittable_list.h:25-39) and the bvh_node::hit contract
+// (src/bvh.h:16-24: box test, near child, then far child with t_max narrowed) with an iterative,
+// short-stack traversal over flat 64-byte node records, four 128-bit loads per visit.
+#pragma once
+
+#include "rt_device.cuh"
+
+namespace rt {
+
+#define RT_SENTINEL ((int)0x80000000)
+#define RT_STACK 64
+
+// Node record (one per inner node, 64 B = 4 x float4), boxes of BOTH children, padded outwards:
+//   q0 = (Lmin.x, Lmin.y, Lmin.z, Lmax.x)   q1 = (Lmax.y, Lmax.z, Rmin.x, Rmin.y)
+//   q2 = (Rmin.z, Rmax.x, Rmax.y, Rmax.z)   q3 = (bits left_ref, bits right_ref, -, -)
+// child ref >= 0: inner node index; < 0: leaf, ~ref = first_slot << 3 | (count - 1).
+template <typename T> struct SceneView {
+    typedef typename Quad<T>::type Q;
+    const float4* nodes;       // global
+    const Q* sa;               // (center1, radius)
+    const Q* sb;               // (center_vec, radius^2)
+    const Q* sc;               // (albedo, param)
+    const int* meta;           // list_index << 3 | moving << 2 | material tag
+    // big spheres: outside the tree, always double, tested first
+    const double4* big_a;
+    const double4* big_b;
+    const double4* big_c;
+    const int* big_meta;
+    int n_slots, n_nodes, n_big, root_ref;
+};
+
+// Slab test, src/aabb.h:35-53 with 1/d hoisted.  Returns entry distance in tnear.
+// float rays: (plane - o) * inv keeps the error relative (2 ulp), covered by the 1+2^-21 factor.
+__device__ __forceinline__ bool slab(float lx, float ly, float lz, float hx, float hy, float hz,
+                                     const Vec<float>& o, const Vec<float>& inv, float tmin, float tmax, float& tnear) {
+    const float t0x = (lx - o.x) * inv.x, t1x = (hx - o.x) * inv.x;
+    const float t0y = (ly - o.y) * inv.y, t1y = (hy - o.y) * inv.y;
+    const float t0z = (lz - o.z) * inv.z, t1z = (hz - o.z) * inv.z;
+    const float tn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), tmin));
+    const float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), tmax));
+    tnear = tn;
+    return tn <= tf * 1.0000005f;
+}
+// double rays against the float boxes (exactly representable in double): the boxes' outward
+// padding (>= 2^-20 relative) dwarfs double rounding.
+__device__ __forceinline__ bool slab(float lx, float ly, float lz, float hx, float hy, float hz,
+                                     const Vec<double>& o, const Vec<double>& inv, double tmin, double tmax, double& tnear) {
+    const double t0x = (double(lx) - o.x) * inv.x, t1x = (double(hx) - o.x) * inv.x;
+    const double t0y = (double(ly) - o.y) * inv.y, t1y = (double(hy) - o.y) * inv.y;
+    const double t0z = (double(lz) - o.z) * inv.z, t1z = (double(hz) - o.z) * inv.z;
+    const double tn = fmax(fmax(fmin(t0x, t1x), fmin(t0y, t1y)), fmax(fmin(t0z, t1z), tmin));
+    const double tf = fmin(fmin(fmax(t0x, t1x), fmax(t0y, t1y)), fmin(fmax(t0z, t1z), tmax));
+    tnear = tn;
+    return tn <= tf;
+}
+
+__device__ __forceinline__ bool leaf_sphere(const float4& a, const float4& b, const Ray<float>& r, float a_len2, float inv_a,
+                                            float tmin, float tbest, int id, int best_id, float& t) {
+    (void)a_len2;
+    return sphere_hit_f32(r.o, r.d, inv_a, sphere_center<float>(a, b, r.tm), b.w, tmin, tbest, id, best_id, t);
+}
+__device__ __forceinline__ bool leaf_sphere(const double4& a, const double4& b, const Ray<double>& r, double a_len2, double inv_a,
+                                            double tmin, double tbest, int id, int best_id, double& t) {
+    (void)inv_a;
+    return sphere_hit_ref(r.o, r.d, a_len2, sphere_center<double>(a, b, r.tm), b.w, tmin, tbest, id, best_id, t);
+}
+
+// Closest hit in (tmin, tmax).  slot_out: tree slot, n_slots + k for big sphere k, or -1.
+// nodes/sa/sb/meta may point to shared memory (staged scene) or global memory.
+template <typename T>
+__device__ __forceinline__ void trace_closest(const SceneView<T>& sv, const float4* __restrict__ nodes,
+                                              const typename Quad<T>::type* __restrict__ sa,
+                                              const typename Quad<T>::type* __restrict__ sb,
+                                              const int* __restrict__ meta,
+                                              const Ray<T>& r, T tmin, T tmax, T& t_out, int& slot_out) {
+    T tbest = tmax;
+    int best_id = -1, best_slot = -1;
+    const T a_len2 = len2(r.d);
+    const T inv_a = T(1) / a_len2;
+
+    // big spheres first, in double in both modes (the r = 1000 ground sphere): a tight t_max for
+    // the tree and no float cancellation in |oc|^2 - r^2
+    if (sv.n_big > 0) {
+        const Vec<double> od = mk<double>(r.o.x, r.o.y, r.o.z), dd = mk<double>(r.d.x, r.d.y, r.d.z);
+        const double ad = len2(dd);
+        double tb = double(tbest);
+        for (int k = 0; k < sv.n_big; ++k) {
+            const double4 a = sv.big_a[k], b = sv.big_b[k];
+            const int id = RT_META_ID(sv.big_meta[k]);
+            double t;
+            if (sphere_hit_ref(od, dd, ad, sphere_center<double>(a, b, double(r.tm)), b.w, double(tmin), tb, id, best_id, t)) {
+                tb = t; best_id = id; best_slot = sv.n_slots + k;
+            }
+        }
+        tbest = T(tb);
+    }
+
+    const Vec<T> inv = mk<T>(T(1) / r.d.x, T(1) / r.d.y, T(1) / r.d.z);
+    int stack[RT_STACK];
+    int sp = 0;
+    int cur = sv.root_ref;
+    while (cur != RT_SENTINEL) {
+        if (cur >= 0) {
+            const float4 q0 = nodes[4 * cur + 0], q1 = nodes[4 * cur + 1], q2 = nodes[4 * cur + 2], q3 = nodes[4 * cur + 3];
+            T tl, tr;
+            const bool hl = slab(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, r.o, inv, tmin, tbest, tl);
+            const bool hr = slab(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, r.o, inv, tmin, tbest, tr);
+            const int cl = __float_as_int(q3.x), cr = __float_as_int(q3.y);
+            if (hl && hr) {
+                const bool left_first = tl <= tr;
+                cur = left_first ? cl : cr;
+                if (sp < RT_STACK) stack[sp++] = left_first ? cr : cl;
+            } else if (hl) {
+                cur = cl;
+            } else if (hr) {
+                cur = cr;
+            } else {
+                cur = sp > 0 ? stack[--sp] : RT_SENTINEL;
+            }
+        } else {
+            const int leaf = ~cur;
+            const int first = leaf >> 3, count = (leaf & 7) + 1;
+            for (int k = 0; k < count; ++k) {
+                const int slot = first + k;
+                const typename Quad<T>::type a = sa[slot], b = sb[slot];
+                const int id = RT_META_ID(meta[slot]);
+                T t;
+                if (leaf_sphere(a, b, r, a_len2, inv_a, tmin, tbest, id, best_id, t)) {
+                    tbest = t; best_id = id; best_slot = slot;
+                }
+            }
+            cur = sp > 0 ? stack[--sp] : RT_SENTINEL;
+        }
+    }
+    t_out = tbest;
+    slot_out = best_slot;
+}
+
+// Linear closest hit over every sphere in list order (device-side ground truth,
+// src/hittable_list.h:25-39).  Tree slots are visited in slot order, so the index tie rule is
+// applied explicitly.
+template <typename T>
+__device__ __forceinline__ void brute_closest(const SceneView<T>& sv, const Ray<T>& r, T tmin, T tmax, T& t_out, int& slot_out) {
+    T tbest = tmax;
+    int best_id = -1, best_slot = -1;
+    const T a_len2 = len2(r.d);
+    const T inv_a = T(1) / a_len2;
+    if (sv.n_big > 0) {
+        const Vec<double> od = mk<double>(r.o.x, r.o.y, r.o.z), dd = mk<double>(r.d.x, r.d.y, r.d.z);
+        const double ad = len2(dd);
+        double tb = double(tbest);
+        for (int k = 0; k < sv.n_big; ++k) {
+            const double4 a = sv.big_a[k], b = sv.big_b[k];
+            const int id = RT_META_ID(sv.big_meta[k]);
+            double t;
+            if (sphere_hit_ref(od, dd, ad, sphere_center<double>(a, b, double(r.tm)), b.w, double(tmin), tb, id, best_id, t)) {
+                tb = t; best_id = id; best_slot = sv.n_slots + k;
+            }
+        }
+        tbest = T(tb);
+    }
+    for (int slot = 0; slot < sv.n_slots; ++slot) {
+        const typename Quad<T>::type a = sv.sa[slot], b = sv.sb[slot];
+        const int id = RT_META_ID(sv.meta[slot]);
+        T t;
+        if (leaf_sphere(a, b, r, a_len2, inv_a, tmin, tbest, id, best_id, t)) {
+            tbest = t; best_id = id; best_slot = slot;
+        }
+    }
+    t_out = tbest;
+    slot_out = best_slot;
+}
+
+// What shading needs about the surface that was hit (replaces hit_record, src/hittable.h:7-22:
+// only (slot, t) leave the traversal; p / normal / front_face are rebuilt here,
+// src/sphere.h:50-54 + src/hittable.h:15-21).
+template <typename T> struct Surface {
+    Vec<T> p, normal, albedo;
+    T param;
+    int type, id;
+    bool front_face;
+};
+
+template <typename T>
+__device__ __forceinline__ Surface<T> surface_at(const SceneView<T>& sv, const typename Quad<T>::type* __restrict__ sa,
+                                                 const typename Quad<T>::type* __restrict__ sb,
+                                                 const typename Quad<T>::type* __restrict__ sc,
+                                                 const int* __restrict__ meta, const Ray<T>& r, T t, int slot) {
+    Surface<T> s;
+    s.p = r.o + t * r.d;                                               // src/ray.h:19-21
+    Vec<T> outward;
+    int m;
+    if (slot < sv.n_slots) {
+        const typename Quad<T>::type a = sa[slot], b = sb[slot], c = sc[slot];
+        m = meta[slot];
+        const Vec<T> center = sphere_center<T>(a, b, r.tm);
+        outward = (T(1) / a.w) * (s.p - center);                        // src/sphere.h:52
+        s.albedo = mk<T>(c.x, c.y, c.z); s.param = c.w;
+    } else {
+        const int k = slot - sv.n_slots;
+        const double4 a = sv.big_a[k], b = sv.big_b[k], c = sv.big_c[k];
+        m = sv.big_meta[k];
+        const Vec<double> center = sphere_center<double>(a, b, double(r.tm));
+        const Vec<double> od = (1.0 / a.w) * (mk<double>(s.p.x, s.p.y, s.p.z) - center);
+        outward = mk<T>(T(od.x), T(od.y), T(od.z));
+        s.albedo = mk<T>(T(c.x), T(c.y), T(c.z)); s.param = T(c.w);
+    }
+    s.type = RT_META_TYPE(m);
+    s.id = RT_META_ID(m);
+    s.front_face = dot(r.d, outward) < T(0);                           // src/hittable.h:19-20
+    s.normal = s.front_face ? outward : -outward;
+    return s;
+}
+
+}  // namespace rt
