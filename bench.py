@@ -1,0 +1,284 @@
+#!/usr/bin/env python
+"""bench.py -- BASELINE.json's headline metric on its named config.
+
+  metric   Msamples/s (and Mrays/s) of the RTiOW final scene, 1920x1080, 500 spp, max_depth 50
+           (BASELINE.json configs[2], "C3"; it fits one GPU, so it is also the N=1 workload)
+  step     one full frame: render (all 500 spp, sample-range sharded over the ranks) -> combine on
+           rank 0 -> resolve to the 8-bit image, everything resident on the device (`value`);
+           `e2e` = the same frame through the public API with HOST buffers: scene upload (H2D) +
+           render + resolve + P3 encode + read-back of rgb8 and the P3 text (D2H) every step.
+  N > 1    one process per GPU (torchrun), strong scaling of the one frame; partial accumulation
+           buffers are combined by an NCCL reduce (default) or the fused IPC peer-reduce resolve.
+
+`--impl reference` times the reference's own CPU code (oracle/_ref, the reference compiled in
+place; else the C oracle port) on this box's host cores on a bounded sample of the same frame.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WIDTH, SPP, DEPTH = 1920, 500, 50
+WORKLOAD = "C3: RTiOW final scene (485 spheres, main.cpp generator), 1920x1080, 500 spp, max_depth 50"
+F_RAY = 528.0            # algorithmic flops per ray at N = 485: 48*ceil(log2 N) + 96
+B_RAY = 608.0            # algorithmic L2 bytes per ray at N = 485: 64*ceil(log2 N) + 32
+
+
+def peaks():
+    p = {}
+    try:
+        p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    return p
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except Exception:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        busy = [c for c in sm if c > 0]
+        return {"sm_mhz": statistics.median(busy) if busy else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_reference_run(spp_sample, threads, steps=1, warmup=0):
+    """The reference's CPU path on a bounded sample of the C3 frame: full 1920x1080 resolution,
+    `spp_sample` of the 500 samples per pixel, linear hittable_list exactly as shipped."""
+    from oracle import oracle as O
+    s, m = O.scene_rtiow()
+    cam = O.camera_rtiow(WIDTH, spp_sample, DEPTH)
+    kind = "reference" if O.have_ref() and os.path.exists(O.LIB_REF) else "port"
+    impl = "ref" if kind == "reference" else "oracle"
+    times, rays = [], 0
+    for it in range(warmup + steps):
+        t0 = time.perf_counter()
+        r = O.render(s, m, cam, rng_mode=O.RNG_PHILOX, seed=0, nthreads=threads, impl=impl, use_bvh=False)
+        dt = time.perf_counter() - t0
+        if it >= warmup:
+            times.append(dt); rays = r["rays"]
+    dt = sum(times) / len(times)
+    samples = WIDTH * r["height"] * spp_sample
+    return {"value": samples / dt / 1e6, "unit": "Msamples/s", "cores": threads, "kind": kind,
+            "mrays_per_s": rays / dt / 1e6, "seconds_per_step": dt,
+            "sample": f"{WIDTH}x{r['height']} at {spp_sample} of {SPP} spp, depth {DEPTH}, linear hittable_list (no BVH, as "
+                      f"src/main.cpp:12,70), keyed Philox stream, {threads} host threads over rows"}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    spp_sample = max(1, args.ref_spp)
+    cb = cpu_reference_run(spp_sample, threads, steps=args.steps, warmup=min(args.warmup, 1))
+    line = {"impl": "reference", "metric": "Msamples/s", "value": cb["value"], "unit": "Msamples/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": cb["seconds_per_step"] * 1e3,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "timed_sample": cb["sample"]},
+            "mrays_per_s": cb["mrays_per_s"],
+            "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": cb["value"], "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--precision", default="f32", choices=["f32", "f64"])
+    ap.add_argument("--combine", default="nccl", choices=["nccl", "ipc"])
+    ap.add_argument("--spp", type=int, default=SPP, help="override spp (a non-default value is NOT the headline config)")
+    ap.add_argument("--ref-spp", type=int, default=1, help="spp of the CPU sample per step for --impl reference / cpu_baseline")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-check", action="store_true", help="skip the untimed f32-vs-f64 image check")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    args.warmup = max(args.warmup, 3)
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import raytracingproject_b200 as rt
+    from raytracingproject_b200 import sharding
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the B200 path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    prec = rt.F32 if args.precision == "f32" else rt.F64
+
+    ctx = rt.Context(local)
+    s, m = rt.scene_rtiow()
+    ctx.upload_scene(s, m)
+    cam = rt.camera_rtiow(WIDTH, args.spp, DEPTH)
+    W, H = WIDTH, 1080
+    stream = torch.cuda.ExternalStream(ctx.stream(), device=torch.device("cuda", local))
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")      # > 126 MB L2
+    begin, count = sharding.sample_shard(args.spp, rank, world)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # warm-up render so buffers exist, then set up the combine
+    sharding.render_sharded(ctx, cam, rank, world, prec)
+    ctx.synchronize()
+    acc = sharding.alias_accum_tensor(ctx) if world > 1 else None
+    if world > 1 and args.combine == "ipc":
+        handles = sharding.exchange_ipc_handles(ctx.ipc_export())
+        if rank == 0:
+            ctx.ipc_open_peers([h for r, h in enumerate(handles) if r != 0])
+
+    def step(e2e):
+        """one frame; returns nothing, everything is enqueued on ctx's stream"""
+        if e2e:
+            ctx.upload_scene(s, m)                                   # H2D: the world, every step
+        sharding.render_sharded(ctx, cam, rank, world, prec)
+        if world > 1:
+            if args.combine == "nccl":
+                with torch.cuda.stream(stream):
+                    sharding.reduce_partials(acc, dst=0)
+            else:
+                stream.synchronize(); dist.barrier()                 # peers' partials complete before rank 0 reads them
+        if rank == 0:
+            if e2e:
+                return ctx.readback(args.spp, want_sum=False, want_rgb8=True, want_ppm=True)
+            return ctx.readback(args.spp, want_sum=False, want_rgb8=False)   # resolve on device, nothing copied
+
+    def timed(e2e, steps, warmup):
+        for _ in range(warmup):
+            step(e2e)
+        times, rays, kernel_ms = [], 0, []
+        sampler = ClockSampler(local)
+        if rank == 0:
+            sampler.start()
+        for _ in range(steps):
+            flush.fill_(1)                                           # evict L2 between timed iterations
+            barrier()
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0 = time.perf_counter()
+            with torch.cuda.stream(stream):
+                ev0.record(stream)
+            out = step(e2e)
+            with torch.cuda.stream(stream):
+                ev1.record(stream)
+            barrier()
+            wall = (time.perf_counter() - t0) * 1e3
+            dev = ev0.elapsed_time(ev1)
+            # device-resident timing uses CUDA events on the launching stream; the end-to-end number
+            # includes host work (BVH build, memcpy completion), so it uses the wall clock between barriers
+            t = torch.tensor([wall if e2e else dev], dtype=torch.float64, device="cuda")
+            st = ctx.stats()
+            r = torch.tensor([st["rays"]], dtype=torch.int64, device="cuda")
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                dist.all_reduce(r, op=dist.ReduceOp.SUM)
+            times.append(t.item()); rays = int(r.item()); kernel_ms.append(st["render_ms"])
+        clocks = sampler.stop() if rank == 0 else None
+        return times, rays, kernel_ms, clocks, out
+
+    times, rays, kernel_ms, clocks, _ = timed(False, args.steps, args.warmup)
+    e2e_times, _, _, _, e2e_out = timed(True, max(2, min(args.steps, 3)), 1)
+    launches = ctx.stats()["kernel_launches"]
+
+    # untimed: the fast mode against parity mode on this very frame (north_star image tolerance)
+    check = None
+    if rank == 0 and world == 1 and not args.no_check and args.precision == "f32":
+        ctx.render(cam, precision=rt.F32, seed=0); a = ctx.readback(args.spp, want_sum=False)["rgb8"]
+        ctx.render(cam, precision=rt.F64, seed=0); b = ctx.readback(args.spp, want_sum=False)["rgb8"]
+        d = np.abs(a.astype(int) - b.astype(int)).max(-1)
+        mse = float(np.mean((a.astype(float) - b.astype(float)) ** 2))
+        check = {"f32_vs_f64_psnr_db": 99.0 if mse == 0 else 10 * np.log10(255.0 ** 2 / mse),
+                 "frac_pixels_within_1_of_255": float((d <= 1).mean()), "frac_pixels_identical": float((d == 0).mean())}
+
+    if rank == 0:
+        pk = peaks()
+        ms = sum(times) / len(times)
+        samples = W * H * args.spp
+        value = samples / ms / 1e3
+        kms = sum(kernel_ms) / len(kernel_ms)                          # rank 0's render kernel, CUDA events
+        rank_rays = rays / world
+        sm_mhz = (clocks or {}).get("sm_mhz") or pk.get("sm_max_mhz", 1965.0)
+        fp32_peak = 148 * 128 * 2 * sm_mhz * 1e6 / 1e12               # TFLOP/s at the clock seen under load
+        achieved = rank_rays * F_RAY / (kms * 1e-3) / 1e12
+        e2e_ms = sum(e2e_times) / len(e2e_times)
+        line = {
+            "metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": args.precision, "data": "synthetic",
+            "config": {"workload": WORKLOAD if args.spp == SPP else f"NOT the headline config: spp={args.spp}",
+                       "variant": "megakernel", "bvh": "host SAH, whole scene staged in shared memory", "seed": 0,
+                       "parallelism": f"sample-range sharding x{world}, combine={args.combine if world > 1 else 'none'}",
+                       "l2": "256 MB buffer written between timed iterations (L2 flushed); scene inputs are 55 KB"},
+            "mrays_per_s": rays / ms / 1e3, "rays_per_sample": rays / samples,
+            "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak,
+                         "traffic": None, "kernel": "render_mega_kernel", "kernel_ms": kms,
+                         "note": f"algorithmic {F_RAY:.0f} flop/ray x {rank_rays:.3e} rays per launch (SURVEY 8d); peak = 148 SMs x 128 "
+                                 f"FP32 lanes x 2 x {sm_mhz:.0f} MHz observed under load (not in MEASURED_PEAKS.json); L2-side figure "
+                                 f"{rank_rays * B_RAY / (kms * 1e-3) / 1e9:.0f} GB/s algorithmic ({B_RAY:.0f} B/ray)"},
+            "e2e": {"value": samples / e2e_ms / 1e3, "unit": "Msamples/s", "ms_per_step": e2e_ms,
+                    "h2d_bytes_per_step": int(s.nbytes + m.nbytes + 104),
+                    "d2h_bytes_per_step": int(W * H * 3 + (len(e2e_out["ppm"]) if e2e_out and e2e_out.get("ppm") else 0)),
+                    "api": "rt_upload_scene + rt_render + rt_readback(rgb8 + P3 text) per step, host buffers"},
+            "gpu_launches": int(launches) * args.steps, "clocks": clocks,
+        }
+        if check:
+            line["image_check"] = check
+        if not args.no_cpu_baseline and world == 1:
+            cb = cpu_reference_run(max(1, args.ref_spp), os.cpu_count() or 1)
+            line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

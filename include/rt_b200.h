@@ -196,6 +196,16 @@ int rt_bench_closest(rt_ctx *ctx, const rt_camera *cam, size_t n, uint64_t seed,
                      int backend, int repeats, double *ms, int32_t *prim_out, float *t_out,
                      rt_ray *rays_out, size_t rays_out_n);
 
+/* write_color (src/color.h:14-35) for n per-pixel sums (3 doubles each) through the resolve kernel,
+ * and the P3 encoder (src/camera.h:35 header + src/color.h:32-34 lines) for a w*h rgb8 image. */
+int rt_write_color(rt_ctx *ctx, const double *sums_rgb, size_t n, int samples_per_pixel, uint8_t *rgb8);
+int rt_encode_p3(rt_ctx *ctx, const uint8_t *rgb8, int width, int height, char *ppm, size_t *ppm_len);
+
+/* Host SAH builder on its own (no device needed): nodes_out receives 16 floats per inner node
+ * (layout in DESIGN.md), order_out the slot -> sphere index permutation.  Capacity: n-1 nodes, n slots. */
+int rt_build_bvh_host(const rt_sphere *spheres, size_t n, int max_leaf, float *nodes_out, int32_t *order_out,
+                      int32_t *root_ref, int32_t *depth, int32_t *n_inner);
+
 /* src/main.cpp:11-68 scene + camera generators (default-seeded mt19937, g++ draw order),
  * generalised for BASELINE configs 4 and 5: grid half-width g (11), thresholds p_diffuse (0.8),
  * p_metal (0.95).  Returns the sphere count (call with cap = 0 to size the arrays). */

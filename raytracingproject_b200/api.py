@@ -214,6 +214,34 @@ class Context:
         return dict(ms=ms.value, prim=prim, t=t, rays=rays)
 
 
+    def write_color(self, sums, spp):
+        sums = np.ascontiguousarray(sums, "f8").reshape(-1, 3)
+        out = np.zeros(sums.shape, "u1")
+        self._ck(self._lib.rt_write_color(self._h, L.ptr(sums), len(sums), spp, L.ptr(out)))
+        return out
+
+    def encode_p3(self, rgb8):
+        rgb8 = np.ascontiguousarray(rgb8, "u1")
+        H, W, _ = rgb8.shape
+        cap = C.c_size_t(H * W * 12 + 64)
+        buf = C.create_string_buffer(cap.value)
+        self._ck(self._lib.rt_encode_p3(self._h, L.ptr(rgb8), W, H, buf, C.byref(cap)))
+        return buf.raw[:cap.value]
+
+
+def build_bvh_host(spheres, max_leaf=4):
+    """Host SAH builder alone (no device).  -> dict(nodes (n_inner,16) f4, order, root_ref, depth)."""
+    spheres = np.ascontiguousarray(spheres)
+    n = len(spheres)
+    nodes = np.zeros((max(n, 1), 16), "f4")
+    order = np.zeros(max(n, 1), "i4")
+    root, depth, n_inner = C.c_int32(), C.c_int32(), C.c_int32()
+    rc = L.lib().rt_build_bvh_host(L.ptr(spheres), n, max_leaf, L.ptr(nodes), L.ptr(order), C.byref(root), C.byref(depth), C.byref(n_inner))
+    if rc != 0:
+        raise RtError("rt_build_bvh_host failed")
+    return dict(nodes=nodes[:n_inner.value], order=order[:n], root_ref=root.value, depth=depth.value)
+
+
 # ----------------------------------------------------------------------------- scenes --
 def scene_rtiow(g=11, p_diffuse=0.8, p_metal=0.95, mt_seed=5489):
     """The world of reference src/main.cpp:11-53 (g, thresholds generalised for configs 4/5)."""

@@ -718,3 +718,62 @@ extern "C" int rt_camera_rtiow(rt_camera* cam, int image_width, int spp, int max
     cam->focus_dist = 10.0 * scale;
     return RT_OK;
 }
+
+// ------------------------------------------------------- framebuffer / builder hooks --
+extern "C" int rt_write_color(rt_ctx* ctx, const double* sums_rgb, size_t n, int samples_per_pixel, uint8_t* rgb8) {
+    if (!ctx || (n && (!sums_rgb || !rgb8)) || samples_per_pixel < 1) return RT_E_INVALID;
+    if (n == 0) return RT_OK;
+    CK(cudaSetDevice(ctx->device));
+    std::vector<double4> q(n);
+    for (size_t i = 0; i < n; ++i) q[i] = make_double4(sums_rgb[3 * i], sums_rgb[3 * i + 1], sums_rgb[3 * i + 2], double(samples_per_pixel));
+    DevBuf<double4> d_q; DevBuf<unsigned char> d_b;
+    CK(d_q.resize(n)); CK(d_b.resize(3 * n + 16));
+    CK(cudaMemcpyAsync(d_q.p, q.data(), n * sizeof(double4), cudaMemcpyHostToDevice, ctx->stream));
+    PeerList none = {};
+    cudaError_t e = launch_resolve<double4>(d_q.p, 1, none, n, 1.0 / samples_per_pixel, nullptr, d_b.p, nullptr, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(rgb8, d_b.p, 3 * n, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    d_q.release(); d_b.release();
+    if (e != cudaSuccess) return cuda_fail(ctx, e, "rt_write_color");
+    return RT_OK;
+}
+
+extern "C" int rt_encode_p3(rt_ctx* ctx, const uint8_t* rgb8, int width, int height, char* ppm, size_t* ppm_len) {
+    if (!ctx || !rgb8 || !ppm_len || width < 1 || height < 1) return RT_E_INVALID;
+    CK(cudaSetDevice(ctx->device));
+    const size_t npix = size_t(width) * height;
+    EncodeHeader hdr;
+    hdr.len = std::snprintf(hdr.text, sizeof hdr.text, "P3\n%d %d\n255\n", width, height);
+    const int nb = encode_blocks(npix);
+    DevBuf<unsigned char> d_b; DevBuf<unsigned> d_s; DevBuf<unsigned long long> d_o; DevBuf<char> d_t;
+    CK(d_b.resize(3 * npix)); CK(d_s.resize(nb + 1)); CK(d_o.resize(nb + 2)); CK(d_t.resize(npix * 12 + 64));
+    CK(cudaMemcpyAsync(d_b.p, rgb8, 3 * npix, cudaMemcpyHostToDevice, ctx->stream));
+    unsigned long long len = 0;
+    cudaError_t e = launch_encode_p3(d_b.p, npix, hdr, d_s.p, d_o.p, d_o.p + nb + 1, d_t.p, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&len, d_o.p + nb + 1, sizeof len, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    int rc = RT_OK;
+    if (e == cudaSuccess) {
+        if (ppm && *ppm_len >= len) e = cudaMemcpy(ppm, d_t.p, size_t(len), cudaMemcpyDeviceToHost);
+        else if (ppm) rc = fail(ctx, RT_E_INVALID, "rt_encode_p3: ppm buffer too small");
+        *ppm_len = size_t(len);
+    }
+    d_b.release(); d_s.release(); d_o.release(); d_t.release();
+    if (e != cudaSuccess) return cuda_fail(ctx, e, "rt_encode_p3");
+    return rc;
+}
+
+extern "C" int rt_build_bvh_host(const rt_sphere* spheres, size_t n, int max_leaf, float* nodes_out, int32_t* order_out,
+                                 int32_t* root_ref, int32_t* depth, int32_t* n_inner) {
+    if (n && !spheres) return RT_E_INVALID;
+    std::vector<HostBox> boxes(n);
+    for (size_t k = 0; k < n; ++k) boxes[k] = sphere_box(spheres[k].center1, spheres[k].center_vec, spheres[k].radius, spheres[k].is_moving != 0);
+    HostBVH bvh;
+    build_bvh_sah(boxes, max_leaf > 0 ? max_leaf : 4, bvh);
+    if (nodes_out && !bvh.nodes.empty()) std::memcpy(nodes_out, bvh.nodes.data(), bvh.nodes.size() * sizeof(float));
+    if (order_out && n) std::memcpy(order_out, bvh.order.data(), n * sizeof(int));
+    if (root_ref) *root_ref = bvh.root_ref;
+    if (depth) *depth = bvh.depth;
+    if (n_inner) *n_inner = bvh.n_inner;
+    return RT_OK;
+}

@@ -1,0 +1,315 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI of librt_b200.so) against the CPU
+oracle on the same seeded inputs and against the reference-generated fixtures in tests/golden/.
+
+Tolerances are north_star's (BASELINE.json): closest-hit primitive id bit-exact; t and normals
+<= 1e-5 relative; scatter outputs <= 1e-6 relative given identical random inputs; images PSNR >= 45 dB
+with >= 99.9 % of pixels within 1/255.  Parity mode (RT_F64) is held to a stricter bar: bit-identical
+hits, scatter outputs, rays and 8-bit images.
+"""
+import numpy as np
+import pytest
+
+from conftest import golden, psnr8
+
+pytestmark = pytest.mark.gpu
+
+T_REL = 1e-5        # north_star: hit t and normals within 1e-5 relative
+SCATTER_REL = 1e-6  # north_star: scatter outputs within 1e-6 relative
+PSNR_MIN = 45.0     # north_star: image PSNR >= 45 dB
+FRAC_MIN = 0.999    # north_star: >= 99.9 % of pixels within 1/255
+
+
+def v3(a):
+    return np.stack([a["x"], a["y"], a["z"]], -1) if a.dtype.names == ("x", "y", "z") else np.asarray(a)
+
+
+def frac_within_1(a, b):
+    return float((np.abs(a.astype(int) - b.astype(int)).max(-1) <= 1).mean())
+
+
+# ------------------------------------------------------------------------ full image --
+def test_c1_image_f64_is_the_reference_image(ctx_scene, rt, O, scene):
+    """BASELINE config 1: final scene 400x225, 10 spp, depth 50.  Parity mode reproduces the
+    reference harness (fixture) and the oracle exactly: bytes, P3 text, ray count."""
+    s, m = scene
+    cam = rt.camera_rtiow(400, 10, 50)
+    ctx_scene.render(cam, precision=rt.F64, seed=0)
+    out = ctx_scene.readback(10, want_ppm=True)
+    st = ctx_scene.stats()
+    g = golden("ref_c1_philox_seed0.npz")
+    assert st["rays"] == int(g["rays"]) == 2324626
+    assert np.array_equal(out["rgb8"], g["rgb8"])
+    assert out["ppm"] == O.ppm_p3(g["rgb8"])
+    # iterative throughput product is left-nested, the reference's recursion right-nested: 1e-13
+    assert np.allclose(out["sum"][100:104], g["sum_rows"], rtol=1e-13, atol=1e-14)
+    ref = O.render(s, m, O.camera_rtiow(400, 10, 50), rng_mode=O.RNG_PHILOX, seed=0, use_bvh=True)
+    assert np.allclose(out["sum"], ref["sum"], rtol=1e-13, atol=1e-14)
+
+
+def test_c1_image_f32_within_north_star_tolerance(ctx_scene, rt):
+    cam = rt.camera_rtiow(400, 10, 50)
+    ctx_scene.render(cam, precision=rt.F32, seed=0)
+    out = ctx_scene.readback(10)
+    g = golden("ref_c1_philox_seed0.npz")
+    assert psnr8(out["rgb8"], g["rgb8"]) >= PSNR_MIN
+    assert frac_within_1(out["rgb8"], g["rgb8"]) >= FRAC_MIN
+    rays = ctx_scene.stats()["rays"]
+    assert abs(rays - int(g["rays"])) / int(g["rays"]) < 5e-3
+
+
+@pytest.mark.parametrize("seed,width,spp,depth", [(1, 160, 4, 50), (2**40 + 5, 97, 3, 7), (9, 64, 1, 1), (3, 48, 2, 0)])
+def test_small_images_f64_match_oracle(ctx_scene, rt, O, scene, seed, width, spp, depth):
+    """other seeds (incl. a 64-bit key), odd sizes (ragged 8x4 tiles), depth 1 and depth 0 (black)."""
+    s, m = scene
+    cam = rt.camera_rtiow(width, spp, depth)
+    ctx_scene.render(cam, precision=rt.F64, seed=seed)
+    out = ctx_scene.readback(spp, want_ppm=True)
+    ref = O.render(s, m, O.camera_rtiow(width, spp, depth), rng_mode=O.RNG_PHILOX, seed=seed, use_bvh=True)
+    assert ctx_scene.stats()["rays"] == ref["rays"]
+    assert np.array_equal(out["rgb8"], ref["rgb8"])
+    assert out["ppm"] == O.ppm_p3(ref["rgb8"])
+    assert np.allclose(out["sum"], ref["sum"], rtol=1e-13, atol=1e-14)
+    if depth == 0:
+        assert not out["rgb8"].any()
+
+
+def test_sample_ranges_accumulate_and_slices_do_not_change_the_image(ctx_scene, rt):
+    """sample-range shards (what a rank renders) add up to the full render; warp slices are invisible."""
+    cam = rt.camera_rtiow(200, 8, 50)
+    ctx_scene.render(cam, precision=rt.F64, seed=4, slices=1)
+    full = ctx_scene.readback(8)
+    ctx_scene.render(cam, precision=rt.F64, seed=4, slices=4)
+    sl = ctx_scene.readback(8)
+    assert np.array_equal(full["rgb8"], sl["rgb8"]) and np.allclose(full["sum"], sl["sum"], rtol=1e-13)
+    ctx_scene.render(cam, precision=rt.F64, seed=4, sample_begin=0, sample_count=3, slices=1)
+    ctx_scene.render(cam, precision=rt.F64, seed=4, sample_begin=3, sample_count=5, slices=1, accumulate=True)
+    acc = ctx_scene.readback(8)
+    assert np.array_equal(full["rgb8"], acc["rgb8"]) and np.allclose(full["sum"], acc["sum"], rtol=1e-13)
+    auto = ctx_scene.readback(0)                       # divisor taken from the buffer's own sample count
+    assert np.array_equal(auto["rgb8"], full["rgb8"])
+
+
+# ----------------------------------------------------------------------- closest hit --
+@pytest.mark.parametrize("backend", ["bvh", "brute"])
+def test_closest_hit_fixture(ctx_scene, rt, backend):
+    """reference-generated rays (camera, bounce-like, axis-aligned, origins inside spheres)"""
+    g = golden("ref_closest_hit.npz")
+    rays, want = g["rays"], g["hits"]
+    be = rt.TRACE_BVH if backend == "bvh" else rt.TRACE_BRUTE
+    h64 = ctx_scene.trace_closest(rays.view(rt.RAY), precision=rt.F64, backend=be)
+    assert h64.tobytes() == want.tobytes()              # parity mode: bit-identical records
+    h32 = ctx_scene.trace_closest(rays.view(rt.RAY), precision=rt.F32, backend=be)
+    assert np.array_equal(h32["prim"], want["prim"])    # primitive id bit-exact
+    hit = want["prim"] >= 0
+    assert hit.sum() > 1000 and (~hit).sum() > 100
+    assert np.all(np.abs(h32["t"][hit] - want["t"][hit]) <= T_REL * want["t"][hit])
+    assert np.abs(h32["normal"][hit] - v3(want["normal"][hit])).max() <= T_REL
+    assert np.array_equal(h32["front_face"], want["front_face"])
+
+
+def test_closest_hit_random_rays_vs_oracle_list(ctx_scene, rt, O, scene):
+    """incoherent rays from everywhere, incl. tmax-limited intervals; ground truth = linear list"""
+    s, _ = scene
+    rng = np.random.default_rng(5)
+    n = 30000
+    rays = np.zeros(n, rt.RAY)
+    rays["orig"] = rng.uniform([-12, 0.05, -12], [12, 3, 12], (n, 3))
+    d = rng.normal(size=(n, 3))
+    rays["dir"] = d / np.linalg.norm(d, axis=1, keepdims=True) * rng.uniform(0.1, 10, (n, 1))
+    rays["tm"] = rng.uniform(0, 1, n)
+    for tmin, tmax in ((0.001, np.inf), (0.5, 3.0)):
+        want = O.closest_hit(s, rays.view(O.RAY), tmin=tmin, tmax=tmax)
+        for be in (rt.TRACE_BVH, rt.TRACE_BRUTE):
+            h64 = ctx_scene.trace_closest(rays, tmin, tmax, precision=rt.F64, backend=be)
+            assert h64.tobytes() == want.tobytes()
+            h32 = ctx_scene.trace_closest(rays, tmin, tmax, precision=rt.F32, backend=be)
+            hit = want["prim"] >= 0
+            # a float ray may legitimately flip a grazing hit/miss; ids must agree wherever both hit
+            both = hit & (h32["prim"] >= 0)
+            assert (h32["prim"] != want["prim"]).mean() < 2e-3
+            same = both & (h32["prim"] == want["prim"])
+            assert np.all(np.abs(h32["t"][same] - want["t"][same]) <= T_REL * want["t"][same])
+
+
+def test_exact_ties_resolve_to_the_lowest_list_index(ctx, rt, O):
+    """two identical spheres: strict '<' in hittable_list::hit keeps the first (src/hittable_list.h:31)"""
+    s = np.zeros(3, rt.SPHERE)
+    m = np.zeros(3, rt.MATERIAL)
+    s["center1"] = [(0, 0, -5), (0, 0, -5), (3, 0, -5)]
+    s["radius"] = [1, 1, 1]
+    s["material"] = [0, 1, 2]
+    ctx.upload_scene(s, m)
+    rays = np.zeros(2, rt.RAY)
+    rays["dir"] = [(0, 0, -1), (0.6, 0, -1)]
+    want = O.closest_hit(s.view(O.SPHERE), rays.view(O.RAY))
+    for prec in (rt.F64, rt.F32):
+        for be in (rt.TRACE_BVH, rt.TRACE_BRUTE):
+            h = ctx.trace_closest(rays, precision=prec, backend=be)
+            assert h["prim"].tolist() == want["prim"].tolist() == [0, 2]
+
+
+# --------------------------------------------------------------- scatter and camera rays --
+def test_scatter_fixture(ctx, rt):
+    g = golden("ref_scatter.npz")
+    mats, rin, hits = g["materials"].view(rt.MATERIAL), g["rays_in"].view(rt.RAY), g["hits"].view(rt.HIT)
+    flag, att, out = ctx.scatter(mats, rin, hits, seed=11, precision=rt.F64)
+    assert np.array_equal(flag, g["flag"])
+    assert att.tobytes() == g["att"].tobytes()
+    assert out.tobytes() == g["out"].tobytes()           # parity mode: bit-identical scattered rays
+    flag32, att32, out32 = ctx.scatter(mats, rin, hits, seed=11, precision=rt.F32)
+    assert (flag32 != g["flag"]).mean() < 2e-3           # metal absorb test dot(d,n) > 0 can flip at 0
+    want_d = v3(g["out"]["dir"])
+    scale = np.linalg.norm(want_d, axis=1, keepdims=True)
+    assert np.all(np.abs(out32["dir"] - want_d) <= SCATTER_REL * np.maximum(scale, 1.0))
+    assert np.all(np.abs(att32 - v3(g["att"])) <= SCATTER_REL)
+    assert np.allclose(out32["orig"], v3(g["out"]["orig"]), rtol=SCATTER_REL, atol=1e-6)
+
+
+def test_scatter_metal_fuzz_is_clamped(ctx, rt, O):
+    """metal(albedo, 7.0) behaves as fuzz = 1 (src/material.h:33)"""
+    mats = np.zeros(64, rt.MATERIAL)
+    mats["type"], mats["albedo"], mats["param"] = rt.METAL, (0.8, 0.7, 0.6), 7.0
+    rin = np.zeros(64, rt.RAY)
+    rin["dir"] = (0.3, -1.0, 0.2)
+    hits = np.zeros(64, rt.HIT)
+    hits["normal"], hits["front_face"], hits["t"] = (0, 1, 0), 1, 1.0
+    f, a, o = ctx.scatter(mats, rin, hits, seed=2, precision=rt.F64)
+    fo, ao, oo = O.scatter(mats.view(O.MATERIAL), rin.view(O.RAY), hits.view(O.HIT), seed=2)
+    clamped = mats.copy()
+    clamped["param"] = 1.0
+    fc, ac, oc = O.scatter(clamped.view(O.MATERIAL), rin.view(O.RAY), hits.view(O.HIT), seed=2)
+    assert o.tobytes() == oc.tobytes() and np.array_equal(f, fc)
+    assert oo.tobytes() != oc.tobytes()                  # the oracle's POD takes fuzz as given (ctor clamps)
+
+
+def test_get_ray_fixture(ctx, rt):
+    g = golden("ref_get_rays.npz")
+    cam = rt.camera_rtiow(400, 10, 50)
+    r64 = ctx.gen_rays(cam, g["px_i"], g["px_j"], g["sample"], seed=5, precision=rt.F64)
+    assert r64.tobytes() == g["rays"].tobytes()
+    r32 = ctx.gen_rays(cam, g["px_i"], g["px_j"], g["sample"], seed=5, precision=rt.F32)
+    want = g["rays"]
+    assert np.allclose(r32["dir"], v3(want["dir"]), rtol=0, atol=SCATTER_REL * 12)
+    assert np.allclose(r32["orig"], v3(want["orig"]), rtol=SCATTER_REL)
+    assert np.array_equal(r32["tm"], want["tm"])         # 24-bit uniforms are exact in float
+
+
+def test_get_ray_without_defocus(ctx, rt, O):
+    cam = rt.camera_rtiow(120, 2, 5)
+    cam.defocus_angle = 0.0                              # src/camera.h:94: origin = center, no disk draws
+    oc = O.camera_rtiow(120, 2, 5)
+    oc["defocus_angle"] = 0.0
+    i, j, s = np.arange(50) % 120, np.arange(50) % 67, np.arange(50) % 2
+    want, _ = O.get_rays(oc, i, j, s, seed=8)
+    got = ctx.gen_rays(cam, i, j, s, seed=8, precision=rt.F64)
+    assert got.tobytes() == want.tobytes()
+
+
+# ------------------------------------------------------------------------- edge scenes --
+def _render_both(ctx, rt, O, s, m, cam, ocam, seed=0):
+    ctx.upload_scene(s, m)
+    ctx.render(cam, precision=rt.F64, seed=seed)
+    out = ctx.readback(cam.samples_per_pixel, want_ppm=True)
+    ref = O.render(s.view(O.SPHERE), m.view(O.MATERIAL), ocam, rng_mode=O.RNG_PHILOX, seed=seed)
+    return out, ref, ctx.stats()
+
+
+def test_empty_world_is_sky(ctx, rt, O):
+    s, m = np.zeros(0, rt.SPHERE), np.zeros(0, rt.MATERIAL)
+    out, ref, st = _render_both(ctx, rt, O, s, m, rt.camera_rtiow(64, 2, 10), O.camera_rtiow(64, 2, 10))
+    assert np.array_equal(out["rgb8"], ref["rgb8"]) and st["rays"] == ref["rays"] == 64 * 36 * 2
+    assert out["ppm"] == O.ppm_p3(ref["rgb8"])
+
+
+def test_ground_only_world(ctx, rt, O):
+    """the PixelMatch world of reference tests/tests.cpp:26-29 (one r = 1000 sphere, kept out of the tree)"""
+    s, m = rt.scene_rtiow()
+    out, ref, st = _render_both(ctx, rt, O, s[:1], m[:1], rt.camera_rtiow(80, 4, 50), O.camera_rtiow(80, 4, 50), seed=6)
+    assert st["n_big"] == 1 and st["n_nodes"] == 0
+    assert np.array_equal(out["rgb8"], ref["rgb8"]) and st["rays"] == ref["rays"]
+    assert np.allclose(out["sum"], ref["sum"], rtol=1e-13, atol=1e-14)
+
+
+def test_glass_metal_heavy_scene(ctx, rt, O):
+    """BASELINE config 4's scene shape (80 % glass/metal) at a small size"""
+    s, m = rt.scene_rtiow(11, 0.2, 0.6, 5489)
+    assert (m["type"] != rt.LAMBERTIAN).mean() > 0.7
+    out, ref, st = _render_both(ctx, rt, O, s, m, rt.camera_rtiow(128, 4, 50), O.camera_rtiow(128, 4, 50), seed=12)
+    assert np.array_equal(out["rgb8"], ref["rgb8"]) and st["rays"] == ref["rays"]
+    ctx.render(rt.camera_rtiow(128, 4, 50), precision=rt.F32, seed=12)
+    o32 = ctx.readback(4)
+    assert psnr8(o32["rgb8"], ref["rgb8"]) >= 35.0       # 4 spp: a flipped path is visible; bound is loose here
+
+
+def test_big_radius_option_keeps_results(ctx, rt, O):
+    """ground sphere inside the tree (big_radius < 0) or outside: same hits"""
+    s, m = rt.scene_rtiow()
+    g = golden("ref_closest_hit.npz")
+    for big in (-1.0, 0.5, 0.0):
+        ctx.upload_scene(s, m, big_radius=big)
+        h = ctx.trace_closest(g["rays"].view(rt.RAY), precision=rt.F64)
+        assert h.tobytes() == g["hits"].tobytes()
+    for leaf in (1, 2, 8):
+        ctx.upload_scene(s, m, max_leaf=leaf)
+        h = ctx.trace_closest(g["rays"].view(rt.RAY), precision=rt.F64)
+        assert h.tobytes() == g["hits"].tobytes()
+
+
+# ----------------------------------------------------------------------- framebuffer --
+def test_write_color_kernel_matches_oracle(ctx, rt, O):
+    rng = np.random.default_rng(1)
+    sums = np.concatenate([rng.uniform(0, 40, (5000, 3)), rng.uniform(0, 1e-3, (500, 3)),
+                           np.array([[0, 0, 0], [30, 30, 30], [1e12, 29.94003, 7.5], [0.03, 1e-300, 29.7]])])
+    assert np.array_equal(ctx.write_color(sums, 30), O.write_color(sums, 30))
+    # byte boundaries: sqrt(sum/spp)*256 just below / at an integer
+    k = np.arange(1, 256, dtype="f8")
+    edge = (k / 256.0) ** 2 * 10
+    for delta in (-1e-12, 0.0, 1e-12):
+        e3 = np.repeat((edge * (1 + delta))[:, None], 3, 1)
+        assert np.array_equal(ctx.write_color(e3, 10), O.write_color(e3, 10))
+
+
+def test_p3_encoder_is_byte_identical(ctx, rt, O):
+    rng = np.random.default_rng(2)
+    for h, w in ((1, 1), (3, 5), (37, 211), (225, 400)):
+        img = rng.integers(0, 256, (h, w, 3)).astype("u1")
+        img.flat[:9] = [0, 9, 10, 99, 100, 255, 1, 11, 111][: min(9, img.size)]
+        assert ctx.encode_p3(img) == O.ppm_p3(img)
+
+
+# ------------------------------------------------------- full-size, size-independent --
+def test_c3_full_size_properties(ctx_scene, rt):
+    """BASELINE config 3's frame (1920x1080, depth 50) at reduced spp: properties that do not need
+    the CPU oracle -- shard additivity, ray-count identity between precisions, f32 vs f64 image."""
+    spp = 24
+    cam = rt.camera_rtiow(1920, spp, 50)
+    ctx_scene.render(cam, precision=rt.F64, seed=0)
+    a = ctx_scene.readback(spp, want_sum=False)
+    ra = ctx_scene.stats()["rays"]
+    assert 2.55 < ra / (1920 * 1080 * spp) < 2.61        # 2.58 rays/sample on the final scene
+    ctx_scene.render(cam, precision=rt.F32, seed=0)
+    b = ctx_scene.readback(spp, want_sum=False)
+    rb = ctx_scene.stats()["rays"]
+    assert abs(ra - rb) / ra < 2e-3
+    assert psnr8(a["rgb8"], b["rgb8"]) >= PSNR_MIN
+    assert frac_within_1(a["rgb8"], b["rgb8"]) >= 0.995   # 24 spp; the 99.9 % bar is checked at 500 spp in the bench
+    # rays of two half renders add up to the rays of the full render
+    ctx_scene.render(cam, precision=rt.F32, seed=0, sample_begin=0, sample_count=12)
+    r1 = ctx_scene.stats()["rays"]
+    ctx_scene.render(cam, precision=rt.F32, seed=0, sample_begin=12, sample_count=12, accumulate=True)
+    r2 = ctx_scene.stats()["rays"]
+    c = ctx_scene.readback(spp, want_sum=False)
+    assert r1 + r2 == rb and np.array_equal(c["rgb8"], b["rgb8"])
+
+
+def test_errors_are_reported(ctx, rt):
+    cam = rt.camera_rtiow(32, 1, 1)
+    c2 = rt.Context(0)
+    with pytest.raises(rt.RtError, match="no scene"):
+        c2.render(cam)
+    s, m = rt.scene_rtiow()
+    bad = s.copy()
+    bad["material"][3] = 10_000
+    with pytest.raises(rt.RtError, match="material index"):
+        c2.upload_scene(bad, m)
+    c2.close()

@@ -1,0 +1,116 @@
+"""CPU: the C-ABI library loads and exports every symbol of include/rt_b200.h; host-side logic
+(scene generator, image size, BVH builder, shard planner) -- no compute calls, no GPU."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+
+
+def header_functions():
+    text = open(os.path.join(ROOT, "include", "rt_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(rt_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol(rt):
+    names = header_functions()
+    assert len(names) >= 20
+    L = C.CDLL(rt.LIB_PATH)
+    for n in names:
+        assert hasattr(L, n), f"librt_b200.so does not export {n}"
+    assert sorted(rt.SYMBOLS) == names, "python binding table and header disagree"
+    assert rt.lib().rt_abi_version() == rt.ABI
+
+
+def test_no_device_is_a_loud_error(rt):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(rt.RtError, match="no CUDA device"):
+        rt.Context(0)
+
+
+def test_product_scene_generator_matches_oracle(rt, O):
+    for g, pd, pm, seed in ((11, 0.8, 0.95, 5489), (11, 0.2, 0.6, 5489), (4, 0.8, 0.95, 7), (20, 0.5, 0.7, 1)):
+        s, m = rt.scene_rtiow(g, pd, pm, seed)
+        os_, om = O.scene_rtiow(g, pd, pm, seed)
+        assert s.tobytes() == os_.tobytes() and m.tobytes() == om.tobytes()
+    assert len(rt.scene_rtiow()[0]) == 485
+
+
+def test_image_size_and_camera(rt):
+    for w, want in ((400, 225), (1920, 1080), (3840, 2160), (3, 1)):
+        cam = rt.Camera()
+        cam.aspect_ratio, cam.image_width = 16.0 / 9.0, w
+        assert cam.image_size() == (w, want)
+    c = rt.camera_rtiow(1920, 500, 50)
+    assert (c.image_width, c.samples_per_pixel, c.max_depth, c.vfov) == (1920, 500, 50, 20.0)
+    assert list(c.lookfrom) == [13.0, 2.0, 3.0] and c.defocus_angle == 0.6 and c.focus_dist == 10.0
+
+
+def _check_bvh(spheres, b):
+    """every sphere in exactly one leaf; every sphere inside the boxes of all its ancestors"""
+    nodes, order, root = b["nodes"], b["order"], b["root_ref"]
+    n = len(spheres)
+    assert sorted(order.tolist()) == list(range(n))
+    c1, cv, r, mov = spheres["center1"], spheres["center_vec"], spheres["radius"], spheres["is_moving"] != 0
+    lo = np.minimum(c1 - r[:, None], np.where(mov[:, None], c1 + cv - r[:, None], np.inf))
+    hi = np.maximum(c1 + r[:, None], np.where(mov[:, None], c1 + cv + r[:, None], -np.inf))
+    seen = np.zeros(n, int)
+
+    def visit(ref, blo, bhi, depth):
+        if ref < 0:
+            leaf = ~ref
+            first, count = leaf >> 3, (leaf & 7) + 1
+            for slot in range(first, first + count):
+                i = order[slot]
+                seen[i] += 1
+                assert np.all(lo[i] >= blo) and np.all(hi[i] <= bhi)
+            return depth
+        f = nodes[ref]
+        refs = f[12:14].view("i4")
+        l = visit(int(refs[0]), np.maximum(blo, f[[0, 1, 2]]), np.minimum(bhi, f[[3, 4, 5]]), depth + 1)
+        r_ = visit(int(refs[1]), np.maximum(blo, f[[6, 7, 8]]), np.minimum(bhi, f[[9, 10, 11]]), depth + 1)
+        return max(l, r_)
+
+    d = visit(root, np.full(3, -np.inf), np.full(3, np.inf), 1)
+    assert np.all(seen == 1)
+    assert d == b["depth"]
+
+
+def test_host_bvh_builder(rt):
+    s, _ = rt.scene_rtiow()
+    small = s[1:]                                   # without the r = 1000 ground sphere, as the upload does
+    for max_leaf in (1, 4, 8):
+        b = rt.build_bvh_host(small, max_leaf)
+        _check_bvh(small, b)
+        assert b["depth"] <= 64
+    b = rt.build_bvh_host(s[:1])                    # single sphere: root is a leaf
+    assert b["root_ref"] < 0 and len(b["nodes"]) == 0
+    _check_bvh(s[:1], b)
+    assert rt.build_bvh_host(s[:0])["root_ref"] == -2 ** 31        # empty: sentinel
+    big, _ = rt.scene_rtiow(40)                     # > 4096 spheres: binned SAH path
+    b = rt.build_bvh_host(big[1:])
+    _check_bvh(big[1:], b)
+    # identical centres (degenerate split) still terminate and cover everything
+    same = np.repeat(s[5:6], 37)
+    _check_bvh(same, rt.build_bvh_host(same, 2))
+
+
+def test_sample_shards_partition_the_samples():
+    from raytracingproject_b200.sharding import row_shard, sample_shard
+    for spp in (1, 7, 10, 500, 1000):
+        for world in (1, 2, 3, 4, 8):
+            shards = [sample_shard(spp, r, world) for r in range(world)]
+            assert shards[0][0] == 0 and sum(c for _, c in shards) == spp
+            for (b0, c0), (b1, _) in zip(shards, shards[1:]):
+                assert b0 + c0 == b1
+            assert max(c for _, c in shards) - min(c for _, c in shards) <= 1
+    rows = np.concatenate([row_shard(225, r, 4) for r in range(4)])
+    assert sorted(rows.tolist()) == list(range(225))
+    with pytest.raises(ValueError):
+        sample_shard(10, 2, 2)
