@@ -74,19 +74,29 @@ def test_small_images_f64_match_oracle(ctx_scene, rt, O, scene, seed, width, spp
 
 
 def test_sample_ranges_accumulate_and_slices_do_not_change_the_image(ctx_scene, rt):
-    """sample-range shards (what a rank renders) add up to the full render; warp slices are invisible."""
+    """sample-range shards (what a rank renders) add up to the full render; warp slices only change the
+    order of the per-pixel sum.  That order matters in the last bit: this scene has sums sitting exactly
+    on a write_color byte boundary (pixel (34,74): blue = 0.5 over 8 spp -> sqrt(1/16)*256 = 64.0), so
+    re-associated sums may move such a pixel by one level; parity mode therefore defaults to one slice."""
+    def same_image(a, b):
+        d = np.abs(a["rgb8"].astype(int) - b["rgb8"].astype(int))
+        return d.max() <= 1 and (d > 0).any(-1).mean() < 1e-3 and np.allclose(a["sum"], b["sum"], rtol=1e-13, atol=1e-14)
+
     cam = rt.camera_rtiow(200, 8, 50)
-    ctx_scene.render(cam, precision=rt.F64, seed=4, slices=1)
+    ctx_scene.render(cam, precision=rt.F64, seed=4)
     full = ctx_scene.readback(8)
-    ctx_scene.render(cam, precision=rt.F64, seed=4, slices=4)
-    sl = ctx_scene.readback(8)
-    assert np.array_equal(full["rgb8"], sl["rgb8"]) and np.allclose(full["sum"], sl["sum"], rtol=1e-13)
-    ctx_scene.render(cam, precision=rt.F64, seed=4, sample_begin=0, sample_count=3, slices=1)
-    ctx_scene.render(cam, precision=rt.F64, seed=4, sample_begin=3, sample_count=5, slices=1, accumulate=True)
+    assert ctx_scene.stats()["slices"] == 1
+    ctx_scene.render(cam, precision=rt.F64, seed=4, slices=8)     # one sample per slice: resolve adds them in sample order
+    assert np.array_equal(ctx_scene.readback(8)["rgb8"], full["rgb8"])
+    for sl in (2, 4):
+        ctx_scene.render(cam, precision=rt.F64, seed=4, slices=sl)
+        assert same_image(ctx_scene.readback(8), full)
+    ctx_scene.render(cam, precision=rt.F64, seed=4, sample_begin=0, sample_count=3)
+    ctx_scene.render(cam, precision=rt.F64, seed=4, sample_begin=3, sample_count=5, accumulate=True)
     acc = ctx_scene.readback(8)
-    assert np.array_equal(full["rgb8"], acc["rgb8"]) and np.allclose(full["sum"], acc["sum"], rtol=1e-13)
+    assert same_image(acc, full)
     auto = ctx_scene.readback(0)                       # divisor taken from the buffer's own sample count
-    assert np.array_equal(auto["rgb8"], full["rgb8"])
+    assert np.array_equal(auto["rgb8"], acc["rgb8"])
 
 
 # ----------------------------------------------------------------------- closest hit --
@@ -128,7 +138,13 @@ def test_closest_hit_random_rays_vs_oracle_list(ctx_scene, rt, O, scene):
             both = hit & (h32["prim"] >= 0)
             assert (h32["prim"] != want["prim"]).mean() < 2e-3
             same = both & (h32["prim"] == want["prim"])
-            assert np.all(np.abs(h32["t"][same] - want["t"][same]) <= T_REL * want["t"][same])
+            # 1e-5 relative, plus what narrowing the ray origin to float costs by itself: these origins
+            # are ~12 units out, so the float ray starts up to 2^-24*|o| away from the double one, which
+            # moves t by that distance over |d| no matter how the kernel computes (visible when t is tiny)
+            o_mag = np.linalg.norm(rays["orig"], axis=1)[same]
+            d_mag = np.linalg.norm(rays["dir"], axis=1)[same]
+            floor = 4 * 2.0 ** -24 * (o_mag + 1.0) / d_mag
+            assert np.all(np.abs(h32["t"][same] - want["t"][same]) <= T_REL * want["t"][same] + floor)
 
 
 def test_exact_ties_resolve_to_the_lowest_list_index(ctx, rt, O):
@@ -299,7 +315,9 @@ def test_c3_full_size_properties(ctx_scene, rt):
     ctx_scene.render(cam, precision=rt.F32, seed=0, sample_begin=12, sample_count=12, accumulate=True)
     r2 = ctx_scene.stats()["rays"]
     c = ctx_scene.readback(spp, want_sum=False)
-    assert r1 + r2 == rb and np.array_equal(c["rgb8"], b["rgb8"])
+    # the float4 buffer holds each shard's sum rounded to float: two shards re-associate the sum
+    dd = np.abs(c["rgb8"].astype(int) - b["rgb8"].astype(int))
+    assert r1 + r2 == rb and dd.max() <= 1 and (dd > 0).any(-1).mean() < 1e-3
 
 
 def test_errors_are_reported(ctx, rt):
