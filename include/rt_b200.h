@@ -42,8 +42,10 @@ enum { RT_LAMBERTIAN = 0, RT_METAL = 1, RT_DIELECTRIC = 2 };
  * as the reference, no FMA contraction.  F32 = fast mode (big spheres intersected in double). */
 enum { RT_F32 = 0, RT_F64 = 1 };
 
-/* bounce-loop variants (north_star item 3) */
-enum { RT_MEGAKERNEL = 0, RT_WAVEFRONT = 1 };
+/* bounce-loop variants (north_star item 3).  RT_MEGAKERNEL: one persistent kernel whose warps
+ * schedule node / leaf / shade sections among their lanes; RT_MEGA_LOCKSTEP: the first, lock-step
+ * form of it (kept for the ncu A/B in profiles/); RT_WAVEFRONT: queue-based stages. */
+enum { RT_MEGAKERNEL = 0, RT_WAVEFRONT = 1, RT_MEGA_LOCKSTEP = 2 };
 
 /* closest-hit back ends for rt_trace_closest / rt_bench_closest */
 enum { RT_TRACE_BVH = 0, RT_TRACE_BRUTE = 1 };
@@ -110,7 +112,7 @@ typedef struct {
     int32_t  accumulate;     /* 0: overwrite the accumulation buffer, 1: add to it (progressive) */
     uint64_t seed;           /* Philox key; stream = (pixel, sample, stage), see DESIGN.md */
     int32_t  slices;         /* sample slices per pixel rendered by different warps (0 = auto) */
-    int32_t  pad;
+    int32_t  sched;          /* tuning: th_s | th_l << 8 of the warp scheduler (0 = defaults) */
 } rt_render_opts;
 
 typedef struct {

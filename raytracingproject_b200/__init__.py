@@ -1,7 +1,7 @@
 """raytracingproject_b200 -- B200-native (sm_100a CUDA) path tracer behind the camera /
 hittable_list / sphere / material API of ShuvalovIvan/RayTracingProject.  Only the reference's
 CPU path-tracing hot path is in scope."""
-from ._lib import (ABI, F32, F64, MEGAKERNEL, WAVEFRONT, TRACE_BVH, TRACE_BRUTE, BVH_SAH_HOST, BVH_LBVH_GPU,
+from ._lib import (ABI, F32, F64, MEGAKERNEL, WAVEFRONT, MEGA_LOCKSTEP, TRACE_BVH, TRACE_BRUTE, BVH_SAH_HOST, BVH_LBVH_GPU,
                    LAMBERTIAN, METAL, DIELECTRIC, SPHERE, MATERIAL, RAY, HIT, LIB_PATH, SYMBOLS, lib)
 from .api import (Camera, Context, Dielectric, HittableList, Lambertian, Metal, RtError, Sphere,
                   build_bvh_host, camera_rtiow, scene_rtiow)

@@ -10,7 +10,7 @@ LIB_PATH = os.path.join(HERE, "librt_b200.so")
 
 ABI = 1
 F32, F64 = 0, 1
-MEGAKERNEL, WAVEFRONT = 0, 1
+MEGAKERNEL, WAVEFRONT, MEGA_LOCKSTEP = 0, 1, 2
 TRACE_BVH, TRACE_BRUTE = 0, 1
 BVH_SAH_HOST, BVH_LBVH_GPU = 0, 1
 LAMBERTIAN, METAL, DIELECTRIC = 0, 1, 2
@@ -39,7 +39,7 @@ class BvhOpts(C.Structure):
 class RenderOpts(C.Structure):
     _fields_ = [("abi", C.c_uint32), ("precision", C.c_int32), ("variant", C.c_int32),
                 ("sample_begin", C.c_int32), ("sample_count", C.c_int32), ("accumulate", C.c_int32),
-                ("seed", C.c_uint64), ("slices", C.c_int32), ("pad", C.c_int32)]
+                ("seed", C.c_uint64), ("slices", C.c_int32), ("sched", C.c_int32)]
 
 
 class Stats(C.Structure):

@@ -123,8 +123,8 @@ class Context:
         self._ck(self._lib.rt_upload_scene(self._h, L.ptr(spheres), len(spheres), L.ptr(materials), len(materials), C.byref(o)))
 
     def render(self, cam, precision=L.F32, seed=0, variant=L.MEGAKERNEL, sample_begin=0, sample_count=0,
-               accumulate=False, slices=0):
-        o = L.RenderOpts(L.ABI, precision, variant, sample_begin, sample_count, int(accumulate), seed, slices, 0)
+               accumulate=False, slices=0, sched=0):
+        o = L.RenderOpts(L.ABI, precision, variant, sample_begin, sample_count, int(accumulate), seed, slices, sched)
         self._ck(self._lib.rt_render(self._h, C.byref(cam), C.byref(o)))
         w, h = C.c_int(), C.c_int()
         self._lib.rt_image_size(C.byref(cam), C.byref(w), C.byref(h))

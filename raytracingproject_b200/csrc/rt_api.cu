@@ -365,6 +365,12 @@ extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_s
 // ------------------------------------------------------------------------------ render --
 namespace {
 
+// o.sched bits 16..19: block shape + 1 (0 = default for the precision)
+template <typename T> int sched_shape(int sched) {
+    const int v = (sched >> 16) & 0xf;
+    return v >= 1 && v <= RT_SCHED_SHAPES ? v - 1 : RT_SCHED_DEFAULT_SHAPE(T);
+}
+
 template <typename T>
 int render_impl(rt_ctx* ctx, const rt_camera& cam, const rt_render_opts& o, int sample_begin, int sample_count, int slices) {
     typedef typename Quad<T>::type Q;
@@ -386,7 +392,11 @@ int render_impl(rt_ctx* ctx, const rt_camera& cam, const rt_render_opts& o, int 
     CK(cudaMemsetAsync(ctx->job_counter.p, 0, sizeof(unsigned int), ctx->stream));
     CK(cudaMemsetAsync(ctx->ray_counter.p, 0, sizeof(unsigned long long), ctx->stream));
     CK(cudaEventRecord(ctx->ev[0], ctx->stream));
-    CK(launch_render_mega<T>(p, staged, smem, ctx->sm_count, ctx->stream));
+    // section thresholds: o.sched = th_s | th_l << 8 (0 = defaults, tuned on B200: see DESIGN.md)
+    p.th_s = (o.sched & 0xff) ? (o.sched & 0xff) : 28;
+    p.th_l = ((o.sched >> 8) & 0xff) ? ((o.sched >> 8) & 0xff) : 33;
+    if (o.variant == RT_MEGA_LOCKSTEP) CK(launch_render_mega<T>(p, staged, smem, ctx->sm_count, ctx->stream));
+    else CK(launch_render_sched<T>(p, sched_shape<T>(o.sched), staged, smem, ctx->sm_count, ctx->stream));
     CK(cudaEventRecord(ctx->ev[1], ctx->stream));
     return RT_OK;
 }
@@ -399,7 +409,7 @@ extern "C" int rt_render(rt_ctx* ctx, const rt_camera* cam, const rt_render_opts
     if (!ctx->has_scene) return fail(ctx, RT_E_STATE, "rt_render: no scene uploaded");
     if (cam->image_width < 1 || !(cam->aspect_ratio > 0)) return fail(ctx, RT_E_INVALID, "rt_render: bad image size");
     if (opts->precision != RT_F32 && opts->precision != RT_F64) return fail(ctx, RT_E_INVALID, "rt_render: bad precision");
-    if (opts->variant != RT_MEGAKERNEL) return fail(ctx, RT_E_INVALID, "rt_render: variant not built");
+    if (opts->variant != RT_MEGAKERNEL && opts->variant != RT_MEGA_LOCKSTEP) return fail(ctx, RT_E_INVALID, "rt_render: variant not built");
     CK(cudaSetDevice(ctx->device));
     const int W = cam->image_width, H = image_height_of(*cam);
     if ((long long)W * H >= (1ll << 32)) return fail(ctx, RT_E_INVALID, "rt_render: image too large for the 32-bit pixel key");
@@ -408,7 +418,8 @@ extern "C" int rt_render(rt_ctx* ctx, const rt_camera* cam, const rt_render_opts
 
     // slices: enough warp jobs to keep every resident warp busy and the tail short
     const long long tiles = (long long)((W + 7) / 8) * ((H + 3) / 4);
-    const int block = opts->precision == RT_F32 ? RT_MEGA_BLOCK(float) : RT_MEGA_BLOCK(double);
+    const int block = opts->variant == RT_MEGA_LOCKSTEP ? (opts->precision == RT_F32 ? RT_MEGA_BLOCK(float) : RT_MEGA_BLOCK(double))
+                                                        : sched_block(opts->precision == RT_F32 ? sched_shape<float>(opts->sched) : sched_shape<double>(opts->sched));
     const long long resident_warps = (long long)ctx->sm_count * 2 * (block / 32);
     // Parity mode keeps ONE slice unless asked otherwise: the per-pixel sum is then formed sample by
     // sample in the reference's order (src/camera.h:41-44).  Any other order can differ in the last

@@ -123,6 +123,133 @@ render_mega_kernel(const RenderParams<T> p) {
     if (lane == 0 && my_rays) atomicAdd(p.ray_counter, my_rays);
 }
 
+// ------------------------------------------------------- warp-scheduled megakernel --
+// Same work split as render_mega_kernel (warp = 8x4 pixel tile x one sample slice, lane = pixel,
+// samples walked in order), but the bounce loop is cut into three SECTIONS and each warp runs, per
+// iteration, the ONE section most of its lanes are waiting for:
+//   N  visit one inner BVH node                       (lanes with cur >= 0)
+//   L  test one leaf's spheres                        (lanes with a leaf in cur)
+//   S  shade the finished segment / sky / start the next sample, then set up the next traversal
+//      (lanes whose traversal ended: cur == RT_SENTINEL)
+// A lane that is not in the chosen section idles for that iteration only.  In the lock-step kernel
+// every lane waited for the slowest traversal of its warp and 7.4 of 32 lanes were active per
+// issued instruction (profiles/r1_mega_v0_ncu_summary.txt); here N runs while most lanes are still
+// traversing and S is postponed until `th_s` lanes wait for it (or nothing else is left), so the
+// expensive section (Philox, normalisations, the double refinement) runs with a well-filled warp.
+// The arithmetic per lane is unchanged, so parity mode stays bit-identical to the oracle.
+template <typename T, bool STAGED, int BLOCK>
+__global__ void __launch_bounds__(BLOCK, 2)
+render_sched_kernel(const RenderParams<T> p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const Staged<T> st = stage_scene<T>(p.scene, smem, STAGED);
+    const SceneView<T>& sv = p.scene;
+    const unsigned FULL = 0xffffffffu;
+
+    const int lane = threadIdx.x & 31;
+    const int W = p.cam.image_width, H = p.cam.image_height;
+    const int njobs = p.tiles_x * p.tiles_y * p.slices;
+    const int th_s = p.th_s, th_l = p.th_l;
+    unsigned long long my_rays = 0;
+    int stack[RT_STACK];
+
+    for (;;) {
+        int job = 0;
+        if (lane == 0) job = int(atomicAdd(p.job_counter, 1u));
+        job = __shfl_sync(FULL, job, 0);
+        if (job >= njobs) break;
+        const int slice = job % p.slices, tile = job / p.slices;
+        const int i = (tile % p.tiles_x) * 8 + (lane & 7);
+        const int j = (tile / p.tiles_x) * 4 + (lane >> 3);
+        const int s_begin = p.sample_begin + int((long long)p.sample_count * slice / p.slices);
+        const int s_end = p.sample_begin + int((long long)p.sample_count * (slice + 1) / p.slices);
+        int s = s_begin;
+        const bool in_image = i < W && j < H;
+        const uint32_t pixel = uint32_t(j) * uint32_t(W) + uint32_t(i);
+
+        double acc_r = 0.0, acc_g = 0.0, acc_b = 0.0;
+        Ray<T> ray; ray.o = mk<T>(0, 0, 0); ray.d = mk<T>(0, 0, 1); ray.tm = 0;
+        Vec<T> thr = mk<T>(1, 1, 1);
+        Trav<T> tv; tv.cur = RT_SENTINEL; tv.sp = 0; tv.tbest = 0; tv.best_id = -1; tv.best_slot = -1; tv.qa = 1; tv.inv = mk<T>(0, 0, 0);
+        int depth = 0;                       // bounces left for the current path; 0 = start the next sample
+        bool alive = in_image && s < s_end;
+
+        for (;;) {
+            const bool isN = alive && tv.cur >= 0;
+            const bool isS = alive && tv.cur == RT_SENTINEL;
+            const bool isL = alive && !isN && !isS;
+            const int nN = __popc(__ballot_sync(FULL, isN));
+            const int nL = __popc(__ballot_sync(FULL, isL));
+            const int nS = __popc(__ballot_sync(FULL, isS));
+            if ((nN | nL | nS) == 0) break;
+
+            if (nS >= th_s || (nN | nL) == 0) {
+                // ---------------------------------------------------------------- section S
+                if (isS) {
+                    bool need_ray = depth == 0;
+                    if (!need_ray) {
+                        // the segment traced last: src/camera_cpu.h:15-25
+                        if (tv.best_slot < 0) {                                   // miss: sky, path ends
+                            const Vec<T> c = thr * sky<T>(ray.d);
+                            acc_r += double(c.x); acc_g += double(c.y); acc_b += double(c.z);
+                            need_ray = true;
+                        } else {
+                            T t = tv.tbest;
+                            const Surface<T> sf = surface_at<T>(sv, st.sa, st.sb, st.sc, st.meta, ray, t, tv.best_slot);
+                            Philox rng; rng.init(p.seed);
+                            rng.set(pixel, uint32_t(s - 1), uint32_t(p.max_depth - depth + 1));   // scatter at the b-th hit: stage b
+                            Vec<T> att, dnew;
+                            if (!scatter<T>(sf.type, sf.albedo, sf.param, ray.d, sf.normal, sf.front_face, rng, att, dnew)) {
+                                need_ray = true;                                  // absorbed: contributes 0 (:20)
+                            } else {
+                                thr = thr * att;
+                                ray.o = sf.p; ray.d = dnew;                       // time is inherited (src/material.h:22)
+                                if (--depth == 0) need_ray = true;                // depth exhausted: contributes 0 (:12-13)
+                            }
+                        }
+                    }
+                    if (need_ray) {
+                        depth = 0;
+                        // camera::render's sample loop (src/camera.h:41-44); max_depth <= 0 -> every sample is black
+                        if (p.max_depth <= 0) s = s_end;
+                        if (s < s_end) {
+                            Philox rng; rng.init(p.seed);
+                            rng.set(pixel, uint32_t(s), 0u);
+                            ray = get_ray<T>(p.cam, i, j, rng);
+                            thr = mk<T>(1, 1, 1);
+                            depth = p.max_depth;
+                            ++s;
+                        } else {
+                            alive = false;
+                        }
+                    }
+                    if (alive) {
+                        ++my_rays;                                                // one ray_color entry with depth > 0
+                        trav_init<T>(sv, ray, T(0.001), T(INFINITY), tv);
+                    }
+                }
+            } else if (nL >= th_l || nL > nN) {
+                // ---------------------------------------------------------------- section L
+                if (isL) trav_leaf<T>(st.sa, st.sb, st.meta, ray, T(0.001), tv, stack);
+            } else {
+                // ---------------------------------------------------------------- section N
+                if (isN) trav_node<T>(st.nodes, ray, T(0.001), tv, stack);
+            }
+        }
+
+        if (in_image) {
+            typedef typename Quad<T>::type Q;
+            Q* dst = p.accum + (size_t(slice) * size_t(H) + size_t(j)) * size_t(W) + size_t(i);
+            Q v;
+            if (p.accumulate) { v = *dst; } else { v.x = 0; v.y = 0; v.z = 0; v.w = 0; }
+            v.x += decltype(v.x)(acc_r); v.y += decltype(v.x)(acc_g); v.z += decltype(v.x)(acc_b);
+            v.w += decltype(v.x)(s_end - s_begin);
+            *dst = v;
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) my_rays += __shfl_xor_sync(FULL, my_rays, o);
+    if (lane == 0 && my_rays) atomicAdd(p.ray_counter, my_rays);
+}
+
 // ------------------------------------------------------------------- parity-hook kernels --
 template <typename T> __device__ __forceinline__ Ray<T> load_ray(const double* rays, size_t i) {
     const double* q = rays + 7 * i;

@@ -16,6 +16,25 @@ template <> cudaError_t launch_render_mega<RT_REAL>(const RenderParams<RT_REAL>&
     return cudaGetLastError();
 }
 
+template <bool STAGED, int BLOCK>
+static cudaError_t launch_sched_shape(const RenderParams<RT_REAL>& p, size_t smem_bytes, int sm_count, cudaStream_t st) {
+    if (STAGED) {
+        cudaError_t e = cudaFuncSetAttribute(render_sched_kernel<RT_REAL, STAGED, BLOCK>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem_bytes));
+        if (e != cudaSuccess) return e;
+    }
+    render_sched_kernel<RT_REAL, STAGED, BLOCK><<<sm_count * 2, BLOCK, STAGED ? smem_bytes : 0, st>>>(p);   // persistent: resident CTAs only
+    return cudaGetLastError();
+}
+
+template <> cudaError_t launch_render_sched<RT_REAL>(const RenderParams<RT_REAL>& p, int shape, bool staged, size_t smem_bytes, int sm_count, cudaStream_t st) {
+    switch (sched_block(shape)) {
+    case 256: return staged ? launch_sched_shape<true, 256>(p, smem_bytes, sm_count, st) : launch_sched_shape<false, 256>(p, smem_bytes, sm_count, st);
+    case 320: return staged ? launch_sched_shape<true, 320>(p, smem_bytes, sm_count, st) : launch_sched_shape<false, 320>(p, smem_bytes, sm_count, st);
+    case 384: return staged ? launch_sched_shape<true, 384>(p, smem_bytes, sm_count, st) : launch_sched_shape<false, 384>(p, smem_bytes, sm_count, st);
+    default:  return staged ? launch_sched_shape<true, 512>(p, smem_bytes, sm_count, st) : launch_sched_shape<false, 512>(p, smem_bytes, sm_count, st);
+    }
+}
+
 template <> cudaError_t launch_trace_closest<RT_REAL>(const SceneView<RT_REAL>& sv, const double* rays, size_t n, double tmin, double tmax,
                                                       int brute, HitRec* out, cudaStream_t st) {
     if (n == 0) return cudaSuccess;

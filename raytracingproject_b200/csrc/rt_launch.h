@@ -11,6 +11,11 @@ namespace rt {
 // megakernel shape: float 512 threads x 2 CTAs/SM (<= 64 regs), double 256 x 2 (<= 128 regs)
 #define RT_MEGA_BLOCK(T) (sizeof(T) == 4 ? 512 : 256)
 #define RT_MEGA_MINBLOCKS(T) 2
+// warp-scheduled megakernel: fewer, fatter threads (more state is live across the sections)
+// block shapes compiled (2 CTAs per SM each): 256 (128 regs), 320 (96), 384 (80), 512 (64)
+#define RT_SCHED_SHAPES 4
+inline int sched_block(int shape) { const int b[RT_SCHED_SHAPES] = { 256, 320, 384, 512 }; return b[shape < 0 || shape >= RT_SCHED_SHAPES ? 0 : shape]; }
+#define RT_SCHED_DEFAULT_SHAPE(T) (sizeof(T) == 4 ? 2 : 0)
 
 template <typename T> struct RenderParams {
     CameraFrame<T> cam;
@@ -22,6 +27,7 @@ template <typename T> struct RenderParams {
     int sample_begin, sample_count, max_depth;
     int slices, tiles_x, tiles_y;
     int accumulate;
+    int th_s, th_l;                     // section thresholds of render_sched_kernel
 };
 
 struct HitRec;
@@ -33,6 +39,7 @@ template <typename T> inline size_t staged_bytes(int n_nodes, int n_slots) {
 }
 
 template <typename T> cudaError_t launch_render_mega(const RenderParams<T>& p, bool staged, size_t smem_bytes, int sm_count, cudaStream_t st);
+template <typename T> cudaError_t launch_render_sched(const RenderParams<T>& p, int shape, bool staged, size_t smem_bytes, int sm_count, cudaStream_t st);
 template <typename T> cudaError_t launch_trace_closest(const SceneView<T>& sv, const double* rays, size_t n, double tmin, double tmax,
                                                        int brute, HitRec* out, cudaStream_t st);
 template <typename T> cudaError_t launch_scatter(const MatRec* mats, const double* rays_in, const HitRec* hits, size_t n, uint64_t seed,

@@ -67,21 +67,23 @@ __device__ __forceinline__ bool leaf_sphere(const double4& a, const double4& b, 
     return sphere_hit_ref(r.o, r.d, a_len2, sphere_center<double>(a, b, r.tm), b.w, tmin, tbest, id, best_id, t);
 }
 
-// Closest hit in (tmin, tmax).  slot_out: tree slot, n_slots + k for big sphere k, or -1.
-// nodes/sa/sb/meta may point to shared memory (staged scene) or global memory.
-template <typename T>
-__device__ __forceinline__ void trace_closest(const SceneView<T>& sv, const float4* __restrict__ nodes,
-                                              const typename Quad<T>::type* __restrict__ sa,
-                                              const typename Quad<T>::type* __restrict__ sb,
-                                              const int* __restrict__ meta,
-                                              const Ray<T>& r, T tmin, T tmax, T& t_out, int& slot_out) {
-    T tbest = tmax;
-    int best_id = -1, best_slot = -1;
-    const T a_len2 = len2(r.d);
-    const T inv_a = T(1) / a_len2;
+// Traversal state of one ray.  The traversal is cut into three steps -- init (big spheres, root),
+// node visit, leaf visit -- so that the render kernel can schedule them per warp (rt_kernels.cuh);
+// trace_closest() below simply runs them to completion for one ray.
+//   cur >= 0: inner node to visit; cur < 0 and != RT_SENTINEL: leaf to test; RT_SENTINEL: finished.
+template <typename T> struct Trav {
+    Vec<T> inv;              // 1 / direction
+    T qa;                    // fast mode: 1 / |d|^2; parity mode: |d|^2 (what each sphere test wants)
+    T tbest;
+    int best_id, best_slot;  // list index (tie rule) and slot (tree slot, or n_slots + k for big sphere k)
+    int cur, sp;
+};
 
-    // big spheres first, in double in both modes (the r = 1000 ground sphere): a tight t_max for
-    // the tree and no float cancellation in |oc|^2 - r^2
+// big spheres first, in double in both modes (the r = 1000 ground sphere): a tight t_max for the
+// tree and no float cancellation in |oc|^2 - r^2
+template <typename T>
+__device__ __forceinline__ void trav_big(const SceneView<T>& sv, const Ray<T>& r, T tmin, T tmax, T& tbest, int& best_id, int& best_slot) {
+    tbest = tmax; best_id = -1; best_slot = -1;
     if (sv.n_big > 0) {
         const Vec<double> od = mk<double>(r.o.x, r.o.y, r.o.z), dd = mk<double>(r.d.x, r.d.y, r.d.z);
         const double ad = len2(dd);
@@ -96,46 +98,80 @@ __device__ __forceinline__ void trace_closest(const SceneView<T>& sv, const floa
         }
         tbest = T(tb);
     }
+}
 
-    const Vec<T> inv = mk<T>(T(1) / r.d.x, T(1) / r.d.y, T(1) / r.d.z);
-    int stack[RT_STACK];
-    int sp = 0;
-    int cur = sv.root_ref;
-    while (cur != RT_SENTINEL) {
-        if (cur >= 0) {
-            const float4 q0 = nodes[4 * cur + 0], q1 = nodes[4 * cur + 1], q2 = nodes[4 * cur + 2], q3 = nodes[4 * cur + 3];
-            T tl, tr;
-            const bool hl = slab(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, r.o, inv, tmin, tbest, tl);
-            const bool hr = slab(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, r.o, inv, tmin, tbest, tr);
-            const int cl = __float_as_int(q3.x), cr = __float_as_int(q3.y);
-            if (hl && hr) {
-                const bool left_first = tl <= tr;
-                cur = left_first ? cl : cr;
-                if (sp < RT_STACK) stack[sp++] = left_first ? cr : cl;
-            } else if (hl) {
-                cur = cl;
-            } else if (hr) {
-                cur = cr;
-            } else {
-                cur = sp > 0 ? stack[--sp] : RT_SENTINEL;
-            }
-        } else {
-            const int leaf = ~cur;
-            const int first = leaf >> 3, count = (leaf & 7) + 1;
-            for (int k = 0; k < count; ++k) {
-                const int slot = first + k;
-                const typename Quad<T>::type a = sa[slot], b = sb[slot];
-                const int id = RT_META_ID(meta[slot]);
-                T t;
-                if (leaf_sphere(a, b, r, a_len2, inv_a, tmin, tbest, id, best_id, t)) {
-                    tbest = t; best_id = id; best_slot = slot;
-                }
-            }
-            cur = sp > 0 ? stack[--sp] : RT_SENTINEL;
+// per-ray constants of the tree walk; tbest / best_id / best_slot are already set (trav_big)
+template <typename T>
+__device__ __forceinline__ void trav_setup(const SceneView<T>& sv, const Ray<T>& r, Trav<T>& tv) {
+    const T a_len2 = len2(r.d);
+    tv.qa = sizeof(T) == 4 ? T(1) / a_len2 : a_len2;
+    tv.inv = mk<T>(T(1) / r.d.x, T(1) / r.d.y, T(1) / r.d.z);
+    tv.cur = sv.root_ref; tv.sp = 0;
+}
+
+template <typename T>
+__device__ __forceinline__ void trav_init(const SceneView<T>& sv, const Ray<T>& r, T tmin, T tmax, Trav<T>& tv) {
+    trav_big<T>(sv, r, tmin, tmax, tv.tbest, tv.best_id, tv.best_slot);
+    trav_setup<T>(sv, r, tv);
+}
+
+// one inner node: both child boxes, near child next, far child pushed (src/bvh.h:16-24 contract)
+template <typename T>
+__device__ __forceinline__ void trav_node(const float4* __restrict__ nodes, const Ray<T>& r, T tmin, Trav<T>& tv, int* stack) {
+    const int cur = tv.cur;
+    const float4 q0 = nodes[4 * cur + 0], q1 = nodes[4 * cur + 1], q2 = nodes[4 * cur + 2], q3 = nodes[4 * cur + 3];
+    T tl, tr;
+    const bool hl = slab(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, r.o, tv.inv, tmin, tv.tbest, tl);
+    const bool hr = slab(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, r.o, tv.inv, tmin, tv.tbest, tr);
+    const int cl = __float_as_int(q3.x), cr = __float_as_int(q3.y);
+    if (hl && hr) {
+        const bool left_first = tl <= tr;
+        tv.cur = left_first ? cl : cr;
+        if (tv.sp < RT_STACK) stack[tv.sp++] = left_first ? cr : cl;
+    } else if (hl) {
+        tv.cur = cl;
+    } else if (hr) {
+        tv.cur = cr;
+    } else {
+        tv.cur = tv.sp > 0 ? stack[--tv.sp] : RT_SENTINEL;
+    }
+}
+
+// one leaf: its 1..8 sphere slots
+template <typename T>
+__device__ __forceinline__ void trav_leaf(const typename Quad<T>::type* __restrict__ sa, const typename Quad<T>::type* __restrict__ sb,
+                                          const int* __restrict__ meta, const Ray<T>& r, T tmin, Trav<T>& tv, const int* stack) {
+    const int leaf = ~tv.cur;
+    const int first = leaf >> 3, count = (leaf & 7) + 1;
+    for (int k = 0; k < count; ++k) {
+        const int slot = first + k;
+        const typename Quad<T>::type a = sa[slot], b = sb[slot];
+        const int id = RT_META_ID(meta[slot]);
+        T t;
+        if (leaf_sphere(a, b, r, tv.qa, tv.qa, tmin, tv.tbest, id, tv.best_id, t)) {
+            tv.tbest = t; tv.best_id = id; tv.best_slot = slot;
         }
     }
-    t_out = tbest;
-    slot_out = best_slot;
+    tv.cur = tv.sp > 0 ? stack[--tv.sp] : RT_SENTINEL;
+}
+
+// Closest hit in (tmin, tmax).  slot_out: tree slot, n_slots + k for big sphere k, or -1.
+// nodes/sa/sb/meta may point to shared memory (staged scene) or global memory.
+template <typename T>
+__device__ __forceinline__ void trace_closest(const SceneView<T>& sv, const float4* __restrict__ nodes,
+                                              const typename Quad<T>::type* __restrict__ sa,
+                                              const typename Quad<T>::type* __restrict__ sb,
+                                              const int* __restrict__ meta,
+                                              const Ray<T>& r, T tmin, T tmax, T& t_out, int& slot_out) {
+    Trav<T> tv;
+    int stack[RT_STACK];
+    trav_init<T>(sv, r, tmin, tmax, tv);
+    while (tv.cur != RT_SENTINEL) {
+        if (tv.cur >= 0) trav_node<T>(nodes, r, tmin, tv, stack);
+        else trav_leaf<T>(sa, sb, meta, r, tmin, tv, stack);
+    }
+    t_out = tv.tbest;
+    slot_out = tv.best_slot;
 }
 
 // Linear closest hit over every sphere in list order (device-side ground truth,
