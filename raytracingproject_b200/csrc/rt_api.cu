@@ -371,6 +371,20 @@ template <typename T> int sched_shape(int sched) {
     return v >= 1 && v <= RT_SCHED_SHAPES ? v - 1 : RT_SCHED_DEFAULT_SHAPE(T);
 }
 
+// wavefront: o.sched bits 16..19 = pool shape + 1; falls back to smaller pools when the staged scene
+// plus the pools do not fit the SM's shared memory, and to an unstaged scene after that
+template <typename T> int pool_shape_for(const rt_ctx* c, int sched, bool* staged) {
+    const int v = (sched >> 16) & 0xf;
+    int shape = v >= 1 && v <= RT_POOL_SHAPES ? v - 1 : RT_POOL_DEFAULT_SHAPE(T);
+    const size_t scene = staged_bytes_aligned<T>(c->n_nodes, c->n_slots);
+    const size_t budget = c->smem_optin;
+    auto need = [&](int sh) { int P, B; pool_shape(sh, &P, &B); return size_t(B / 32) * pool_warp_bytes<T>(P); };
+    *staged = c->n_slots > 0 && scene + need(shape) + 8 * 1024 <= budget;
+    if (!*staged && c->n_slots > 0 && scene + need(0) + 8 * 1024 <= budget) { shape = 0; *staged = true; }
+    if (!*staged && need(shape) > budget) shape = 0;
+    return shape;
+}
+
 template <typename T>
 int render_impl(rt_ctx* ctx, const rt_camera& cam, const rt_render_opts& o, int sample_begin, int sample_count, int slices) {
     typedef typename Quad<T>::type Q;
@@ -387,15 +401,22 @@ int render_impl(rt_ctx* ctx, const rt_camera& cam, const rt_render_opts& o, int 
     p.tiles_x = (ctx->W + 7) / 8; p.tiles_y = (ctx->H + 3) / 4;
     p.accumulate = o.accumulate;
     size_t smem = 0;
-    const bool staged = can_stage<T>(ctx, &smem);
+    bool staged = can_stage<T>(ctx, &smem);
+    int pshape = 0;
+    if (o.variant == RT_WAVEFRONT) {
+        pshape = pool_shape_for<T>(ctx, o.sched, &staged);
+        int P, B; pool_shape(pshape, &P, &B);
+        p.tiles_x = (ctx->W + 15) / 16; p.tiles_y = (ctx->H + P / 16 - 1) / (P / 16);
+    }
     ctx->stats.scene_in_smem = staged;
     CK(cudaMemsetAsync(ctx->job_counter.p, 0, sizeof(unsigned int), ctx->stream));
     CK(cudaMemsetAsync(ctx->ray_counter.p, 0, sizeof(unsigned long long), ctx->stream));
     CK(cudaEventRecord(ctx->ev[0], ctx->stream));
     // section thresholds: o.sched = th_s | th_l << 8 (0 = defaults, tuned on B200: see DESIGN.md)
-    p.th_s = (o.sched & 0xff) ? (o.sched & 0xff) : 28;
+    p.th_s = (o.sched & 0xff) ? (o.sched & 0xff) : (o.variant == RT_WAVEFRONT ? 8 : 28);
     p.th_l = ((o.sched >> 8) & 0xff) ? ((o.sched >> 8) & 0xff) : 33;
-    if (o.variant == RT_MEGA_LOCKSTEP) CK(launch_render_mega<T>(p, staged, smem, ctx->sm_count, ctx->stream));
+    if (o.variant == RT_WAVEFRONT) CK(launch_render_pool<T>(p, pshape, staged, ctx->sm_count, ctx->stream));
+    else if (o.variant == RT_MEGA_LOCKSTEP) CK(launch_render_mega<T>(p, staged, smem, ctx->sm_count, ctx->stream));
     else CK(launch_render_sched<T>(p, sched_shape<T>(o.sched), staged, smem, ctx->sm_count, ctx->stream));
     CK(cudaEventRecord(ctx->ev[1], ctx->stream));
     return RT_OK;
@@ -409,7 +430,7 @@ extern "C" int rt_render(rt_ctx* ctx, const rt_camera* cam, const rt_render_opts
     if (!ctx->has_scene) return fail(ctx, RT_E_STATE, "rt_render: no scene uploaded");
     if (cam->image_width < 1 || !(cam->aspect_ratio > 0)) return fail(ctx, RT_E_INVALID, "rt_render: bad image size");
     if (opts->precision != RT_F32 && opts->precision != RT_F64) return fail(ctx, RT_E_INVALID, "rt_render: bad precision");
-    if (opts->variant != RT_MEGAKERNEL && opts->variant != RT_MEGA_LOCKSTEP) return fail(ctx, RT_E_INVALID, "rt_render: variant not built");
+    if (opts->variant != RT_MEGAKERNEL && opts->variant != RT_MEGA_LOCKSTEP && opts->variant != RT_WAVEFRONT) return fail(ctx, RT_E_INVALID, "rt_render: variant not built");
     CK(cudaSetDevice(ctx->device));
     const int W = cam->image_width, H = image_height_of(*cam);
     if ((long long)W * H >= (1ll << 32)) return fail(ctx, RT_E_INVALID, "rt_render: image too large for the 32-bit pixel key");
@@ -417,10 +438,18 @@ extern "C" int rt_render(rt_ctx* ctx, const rt_camera* cam, const rt_render_opts
     const int sample_count = opts->sample_count > 0 ? opts->sample_count : std::max(0, cam->samples_per_pixel - sample_begin);
 
     // slices: enough warp jobs to keep every resident warp busy and the tail short
-    const long long tiles = (long long)((W + 7) / 8) * ((H + 3) / 4);
-    const int block = opts->variant == RT_MEGA_LOCKSTEP ? (opts->precision == RT_F32 ? RT_MEGA_BLOCK(float) : RT_MEGA_BLOCK(double))
+    long long tiles = (long long)((W + 7) / 8) * ((H + 3) / 4);
+    int ctas_per_sm = 2;
+    int block = opts->variant == RT_MEGA_LOCKSTEP ? (opts->precision == RT_F32 ? RT_MEGA_BLOCK(float) : RT_MEGA_BLOCK(double))
                                                         : sched_block(opts->precision == RT_F32 ? sched_shape<float>(opts->sched) : sched_shape<double>(opts->sched));
-    const long long resident_warps = (long long)ctx->sm_count * 2 * (block / 32);
+    if (opts->variant == RT_WAVEFRONT) {
+        bool staged; int P;
+        const int sh = opts->precision == RT_F32 ? pool_shape_for<float>(ctx, opts->sched, &staged) : pool_shape_for<double>(ctx, opts->sched, &staged);
+        pool_shape(sh, &P, &block);
+        tiles = (long long)((W + 15) / 16) * ((H + P / 16 - 1) / (P / 16));
+        ctas_per_sm = 1;
+    }
+    const long long resident_warps = (long long)ctx->sm_count * ctas_per_sm * (block / 32);
     // Parity mode keeps ONE slice unless asked otherwise: the per-pixel sum is then formed sample by
     // sample in the reference's order (src/camera.h:41-44).  Any other order can differ in the last
     // bit, and this scene has sums that sit exactly on a byte boundary of write_color (albedo 0.5 x

@@ -88,16 +88,48 @@ template <typename T> __device__ __forceinline__ T u01(uint32_t m) { return T(m)
 // path take the same accept/reject decision as the reference.
 __device__ __forceinline__ int32_t sym24(uint32_t m) { return int32_t(m) - (1 << 23); }
 
-// src/vec3.h:129-135 with the g++ draw order z, y, x
+// src/vec3.h:129-135 with the g++ draw order z, y, x.  Generic form: continues the
+// stream wherever it stands (used by the C2 ray generator).
+template <typename T> __device__ __forceinline__ bool ball_accept(uint32_t mz, uint32_t my, uint32_t mx, Vec<T>& out) {
+    const int32_t az = sym24(mz), ay = sym24(my), ax = sym24(mx);
+    const int64_t l2 = int64_t(ax) * ax + int64_t(ay) * ay + int64_t(az) * az;
+    if (l2 >= (int64_t(1) << 46)) return false;
+    out = mk<T>(T(ax) * T(1.0 / 8388608.0), T(ay) * T(1.0 / 8388608.0), T(az) * T(1.0 / 8388608.0));
+    return true;
+}
 template <typename T> __device__ __forceinline__ Vec<T> random_in_unit_sphere(Philox& rng) {
     for (;;) {
-        const int32_t az = sym24(rng.next24());
-        const int32_t ay = sym24(rng.next24());
-        const int32_t ax = sym24(rng.next24());
-        const int64_t l2 = int64_t(ax) * ax + int64_t(ay) * ay + int64_t(az) * az;
-        if (l2 < (int64_t(1) << 46))
-            return mk<T>(T(ax) * T(1.0 / 8388608.0), T(ay) * T(1.0 / 8388608.0), T(az) * T(1.0 / 8388608.0));
+        const uint32_t mz = rng.next24(), my = rng.next24(), mx = rng.next24();
+        Vec<T> v;
+        if (ball_accept<T>(mz, my, mx, v)) return v;
     }
+}
+
+// The same sampler for a stream that stands at draw 0 of its stage (every scatter does): identical
+// draws, but the Philox rounds are emitted ONCE, in a loop over 4-word blocks, instead of once per
+// draw site -- the triplets (z, y, x) of iteration i are draws 3i..3i+2, so block b completes one
+// triplet (b % 3 == 0, 1) or two (b % 3 == 2).  Smaller code (the kernels are I-cache bound) and
+// the lanes of a warp stay converged on the expensive part.
+template <typename T> __device__ __forceinline__ Vec<T> random_in_unit_sphere_from0(Philox& rng) {
+    uint32_t c0 = 0, c1 = 0;
+    int nc = 0;
+    Vec<T> v = mk<T>(T(0), T(0), T(0));
+    for (uint32_t b = 0;; ++b) {
+        rng.generate(b);
+        const uint32_t w0 = rng.w0 >> 8, w1 = rng.w1 >> 8, w2 = rng.w2 >> 8, w3 = rng.w3 >> 8;
+        if (nc == 0) {
+            if (ball_accept<T>(w0, w1, w2, v)) break;
+            c0 = w3; nc = 1;
+        } else if (nc == 1) {
+            if (ball_accept<T>(c0, w0, w1, v)) break;
+            c0 = w2; c1 = w3; nc = 2;
+        } else {
+            if (ball_accept<T>(c0, c1, w0, v)) break;
+            if (ball_accept<T>(w1, w2, w3, v)) break;
+            nc = 0;
+        }
+    }
+    return v;
 }
 
 // ------------------------------------------------------------------------------ camera --
@@ -115,24 +147,31 @@ template <typename T> struct Ray { Vec<T> o, d; T tm; };
 // second -> x (src/vec3.h:123 under g++); time (:97).  Stream stage 0.
 template <typename T> __device__ __forceinline__ Ray<T> get_ray(const CameraFrame<T>& c, int i, int j, Philox& rng) {
     const Vec<T> pixel_center = (c.pixel00_loc + T(i) * c.pixel_delta_u) + T(j) * c.pixel_delta_v;
-    const T px = T(-0.5) + u01<T>(rng.next24());
-    const T py = T(-0.5) + u01<T>(rng.next24());
+    rng.generate(0u);                                   // draws 0..3: px, py, first disk pair (or time)
+    const T px = T(-0.5) + u01<T>(rng.w0 >> 8);
+    const T py = T(-0.5) + u01<T>(rng.w1 >> 8);
     const Vec<T> pixel_sample = pixel_center + (px * c.pixel_delta_u + py * c.pixel_delta_v);
     Ray<T> r;
+    uint32_t mt;                                        // the draw that follows the accepted disk pair
     if (!c.defocus) {
         r.o = c.center;
+        mt = rng.w2 >> 8;
     } else {
-        int32_t ax, ay;
-        for (;;) {
-            ay = sym24(rng.next24());
-            ax = sym24(rng.next24());
-            if (int64_t(ax) * ax + int64_t(ay) * ay < (int64_t(1) << 46)) break;
+        int32_t ay = sym24(rng.w2 >> 8), ax = sym24(rng.w3 >> 8);
+        bool ok = int64_t(ax) * ax + int64_t(ay) * ay < (int64_t(1) << 46);
+        for (uint32_t b = 1u;; ++b) {                   // pairs never straddle a block: draws 4b, 4b+1 | 4b+2, 4b+3
+            rng.generate(b);
+            if (ok) { mt = rng.w0 >> 8; break; }
+            ay = sym24(rng.w0 >> 8); ax = sym24(rng.w1 >> 8);
+            if (int64_t(ax) * ax + int64_t(ay) * ay < (int64_t(1) << 46)) { mt = rng.w2 >> 8; break; }
+            ay = sym24(rng.w2 >> 8); ax = sym24(rng.w3 >> 8);
+            ok = int64_t(ax) * ax + int64_t(ay) * ay < (int64_t(1) << 46);
         }
         const T dx = T(ax) * T(1.0 / 8388608.0), dy = T(ay) * T(1.0 / 8388608.0);
         r.o = (c.center + dx * c.defocus_disk_u) + dy * c.defocus_disk_v;
     }
     r.d = pixel_sample - r.o;
-    r.tm = u01<T>(rng.next24());
+    r.tm = u01<T>(mt);
     return r;
 }
 
@@ -179,6 +218,41 @@ __device__ __forceinline__ bool sphere_hit_ref(const Vec<double>& o, const Vec<d
     return true;
 }
 
+// Fast-mode double helpers: reciprocal and square root good to ~1e-15 relative from a float seed and
+// two Newton steps (8 and 10 instructions instead of the ~70 / ~85 of the IEEE-rounded routines).
+// Only the fast mode uses them; parity mode keeps `/` and sqrt().
+__device__ __forceinline__ double rcp_newton(double x) {
+    double r = double(__fdividef(1.0f, float(x)));
+    r = fma(r, fma(-x, r, 1.0), r);
+    return fma(r, fma(-x, r, 1.0), r);
+}
+__device__ __forceinline__ double sqrt_newton(double x) {                 // x >= 0
+    const double y0 = double(rsqrtf(fmaxf(float(x), 1e-36f)));
+    const double y = y0 * fma(-0.5 * x * y0, y0, 1.5);                    // 1/sqrt(x) to ~1e-14
+    const double s = x * y;
+    return fma(0.5 * y, fma(-s, s, x), s);
+}
+
+// Fast-mode test of a BIG sphere (kept out of the tree, e.g. the r = 1000 ground): the quadratic of
+// sphere_hit_ref in double -- |oc|^2 - r^2 must not cancel in float and the self-intersection root
+// has to stay below tmin = 0.001 -- with inv_a = 1/|d|^2 hoisted per ray.
+__device__ __forceinline__ bool sphere_hit_big(const Vec<double>& o, const Vec<double>& d, double a, double inv_a, const Vec<double>& center,
+                                               double rr, double tmin, double tbest, int id, int best_id, double& t_out) {
+    const Vec<double> oc = o - center;
+    const double half_b = dot(oc, d);
+    const double c = len2(oc) - rr;
+    const double discriminant = half_b * half_b - a * c;
+    if (discriminant < 0) return false;
+    const double sqrtd = sqrt_newton(discriminant);
+    double root = (-half_b - sqrtd) * inv_a;
+    if (!root_ok(root, tmin, tbest, id, best_id)) {
+        root = (-half_b + sqrtd) * inv_a;
+        if (!root_ok(root, tmin, tbest, id, best_id)) return false;
+    }
+    t_out = root;
+    return true;
+}
+
 // Fast-mode sphere test (float): the same quadratic, solved around the closest-approach point
 // so that r^2 - |l|^2 does not cancel catastrophically (l = oc - (oc.d/a) d).  inv_a = 1/a.
 __device__ __forceinline__ bool sphere_hit_f32(const Vec<float>& o, const Vec<float>& d, float inv_a, const Vec<float>& center,
@@ -211,14 +285,17 @@ template <typename T> __device__ __forceinline__ T reflectance(T cosine, T ref_i
 
 template <typename T> __device__ __forceinline__ bool scatter(int type, Vec<T> albedo, T param, const Vec<T>& d_in, const Vec<T>& n,
                                                               bool front_face, Philox& rng, Vec<T>& attenuation, Vec<T>& d_out) {
-    if (type == 0) {                                   // lambertian, no near_zero guard (:21)
-        d_out = n + unit_vector(random_in_unit_sphere<T>(rng));
+    if (type < 2) {
+        // both opaque materials draw one point in the unit ball first (3k draws, metal even when
+        // fuzz == 0, :38); the sampler is instantiated once for the two of them
+        const Vec<T> ball = random_in_unit_sphere_from0<T>(rng);
         attenuation = albedo;
-        return true;
-    } else if (type == 1) {                            // metal: 3k draws even when fuzz == 0 (:38)
-        const Vec<T> reflected = reflect(unit_vector(d_in), n);
-        d_out = reflected + param * random_in_unit_sphere<T>(rng);
-        attenuation = albedo;
+        if (type == 0) {                               // lambertian, no near_zero guard (:21)
+            d_out = n + unit_vector(ball);
+            return true;
+        }
+        const Vec<T> reflected = reflect(unit_vector(d_in), n);   // metal (:37-40)
+        d_out = reflected + param * ball;
         return dot(d_out, n) > T(0);
     } else {                                           // dielectric
         attenuation = mk<T>(T(1), T(1), T(1));
@@ -228,7 +305,9 @@ template <typename T> __device__ __forceinline__ bool scatter(int type, Vec<T> a
         const T sin_theta = rt_sqrt(T(1) - cos_theta * cos_theta);
         const bool cannot_refract = refraction_ratio * sin_theta > T(1);
         // `||` short-circuit (:64): the uniform is drawn only when refraction is possible
-        if (cannot_refract || reflectance(cos_theta, refraction_ratio) > u01<T>(rng.next24()))
+        bool do_reflect = cannot_refract;
+        if (!do_reflect) { rng.generate(0u); do_reflect = reflectance(cos_theta, refraction_ratio) > u01<T>(rng.w0 >> 8); }
+        if (do_reflect)
             d_out = reflect(unit_direction, n);
         else
             d_out = refract(unit_direction, n, refraction_ratio);

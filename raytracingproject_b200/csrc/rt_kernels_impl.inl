@@ -1,5 +1,6 @@
 // rt_kernels_impl.inl -- launchers, included by rt_kernels_f32.cu / rt_kernels_f64.cu with RT_REAL set.
 #include "rt_kernels.cuh"
+#include "rt_wavefront.cuh"
 
 namespace rt {
 
@@ -33,6 +34,28 @@ template <> cudaError_t launch_render_sched<RT_REAL>(const RenderParams<RT_REAL>
     case 384: return staged ? launch_sched_shape<true, 384>(p, smem_bytes, sm_count, st) : launch_sched_shape<false, 384>(p, smem_bytes, sm_count, st);
     default:  return staged ? launch_sched_shape<true, 512>(p, smem_bytes, sm_count, st) : launch_sched_shape<false, 512>(p, smem_bytes, sm_count, st);
     }
+}
+
+template <bool STAGED, int P, int BLOCK>
+static cudaError_t launch_pool_shape(const RenderParams<RT_REAL>& p, int sm_count, cudaStream_t st) {
+    static_assert(Pool<RT_REAL, P>::bytes == int(P * (11 * sizeof(RT_REAL) + 3 * 4 + 4)), "pool_warp_bytes mirrors Pool::bytes");
+    const size_t smem = (STAGED ? staged_bytes_aligned<RT_REAL>(p.scene.n_nodes, p.scene.n_slots) : 0) + size_t(BLOCK / 32) * Pool<RT_REAL, P>::bytes;
+    cudaError_t e = cudaFuncSetAttribute(render_pool_kernel<RT_REAL, STAGED, P, BLOCK>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+    if (e != cudaSuccess) return e;
+    render_pool_kernel<RT_REAL, STAGED, P, BLOCK><<<sm_count, BLOCK, smem, st>>>(p);      // persistent: one CTA per SM
+    return cudaGetLastError();
+}
+
+template <> cudaError_t launch_render_pool<RT_REAL>(const RenderParams<RT_REAL>& p, int shape, bool staged, int sm_count, cudaStream_t st) {
+#define RT_POOL_CASE(S, P, B) case S: return staged ? launch_pool_shape<true, P, B>(p, sm_count, st) : launch_pool_shape<false, P, B>(p, sm_count, st)
+    switch (shape) {
+    RT_POOL_CASE(1, 128, 512);
+    RT_POOL_CASE(2, 128, 640);
+    RT_POOL_CASE(3, 64, 768);
+    RT_POOL_CASE(4, 128, 704);
+    default: RT_POOL_CASE(0, 128, 256);
+    }
+#undef RT_POOL_CASE
 }
 
 template <> cudaError_t launch_trace_closest<RT_REAL>(const SceneView<RT_REAL>& sv, const double* rays, size_t n, double tmin, double tmax,

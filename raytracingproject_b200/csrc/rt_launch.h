@@ -38,6 +38,22 @@ template <typename T> inline size_t staged_bytes(int n_nodes, int n_slots) {
     return size_t(n_nodes) * 64 + size_t(n_slots) * (3 * sizeof(typename Quad<T>::type) + sizeof(int));
 }
 
+// the same, rounded up so that what follows the staged scene in shared memory stays 16-byte aligned
+template <typename T> __host__ __device__ inline size_t staged_bytes_aligned(int n_nodes, int n_slots) {
+    return (size_t(n_nodes) * 64 + size_t(n_slots) * (3 * sizeof(typename Quad<T>::type) + sizeof(int)) + 15) & ~size_t(15);
+}
+
+// SM-resident wavefront (rt_wavefront.cuh): pool of P paths per warp, one CTA of BLOCK threads per SM
+#define RT_POOL_SHAPES 5
+inline void pool_shape(int shape, int* paths, int* block) {
+    const int P[RT_POOL_SHAPES] = { 128, 128, 128, 64, 128 }, B[RT_POOL_SHAPES] = { 256, 512, 640, 768, 704 };
+    if (shape < 0 || shape >= RT_POOL_SHAPES) shape = 0;
+    *paths = P[shape]; *block = B[shape];
+}
+template <typename T> inline size_t pool_warp_bytes(int paths) { return size_t(paths) * (11 * sizeof(T) + 3 * 4 + 4); }
+#define RT_POOL_DEFAULT_SHAPE(T) (sizeof(T) == 4 ? 2 : 0)
+template <typename T> cudaError_t launch_render_pool(const RenderParams<T>& p, int shape, bool staged, int sm_count, cudaStream_t st);
+
 template <typename T> cudaError_t launch_render_mega(const RenderParams<T>& p, bool staged, size_t smem_bytes, int sm_count, cudaStream_t st);
 template <typename T> cudaError_t launch_render_sched(const RenderParams<T>& p, int shape, bool staged, size_t smem_bytes, int sm_count, cudaStream_t st);
 template <typename T> cudaError_t launch_trace_closest(const SceneView<T>& sv, const double* rays, size_t n, double tmin, double tmax,

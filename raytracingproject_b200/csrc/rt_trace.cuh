@@ -32,7 +32,8 @@ template <typename T> struct SceneView {
 };
 
 // Slab test, src/aabb.h:35-53 with 1/d hoisted.  Returns entry distance in tnear.
-// float rays: (plane - o) * inv keeps the error relative (2 ulp), covered by the 1+2^-21 factor.
+// float rays: (plane - o) * inv keeps the error relative (2 ulp + 1 ulp of the approximate
+// reciprocal in inv), covered by the 1 + 2^-20 factor.
 __device__ __forceinline__ bool slab(float lx, float ly, float lz, float hx, float hy, float hz,
                                      const Vec<float>& o, const Vec<float>& inv, float tmin, float tmax, float& tnear) {
     const float t0x = (lx - o.x) * inv.x, t1x = (hx - o.x) * inv.x;
@@ -41,7 +42,7 @@ __device__ __forceinline__ bool slab(float lx, float ly, float lz, float hx, flo
     const float tn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), tmin));
     const float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), tmax));
     tnear = tn;
-    return tn <= tf * 1.0000005f;
+    return tn <= tf * 1.000001f;
 }
 // double rays against the float boxes (exactly representable in double): the boxes' outward
 // padding (>= 2^-20 relative) dwarfs double rounding.
@@ -87,14 +88,16 @@ __device__ __forceinline__ void trav_big(const SceneView<T>& sv, const Ray<T>& r
     if (sv.n_big > 0) {
         const Vec<double> od = mk<double>(r.o.x, r.o.y, r.o.z), dd = mk<double>(r.d.x, r.d.y, r.d.z);
         const double ad = len2(dd);
+        const double inv_ad = sizeof(T) == 4 ? rcp_newton(ad) : 0.0;
         double tb = double(tbest);
         for (int k = 0; k < sv.n_big; ++k) {
             const double4 a = sv.big_a[k], b = sv.big_b[k];
             const int id = RT_META_ID(sv.big_meta[k]);
             double t;
-            if (sphere_hit_ref(od, dd, ad, sphere_center<double>(a, b, double(r.tm)), b.w, double(tmin), tb, id, best_id, t)) {
-                tb = t; best_id = id; best_slot = sv.n_slots + k;
-            }
+            const bool hit = sizeof(T) == 4
+                ? sphere_hit_big(od, dd, ad, inv_ad, sphere_center<double>(a, b, double(r.tm)), b.w, double(tmin), tb, id, best_id, t)
+                : sphere_hit_ref(od, dd, ad, sphere_center<double>(a, b, double(r.tm)), b.w, double(tmin), tb, id, best_id, t);
+            if (hit) { tb = t; best_id = id; best_slot = sv.n_slots + k; }
         }
         tbest = T(tb);
     }
@@ -179,24 +182,11 @@ __device__ __forceinline__ void trace_closest(const SceneView<T>& sv, const floa
 // applied explicitly.
 template <typename T>
 __device__ __forceinline__ void brute_closest(const SceneView<T>& sv, const Ray<T>& r, T tmin, T tmax, T& t_out, int& slot_out) {
-    T tbest = tmax;
-    int best_id = -1, best_slot = -1;
+    T tbest;
+    int best_id, best_slot;
+    trav_big<T>(sv, r, tmin, tmax, tbest, best_id, best_slot);
     const T a_len2 = len2(r.d);
     const T inv_a = T(1) / a_len2;
-    if (sv.n_big > 0) {
-        const Vec<double> od = mk<double>(r.o.x, r.o.y, r.o.z), dd = mk<double>(r.d.x, r.d.y, r.d.z);
-        const double ad = len2(dd);
-        double tb = double(tbest);
-        for (int k = 0; k < sv.n_big; ++k) {
-            const double4 a = sv.big_a[k], b = sv.big_b[k];
-            const int id = RT_META_ID(sv.big_meta[k]);
-            double t;
-            if (sphere_hit_ref(od, dd, ad, sphere_center<double>(a, b, double(r.tm)), b.w, double(tmin), tb, id, best_id, t)) {
-                tb = t; best_id = id; best_slot = sv.n_slots + k;
-            }
-        }
-        tbest = T(tb);
-    }
     for (int slot = 0; slot < sv.n_slots; ++slot) {
         const typename Quad<T>::type a = sv.sa[slot], b = sv.sb[slot];
         const int id = RT_META_ID(sv.meta[slot]);
@@ -229,8 +219,8 @@ __device__ __forceinline__ void refine_hit(const Vec<double>& o, const Vec<doubl
     const double a = len2(d), half_b = dot(oc, d), c = len2(oc) - rr;
     const double disc = half_b * half_b - a * c;
     if (disc < 0) return;                               // grazing: keep the float root
-    const double sq = sqrt(disc);
-    const double r1 = (-half_b - sq) / a, r2 = (-half_b + sq) / a;
+    const double sq = sqrt_newton(disc), inv_a = rcp_newton(a);
+    const double r1 = (-half_b - sq) * inv_a, r2 = (-half_b + sq) * inv_a;
     t = fabs(r1 - t) <= fabs(r2 - t) ? r1 : r2;
 }
 
@@ -240,47 +230,38 @@ __device__ __forceinline__ Surface<T> surface_at(const SceneView<T>& sv, const t
                                                  const typename Quad<T>::type* __restrict__ sc,
                                                  const int* __restrict__ meta, const Ray<T>& r, T& t, int slot) {
     Surface<T> s;
-    Vec<T> outward;
+    // the sphere that was hit, as doubles (exact for both the float slots and the double big spheres)
+    double4 A, B;
     int m;
     if (slot < sv.n_slots) {
         const typename Quad<T>::type a = sa[slot], b = sb[slot], c = sc[slot];
         m = meta[slot];
-        if (sizeof(T) == 4) {
-            const Vec<double> od = mk<double>(r.o.x, r.o.y, r.o.z), dd = mk<double>(r.d.x, r.d.y, r.d.z);
-            const Vec<double> center = mk<double>(a.x, a.y, a.z) + double(r.tm) * mk<double>(b.x, b.y, b.z);
-            double td = double(t);
-            refine_hit(od, dd, center, double(a.w) * double(a.w), td);
-            const Vec<double> pd = od + td * dd;
-            const Vec<double> nd = (1.0 / double(a.w)) * (pd - center);
-            t = T(td);
-            s.p = mk<T>(T(pd.x), T(pd.y), T(pd.z));
-            outward = mk<T>(T(nd.x), T(nd.y), T(nd.z));
-        } else {
-            s.p = r.o + t * r.d;                                        // src/ray.h:19-21
-            const Vec<T> center = sphere_center<T>(a, b, r.tm);
-            outward = (T(1) / a.w) * (s.p - center);                    // src/sphere.h:52
-        }
+        A = make_double4(a.x, a.y, a.z, a.w); B = make_double4(b.x, b.y, b.z, 0.0);
         s.albedo = mk<T>(c.x, c.y, c.z); s.param = c.w;
     } else {
         const int k = slot - sv.n_slots;
-        const double4 a = sv.big_a[k], b = sv.big_b[k], c = sv.big_c[k];
+        A = sv.big_a[k]; B = sv.big_b[k];
+        const double4 c = sv.big_c[k];
         m = sv.big_meta[k];
-        const Vec<double> center = sphere_center<double>(a, b, double(r.tm));
-        Vec<double> pd;
-        if (sizeof(T) == 4) {
-            const Vec<double> od = mk<double>(r.o.x, r.o.y, r.o.z), dd = mk<double>(r.d.x, r.d.y, r.d.z);
-            double td = double(t);
-            refine_hit(od, dd, center, b.w, td);                        // t was narrowed to float on the way out
-            pd = od + td * dd;
-            t = T(td);
-            s.p = mk<T>(T(pd.x), T(pd.y), T(pd.z));
-        } else {
-            s.p = r.o + t * r.d;
-            pd = mk<double>(s.p.x, s.p.y, s.p.z);
-        }
-        const Vec<double> od2 = (1.0 / a.w) * (pd - center);
-        outward = mk<T>(T(od2.x), T(od2.y), T(od2.z));
         s.albedo = mk<T>(T(c.x), T(c.y), T(c.z)); s.param = T(c.w);
+    }
+    const Vec<double> center = mk<double>(A.x, A.y, A.z) + double(r.tm) * mk<double>(B.x, B.y, B.z);   // src/sphere.h:68-72
+    Vec<T> outward;
+    if (sizeof(T) == 4) {
+        // fast mode: one double solve of the winning sphere on the same float inputs (refine_hit)
+        const Vec<double> od = mk<double>(r.o.x, r.o.y, r.o.z), dd = mk<double>(r.d.x, r.d.y, r.d.z);
+        double td = double(t);
+        refine_hit(od, dd, center, A.w * A.w, td);
+        const Vec<double> pd = od + td * dd;
+        const Vec<double> nd = rcp_newton(A.w) * (pd - center);
+        t = T(td);
+        s.p = mk<T>(T(pd.x), T(pd.y), T(pd.z));
+        outward = mk<T>(T(nd.x), T(nd.y), T(nd.z));
+    } else {
+        s.p = r.o + t * r.d;                                            // src/ray.h:19-21
+        const Vec<double> pd = mk<double>(s.p.x, s.p.y, s.p.z);
+        const Vec<double> nd = (1.0 / A.w) * (pd - center);             // src/sphere.h:52
+        outward = mk<T>(T(nd.x), T(nd.y), T(nd.z));
     }
     s.type = RT_META_TYPE(m);
     s.id = RT_META_ID(m);

@@ -1,0 +1,261 @@
+// rt_wavefront.cuh -- the wavefront bounce loop, SM-resident.
+//
+// ray_color's recursion (src/camera_cpu.h:8-26) as a queue-driven wavefront: paths live in a POOL,
+// stages (trace / shade by material / end-of-path + next sample) work on QUEUES of path ids, every
+// stage runs over a compacted queue (warp ballot + prefix popcount), hits are regrouped by material
+// before shading.  B200-first twist: the pool and its queues live in SHARED memory (227 KB per SM)
+// next to the staged scene, one pool of P paths per warp, so regrouping costs a few LDS/STS instead
+// of a round trip of the ray state through HBM and a kernel launch per stage; a warp needs only
+// __syncwarp() between its stages, and the other warps of the SM fill the issue slots meanwhile.
+//
+//   pool slot  = one pixel of the warp's 16 x (P/16) tile (x one sample slice): samples of a pixel
+//                are walked in order by its slot, so the per-pixel sum has the reference's order
+//                (src/camera.h:41-44) and needs no atomics
+//   TRACE      lanes PULL rays from the trace queue; node / leaf / pull sections are scheduled per
+//                warp like in render_sched_kernel, but a lane whose ray ends pulls the next ray at
+//                once (cheap: 9 LDS + 4 divisions) instead of waiting for a shade section
+//   HIT        finished rays, grouped opaque (lambertian + metal) | glass: surface_at + scatter
+//   END        misses (sky) and ended paths: accumulate, start the pixel's next sample (get_ray)
+//
+// Per-lane arithmetic is the same device functions as the megakernels, so parity mode (T = double)
+// stays bit-identical to the oracle.
+#pragma once
+
+#include "rt_kernels.cuh"
+
+namespace rt {
+
+template <typename T, int P> struct Pool {
+    enum { OX, OY, OZ, TM, DX, DY, DZ, TR, TG, TB, TBEST, NF };        // T arrays [P]
+    enum { BEST, SAMPLE, DEPTH, NI };                                   // int arrays [P]
+    enum { QUEUE, LOPAQUE, LGLASS, LEND, NL };                          // byte lists [P]
+    static constexpr int bytes = NF * P * int(sizeof(T)) + NI * P * 4 + NL * P;
+    static constexpr int tile_w = 16, tile_h = P / 16;
+    static_assert(P % 32 == 0 && P <= 128, "pool: path id is 7 bits, lists are filled 32 at a time");
+};
+
+template <typename T, bool STAGED, int P, int BLOCK>
+__global__ void __launch_bounds__(BLOCK, 1)
+render_pool_kernel(const RenderParams<T> p) {
+    typedef Pool<T, P> L;
+    typedef typename Quad<T>::type Q;
+    extern __shared__ __align__(16) unsigned char smem[];
+    const Staged<T> st = stage_scene<T>(p.scene, smem, STAGED);
+    const SceneView<T>& sv = p.scene;
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned lt = (1u << lane) - 1u;
+
+    unsigned char* wb = smem + (STAGED ? staged_bytes_aligned<T>(sv.n_nodes, sv.n_slots) : 0) + size_t(warp) * L::bytes;
+    T* const F = reinterpret_cast<T*>(wb);
+    int* const I = reinterpret_cast<int*>(F + L::NF * P);
+    unsigned char* const B = reinterpret_cast<unsigned char*>(I + L::NI * P);
+
+    const int W = p.cam.image_width, H = p.cam.image_height;
+    const int njobs = p.tiles_x * p.tiles_y * p.slices;
+    const int th_p = p.th_s, th_l = p.th_l;
+    unsigned long long my_rays = 0;
+    int stack[RT_STACK];
+
+    for (;;) {
+        int job = 0;
+        if (lane == 0) job = int(atomicAdd(p.job_counter, 1u));
+        job = __shfl_sync(FULL, job, 0);
+        if (job >= njobs) break;
+        const int slice = job % p.slices, tile = job / p.slices;
+        const int bx = (tile % p.tiles_x) * L::tile_w, by = (tile / p.tiles_x) * L::tile_h;
+        const int s_begin = p.sample_begin + int((long long)p.sample_count * slice / p.slices);
+        const int s_end = p.sample_begin + int((long long)p.sample_count * (slice + 1) / p.slices);
+        Q* const acc_base = p.accum + size_t(slice) * size_t(H) * size_t(W);
+
+        int n_q = 0, n_end = 0, n_opq = 0, n_gls = 0;
+        // every pixel of the tile: set up the accumulator, queue the first sample
+        for (int k = lane; k < P; k += 32) {
+            const int i = bx + (k & 15), j = by + (k >> 4);
+            const bool in_image = i < W && j < H;
+            if (in_image) {
+                Q* dst = acc_base + size_t(j) * size_t(W) + size_t(i);
+                Q v;
+                if (p.accumulate) { v = *dst; } else { v.x = 0; v.y = 0; v.z = 0; v.w = 0; }
+                v.w += decltype(v.x)(s_end - s_begin);
+                *dst = v;
+            }
+            I[L::SAMPLE * P + k] = s_begin; I[L::DEPTH * P + k] = 0;
+            const bool start = in_image && s_begin < s_end && p.max_depth > 0;    // max_depth <= 0: black (src/camera_cpu.h:12-13)
+            const unsigned m = __ballot_sync(FULL, start);
+            if (start) B[L::LEND * P + n_end + __popc(m & lt)] = (unsigned char)(k | 0x80);   // 0x80: nothing to add
+            n_end += __popc(m);
+        }
+        __syncwarp();
+
+        for (;;) {
+            // ------------------------------------------------------------------ END stage
+            // misses add thr * sky (src/camera_cpu.h:23-25); every entry then starts its pixel's
+            // next sample (camera::render's sample loop + get_ray, src/camera.h:41-44,87-100)
+            for (int b = 0; b < n_end; b += 32) {
+                const int idx = b + lane;
+                bool push = false; int pid = 0;
+                if (idx < n_end) {
+                    const int e = B[L::LEND * P + idx];
+                    pid = e & 0x7f;
+                    const int i = bx + (pid & 15), j = by + (pid >> 4);
+                    if (!(e & 0x80)) {
+                        const Vec<T> d = mk<T>(F[L::DX * P + pid], F[L::DY * P + pid], F[L::DZ * P + pid]);
+                        const Vec<T> thr = mk<T>(F[L::TR * P + pid], F[L::TG * P + pid], F[L::TB * P + pid]);
+                        const Vec<T> c = thr * sky<T>(d);
+                        Q* dst = acc_base + size_t(j) * size_t(W) + size_t(i);
+                        Q v = *dst;
+                        v.x += decltype(v.x)(c.x); v.y += decltype(v.x)(c.y); v.z += decltype(v.x)(c.z);
+                        *dst = v;
+                    }
+                    const int s = I[L::SAMPLE * P + pid];
+                    if (s < s_end) {
+                        Philox rng; rng.init(p.seed);
+                        rng.set(uint32_t(j) * uint32_t(W) + uint32_t(i), uint32_t(s), 0u);
+                        const Ray<T> ray = get_ray<T>(p.cam, i, j, rng);
+                        F[L::OX * P + pid] = ray.o.x; F[L::OY * P + pid] = ray.o.y; F[L::OZ * P + pid] = ray.o.z; F[L::TM * P + pid] = ray.tm;
+                        F[L::DX * P + pid] = ray.d.x; F[L::DY * P + pid] = ray.d.y; F[L::DZ * P + pid] = ray.d.z;
+                        F[L::TR * P + pid] = T(1); F[L::TG * P + pid] = T(1); F[L::TB * P + pid] = T(1);
+                        I[L::SAMPLE * P + pid] = s + 1; I[L::DEPTH * P + pid] = p.max_depth;
+                        push = true;
+                    }
+                }
+                const unsigned m = __ballot_sync(FULL, push);
+                if (push) B[L::QUEUE * P + n_q + __popc(m & lt)] = (unsigned char)pid;
+                n_q += __popc(m);
+            }
+            n_end = 0;
+            __syncwarp();
+            if (n_q == 0) break;                                   // every pixel of the tile is done
+
+            // ------------------------------------------------------------------ BIG stage
+            // every queued ray against the spheres kept out of the tree (the r = 1000 ground), in
+            // double, with a full warp: gives the tree walk a tight t_max from its first node on
+            if (sv.n_big > 0) {
+                for (int b = 0; b < n_q; b += 32) {
+                    const int idx = b + lane;
+                    if (idx < n_q) {
+                        const int pid = B[L::QUEUE * P + idx];
+                        Ray<T> ray;
+                        ray.o = mk<T>(F[L::OX * P + pid], F[L::OY * P + pid], F[L::OZ * P + pid]);
+                        ray.d = mk<T>(F[L::DX * P + pid], F[L::DY * P + pid], F[L::DZ * P + pid]);
+                        ray.tm = F[L::TM * P + pid];
+                        T tb; int bid, bslot;
+                        trav_big<T>(sv, ray, T(0.001), T(INFINITY), tb, bid, bslot);
+                        F[L::TBEST * P + pid] = tb; I[L::BEST * P + pid] = bslot;
+                    }
+                }
+                __syncwarp();
+            }
+
+            // ---------------------------------------------------------------- TRACE stage
+            {
+                int head = 0, pid = 0;
+                bool has = false;
+                Ray<T> ray; ray.o = mk<T>(0, 0, 0); ray.d = mk<T>(0, 0, 1); ray.tm = 0;
+                Trav<T> tv; tv.cur = RT_SENTINEL; tv.sp = 0; tv.tbest = 0; tv.best_id = -1; tv.best_slot = -1; tv.qa = 1; tv.inv = mk<T>(0, 0, 0);
+                for (;;) {
+                    const bool isN = tv.cur >= 0;
+                    const bool isP = tv.cur == RT_SENTINEL;
+                    const bool isL = !isN && !isP;
+                    const int nN = __popc(__ballot_sync(FULL, isN));
+                    const int nL = __popc(__ballot_sync(FULL, isL));
+                    const unsigned mP = __ballot_sync(FULL, isP);
+                    const bool any_result = __ballot_sync(FULL, isP && has) != 0u;
+                    const int avail = n_q - head, nP = 32 - nN - nL;
+                    const bool can_pull = any_result || (avail > 0 && nP > 0);
+                    if ((nN | nL) == 0 && !can_pull) break;
+
+                    if (can_pull && (nP >= th_p || (nN | nL) == 0)) {
+                        // ---- pull: hand in the finished ray (regrouped by what it hit), take the next one
+                        int key = -1;
+                        if (isP && has) {
+                            F[L::TBEST * P + pid] = tv.tbest; I[L::BEST * P + pid] = tv.best_slot;
+                            has = false;
+                            if (tv.best_slot < 0) key = 2;
+                            else {
+                                const int m = tv.best_slot < sv.n_slots ? st.meta[tv.best_slot] : sv.big_meta[tv.best_slot - sv.n_slots];
+                                key = RT_META_TYPE(m) == 2 ? 1 : 0;
+                            }
+                        }
+                        const unsigned m0 = __ballot_sync(FULL, key == 0), m1 = __ballot_sync(FULL, key == 1), m2 = __ballot_sync(FULL, key == 2);
+                        if (key == 0) B[L::LOPAQUE * P + n_opq + __popc(m0 & lt)] = (unsigned char)pid;
+                        if (key == 1) B[L::LGLASS * P + n_gls + __popc(m1 & lt)] = (unsigned char)pid;
+                        if (key == 2) B[L::LEND * P + n_end + __popc(m2 & lt)] = (unsigned char)pid;     // miss: sky is added in END
+                        n_opq += __popc(m0); n_gls += __popc(m1); n_end += __popc(m2);
+                        const int rank = __popc(mP & lt);
+                        if (isP && rank < avail) {
+                            pid = B[L::QUEUE * P + head + rank];
+                            ray.o = mk<T>(F[L::OX * P + pid], F[L::OY * P + pid], F[L::OZ * P + pid]);
+                            ray.d = mk<T>(F[L::DX * P + pid], F[L::DY * P + pid], F[L::DZ * P + pid]);
+                            ray.tm = F[L::TM * P + pid];
+                            tv.tbest = T(INFINITY); tv.best_slot = -1; tv.best_id = -1;
+                            if (sv.n_big > 0) {
+                                tv.tbest = F[L::TBEST * P + pid]; tv.best_slot = I[L::BEST * P + pid];
+                                if (tv.best_slot >= 0) tv.best_id = RT_META_ID(sv.big_meta[tv.best_slot - sv.n_slots]);
+                            }
+                            trav_setup<T>(sv, ray, tv);
+                            has = true;
+                            ++my_rays;                                   // one ray_color entry with depth > 0
+                        }
+                        head += min(__popc(mP), avail);
+                    } else if (nL >= th_l || nL > nN) {
+                        if (isL) trav_leaf<T>(st.sa, st.sb, st.meta, ray, T(0.001), tv, stack);
+                    } else {
+                        if (isN) trav_node<T>(st.nodes, ray, T(0.001), tv, stack);
+                    }
+                }
+            }
+            n_q = 0;
+            __syncwarp();
+
+            // ------------------------------------------------------------------ HIT stage
+            // rec.mat->scatter (src/camera_cpu.h:18-20), opaque hits first, then glass
+            for (int l = 0; l < 2; ++l) {
+                const unsigned char* list = B + (l ? L::LGLASS : L::LOPAQUE) * P;
+                const int n = l ? n_gls : n_opq;
+                for (int b = 0; b < n; b += 32) {
+                    const int idx = b + lane;
+                    bool cont = false, ended = false; int pid = 0;
+                    if (idx < n) {
+                        pid = list[idx];
+                        const int i = bx + (pid & 15), j = by + (pid >> 4);
+                        Ray<T> ray;
+                        ray.o = mk<T>(F[L::OX * P + pid], F[L::OY * P + pid], F[L::OZ * P + pid]);
+                        ray.d = mk<T>(F[L::DX * P + pid], F[L::DY * P + pid], F[L::DZ * P + pid]);
+                        ray.tm = F[L::TM * P + pid];
+                        T t = F[L::TBEST * P + pid];
+                        const int slot = I[L::BEST * P + pid], s = I[L::SAMPLE * P + pid];
+                        int depth = I[L::DEPTH * P + pid];
+                        const Surface<T> sf = surface_at<T>(sv, st.sa, st.sb, st.sc, st.meta, ray, t, slot);
+                        Philox rng; rng.init(p.seed);
+                        rng.set(uint32_t(j) * uint32_t(W) + uint32_t(i), uint32_t(s - 1), uint32_t(p.max_depth - depth + 1));   // b-th hit: stage b
+                        Vec<T> att, dnew;
+                        if (!scatter<T>(sf.type, sf.albedo, sf.param, ray.d, sf.normal, sf.front_face, rng, att, dnew)) {
+                            ended = true;                                       // absorbed: contributes 0 (:20)
+                        } else if (--depth == 0) {
+                            ended = true;                                       // depth exhausted: contributes 0 (:12-13)
+                        } else {
+                            cont = true;
+                            ray.o = sf.p; ray.d = dnew;                         // time is inherited (src/material.h:22)
+                            F[L::OX * P + pid] = ray.o.x; F[L::OY * P + pid] = ray.o.y; F[L::OZ * P + pid] = ray.o.z;
+                            F[L::DX * P + pid] = ray.d.x; F[L::DY * P + pid] = ray.d.y; F[L::DZ * P + pid] = ray.d.z;
+                            F[L::TR * P + pid] *= att.x; F[L::TG * P + pid] *= att.y; F[L::TB * P + pid] *= att.z;
+                            I[L::DEPTH * P + pid] = depth;
+                        }
+                    }
+                    const unsigned mc = __ballot_sync(FULL, cont), me = __ballot_sync(FULL, ended);
+                    if (cont) B[L::QUEUE * P + n_q + __popc(mc & lt)] = (unsigned char)pid;
+                    if (ended) B[L::LEND * P + n_end + __popc(me & lt)] = (unsigned char)(pid | 0x80);
+                    n_q += __popc(mc); n_end += __popc(me);
+                }
+            }
+            n_opq = 0; n_gls = 0;
+            __syncwarp();
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) my_rays += __shfl_xor_sync(FULL, my_rays, o);
+    if (lane == 0 && my_rays) atomicAdd(p.ray_counter, my_rays);
+}
+
+}  // namespace rt

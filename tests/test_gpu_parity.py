@@ -27,13 +27,21 @@ def frac_within_1(a, b):
     return float((np.abs(a.astype(int) - b.astype(int)).max(-1) <= 1).mean())
 
 
+VARIANTS = ["megakernel", "wavefront", "lockstep"]
+
+
+def variant_of(rt, name):
+    return {"megakernel": rt.MEGAKERNEL, "wavefront": rt.WAVEFRONT, "lockstep": rt.MEGA_LOCKSTEP}[name]
+
+
 # ------------------------------------------------------------------------ full image --
-def test_c1_image_f64_is_the_reference_image(ctx_scene, rt, O, scene):
+@pytest.mark.parametrize("variant", VARIANTS)
+def test_c1_image_f64_is_the_reference_image(ctx_scene, rt, O, scene, variant):
     """BASELINE config 1: final scene 400x225, 10 spp, depth 50.  Parity mode reproduces the
     reference harness (fixture) and the oracle exactly: bytes, P3 text, ray count."""
     s, m = scene
     cam = rt.camera_rtiow(400, 10, 50)
-    ctx_scene.render(cam, precision=rt.F64, seed=0)
+    ctx_scene.render(cam, precision=rt.F64, seed=0, variant=variant_of(rt, variant))
     out = ctx_scene.readback(10, want_ppm=True)
     st = ctx_scene.stats()
     g = golden("ref_c1_philox_seed0.npz")
@@ -46,9 +54,10 @@ def test_c1_image_f64_is_the_reference_image(ctx_scene, rt, O, scene):
     assert np.allclose(out["sum"], ref["sum"], rtol=1e-13, atol=1e-14)
 
 
-def test_c1_image_f32_within_north_star_tolerance(ctx_scene, rt):
+@pytest.mark.parametrize("variant", VARIANTS)
+def test_c1_image_f32_within_north_star_tolerance(ctx_scene, rt, variant):
     cam = rt.camera_rtiow(400, 10, 50)
-    ctx_scene.render(cam, precision=rt.F32, seed=0)
+    ctx_scene.render(cam, precision=rt.F32, seed=0, variant=variant_of(rt, variant))
     out = ctx_scene.readback(10)
     g = golden("ref_c1_philox_seed0.npz")
     assert psnr8(out["rgb8"], g["rgb8"]) >= PSNR_MIN
@@ -57,12 +66,13 @@ def test_c1_image_f32_within_north_star_tolerance(ctx_scene, rt):
     assert abs(rays - int(g["rays"])) / int(g["rays"]) < 5e-3
 
 
+@pytest.mark.parametrize("variant", VARIANTS)
 @pytest.mark.parametrize("seed,width,spp,depth", [(1, 160, 4, 50), (2**40 + 5, 97, 3, 7), (9, 64, 1, 1), (3, 48, 2, 0)])
-def test_small_images_f64_match_oracle(ctx_scene, rt, O, scene, seed, width, spp, depth):
-    """other seeds (incl. a 64-bit key), odd sizes (ragged 8x4 tiles), depth 1 and depth 0 (black)."""
+def test_small_images_f64_match_oracle(ctx_scene, rt, O, scene, seed, width, spp, depth, variant):
+    """other seeds (incl. a 64-bit key), odd sizes (ragged tiles), depth 1 and depth 0 (black)."""
     s, m = scene
     cam = rt.camera_rtiow(width, spp, depth)
-    ctx_scene.render(cam, precision=rt.F64, seed=seed)
+    ctx_scene.render(cam, precision=rt.F64, seed=seed, variant=variant_of(rt, variant))
     out = ctx_scene.readback(spp, want_ppm=True)
     ref = O.render(s, m, O.camera_rtiow(width, spp, depth), rng_mode=O.RNG_PHILOX, seed=seed, use_bvh=True)
     assert ctx_scene.stats()["rays"] == ref["rays"]

@@ -14,6 +14,7 @@ def run(variant, sched=0, slices=0, reps=3):
         ctx.render(cam, precision=prec, seed=0, variant=variant, sched=sched, slices=slices)
         ctx.synchronize(); st = ctx.stats(); best = min(best, st["render_ms"])
     return best, st
+VAR = int(os.environ.get("VARIANT", str(rt.MEGAKERNEL)))
 ms, st = run(rt.MEGA_LOCKSTEP)
 ref = ctx.readback(spp, want_sum=False)["rgb8"]
 print(f"lockstep            ms {ms:8.3f} Msamples/s {st['samples']/ms/1e3:8.1f} Mrays/s {st['rays']/ms/1e3:8.1f} slices {st['slices']}")
@@ -25,7 +26,7 @@ for shape in shapes:
     for t in ths:
         for l in thl:
             for sl in sls:
-                ms, st = run(rt.MEGAKERNEL, sched=t | (l << 8) | (shape << 16), slices=sl)
+                ms, st = run(VAR, sched=t | (l << 8) | (shape << 16), slices=sl)
                 img = ctx.readback(spp, want_sum=False)["rgb8"]
-                same = bool(np.array_equal(img, ref))
+                same = float((np.abs(img.astype(int) - ref.astype(int)).max(-1) <= 1).mean())
                 print(f"shape {shape} th_s {t:2d} th_l {l:2d} slices {st['slices']:2d} ms {ms:8.3f} Msamples/s {st['samples']/ms/1e3:8.1f} Mrays/s {st['rays']/ms/1e3:8.1f} same_image {same}", flush=True)
