@@ -157,6 +157,9 @@ template <typename T> SceneView<T> scene_view(const rt_ctx* c) {
     sv.meta = c->meta.p;
     sv.big_a = c->big_a.p; sv.big_b = c->big_b.p; sv.big_c = c->big_c.p; sv.big_meta = c->big_meta.p;
     sv.n_slots = c->n_slots; sv.n_nodes = c->n_nodes; sv.n_big = c->n_big; sv.root_ref = c->root_ref;
+    const int q = int(sizeof(typename Quad<T>::type));
+    sv.off_sa = c->n_nodes * 64; sv.off_sb = sv.off_sa + c->n_slots * q; sv.off_sc = sv.off_sb + c->n_slots * q;
+    sv.off_meta = sv.off_sc + c->n_slots * q;
     return sv;
 }
 
@@ -413,8 +416,9 @@ int render_impl(rt_ctx* ctx, const rt_camera& cam, const rt_render_opts& o, int 
     CK(cudaMemsetAsync(ctx->ray_counter.p, 0, sizeof(unsigned long long), ctx->stream));
     CK(cudaEventRecord(ctx->ev[0], ctx->stream));
     // section thresholds: o.sched = th_s | th_l << 8 (0 = defaults, tuned on B200: see DESIGN.md)
-    p.th_s = (o.sched & 0xff) ? (o.sched & 0xff) : (o.variant == RT_WAVEFRONT ? 8 : 28);
+    p.th_s = (o.sched & 0xff) ? (o.sched & 0xff) : (o.variant == RT_WAVEFRONT ? 24 : 28);
     p.th_l = ((o.sched >> 8) & 0xff) ? ((o.sched >> 8) & 0xff) : 33;
+    p.th_n = ((o.sched >> 20) & 0xf) ? ((o.sched >> 20) & 0xf) : 4;      // node loop runs while >= th_n/8 of its lanes remain
     if (o.variant == RT_WAVEFRONT) CK(launch_render_pool<T>(p, pshape, staged, ctx->sm_count, ctx->stream));
     else if (o.variant == RT_MEGA_LOCKSTEP) CK(launch_render_mega<T>(p, staged, smem, ctx->sm_count, ctx->stream));
     else CK(launch_render_sched<T>(p, sched_shape<T>(o.sched), staged, smem, ctx->sm_count, ctx->stream));

@@ -23,11 +23,13 @@ __device__ __forceinline__ Staged<T> stage_scene(const SceneView<T>& sv, unsigne
         st.nodes = sv.nodes; st.sa = sv.sa; st.sb = sv.sb; st.sc = sv.sc; st.meta = sv.meta;
         return st;
     }
+    // offsets come precomputed from the host (constant bank): one add per use when the compiler
+    // rematerialises these pointers inside the hot loops instead of a chain of multiplies
     float4* n = reinterpret_cast<float4*>(smem);
-    Q* a = reinterpret_cast<Q*>(n + 4 * sv.n_nodes);
-    Q* b = a + sv.n_slots;
-    Q* c = b + sv.n_slots;
-    int* m = reinterpret_cast<int*>(c + sv.n_slots);
+    Q* a = reinterpret_cast<Q*>(smem + sv.off_sa);
+    Q* b = reinterpret_cast<Q*>(smem + sv.off_sb);
+    Q* c = reinterpret_cast<Q*>(smem + sv.off_sc);
+    int* m = reinterpret_cast<int*>(smem + sv.off_meta);
     for (int i = threadIdx.x; i < 4 * sv.n_nodes; i += blockDim.x) n[i] = sv.nodes[i];
     for (int i = threadIdx.x; i < sv.n_slots; i += blockDim.x) { a[i] = sv.sa[i]; b[i] = sv.sb[i]; c[i] = sv.sc[i]; m[i] = sv.meta[i]; }
     __syncthreads();

@@ -27,7 +27,7 @@ template <typename T> struct RenderParams {
     int sample_begin, sample_count, max_depth;
     int slices, tiles_x, tiles_y;
     int accumulate;
-    int th_s, th_l;                     // section thresholds of render_sched_kernel
+    int th_s, th_l, th_n;               // section thresholds of the warp schedulers (render_sched_kernel, render_pool_kernel)
 };
 
 struct HitRec;
@@ -51,7 +51,7 @@ inline void pool_shape(int shape, int* paths, int* block) {
     *paths = P[shape]; *block = B[shape];
 }
 template <typename T> inline size_t pool_warp_bytes(int paths) { return size_t(paths) * (11 * sizeof(T) + 3 * 4 + 4); }
-#define RT_POOL_DEFAULT_SHAPE(T) (sizeof(T) == 4 ? 2 : 0)
+#define RT_POOL_DEFAULT_SHAPE(T) (sizeof(T) == 4 ? 4 : 0)
 template <typename T> cudaError_t launch_render_pool(const RenderParams<T>& p, int shape, bool staged, int sm_count, cudaStream_t st);
 
 template <typename T> cudaError_t launch_render_mega(const RenderParams<T>& p, bool staged, size_t smem_bytes, int sm_count, cudaStream_t st);

@@ -29,6 +29,7 @@ template <typename T> struct SceneView {
     const double4* big_c;
     const int* big_meta;
     int n_slots, n_nodes, n_big, root_ref;
+    int off_sa, off_sb, off_sc, off_meta;   // byte offsets of the staged copies in shared memory (nodes at 0)
 };
 
 // Slab test, src/aabb.h:35-53 with 1/d hoisted.  Returns entry distance in tnear.

@@ -53,7 +53,7 @@ render_pool_kernel(const RenderParams<T> p) {
 
     const int W = p.cam.image_width, H = p.cam.image_height;
     const int njobs = p.tiles_x * p.tiles_y * p.slices;
-    const int th_p = p.th_s, th_l = p.th_l;
+    const int th_p = p.th_s, th_l = p.th_l, th_n = p.th_n;
     unsigned long long my_rays = 0;
     int stack[RT_STACK];
 
@@ -151,38 +151,19 @@ render_pool_kernel(const RenderParams<T> p) {
             // ---------------------------------------------------------------- TRACE stage
             {
                 int head = 0, pid = 0;
-                bool has = false;
                 Ray<T> ray; ray.o = mk<T>(0, 0, 0); ray.d = mk<T>(0, 0, 1); ray.tm = 0;
                 Trav<T> tv; tv.cur = RT_SENTINEL; tv.sp = 0; tv.tbest = 0; tv.best_id = -1; tv.best_slot = -1; tv.qa = 1; tv.inv = mk<T>(0, 0, 0);
                 for (;;) {
                     const bool isN = tv.cur >= 0;
                     const bool isP = tv.cur == RT_SENTINEL;
-                    const bool isL = !isN && !isP;
                     const int nN = __popc(__ballot_sync(FULL, isN));
-                    const int nL = __popc(__ballot_sync(FULL, isL));
                     const unsigned mP = __ballot_sync(FULL, isP);
-                    const bool any_result = __ballot_sync(FULL, isP && has) != 0u;
-                    const int avail = n_q - head, nP = 32 - nN - nL;
-                    const bool can_pull = any_result || (avail > 0 && nP > 0);
-                    if ((nN | nL) == 0 && !can_pull) break;
+                    const int nP = __popc(mP), nL = 32 - nN - nP;
+                    const int avail = n_q - head;
+                    if (nP == 32 && avail == 0) break;
 
-                    if (can_pull && (nP >= th_p || (nN | nL) == 0)) {
-                        // ---- pull: hand in the finished ray (regrouped by what it hit), take the next one
-                        int key = -1;
-                        if (isP && has) {
-                            F[L::TBEST * P + pid] = tv.tbest; I[L::BEST * P + pid] = tv.best_slot;
-                            has = false;
-                            if (tv.best_slot < 0) key = 2;
-                            else {
-                                const int m = tv.best_slot < sv.n_slots ? st.meta[tv.best_slot] : sv.big_meta[tv.best_slot - sv.n_slots];
-                                key = RT_META_TYPE(m) == 2 ? 1 : 0;
-                            }
-                        }
-                        const unsigned m0 = __ballot_sync(FULL, key == 0), m1 = __ballot_sync(FULL, key == 1), m2 = __ballot_sync(FULL, key == 2);
-                        if (key == 0) B[L::LOPAQUE * P + n_opq + __popc(m0 & lt)] = (unsigned char)pid;
-                        if (key == 1) B[L::LGLASS * P + n_gls + __popc(m1 & lt)] = (unsigned char)pid;
-                        if (key == 2) B[L::LEND * P + n_end + __popc(m2 & lt)] = (unsigned char)pid;     // miss: sky is added in END
-                        n_opq += __popc(m0); n_gls += __popc(m1); n_end += __popc(m2);
+                    if (avail > 0 && (nP >= th_p || (nN | nL) == 0)) {
+                        // ---- pull: idle lanes take the next rays of the queue
                         const int rank = __popc(mP & lt);
                         if (isP && rank < avail) {
                             pid = B[L::QUEUE * P + head + rank];
@@ -195,16 +176,49 @@ render_pool_kernel(const RenderParams<T> p) {
                                 if (tv.best_slot >= 0) tv.best_id = RT_META_ID(sv.big_meta[tv.best_slot - sv.n_slots]);
                             }
                             trav_setup<T>(sv, ray, tv);
-                            has = true;
+                            if (tv.cur == RT_SENTINEL) { F[L::TBEST * P + pid] = tv.tbest; I[L::BEST * P + pid] = tv.best_slot; }   // no tree
                             ++my_rays;                                   // one ray_color entry with depth > 0
                         }
-                        head += min(__popc(mP), avail);
+                        head += min(nP, avail);
                     } else if (nL >= th_l || nL > nN) {
-                        if (isL) trav_leaf<T>(st.sa, st.sb, st.meta, ray, T(0.001), tv, stack);
+                        if (!isN && !isP) {
+                            trav_leaf<T>(st.sa, st.sb, st.meta, ray, T(0.001), tv, stack);
+                            if (tv.cur == RT_SENTINEL) { F[L::TBEST * P + pid] = tv.tbest; I[L::BEST * P + pid] = tv.best_slot; }
+                        }
                     } else {
-                        if (isN) trav_node<T>(st.nodes, ray, T(0.001), tv, stack);
+                        // node visits, repeated while most of the lanes that started them still have a node
+                        int now;
+                        do {
+                            if (tv.cur >= 0) {
+                                trav_node<T>(st.nodes, ray, T(0.001), tv, stack);
+                                if (tv.cur == RT_SENTINEL) { F[L::TBEST * P + pid] = tv.tbest; I[L::BEST * P + pid] = tv.best_slot; }
+                            }
+                            now = __popc(__ballot_sync(FULL, tv.cur >= 0));
+                        } while (now > 0 && now * 8 >= nN * th_n);
                     }
                 }
+            }
+            __syncwarp();
+
+            // ------------------------------------------------------------- CLASSIFY stage
+            // regroup the traced rays by what they hit: opaque | glass | nothing (warp ballot + prefix popcount)
+            for (int b = 0; b < n_q; b += 32) {
+                const int idx = b + lane;
+                int key = -1, pid = 0;
+                if (idx < n_q) {
+                    pid = B[L::QUEUE * P + idx];
+                    const int slot = I[L::BEST * P + pid];
+                    if (slot < 0) key = 2;
+                    else {
+                        const int m = slot < sv.n_slots ? st.meta[slot] : sv.big_meta[slot - sv.n_slots];
+                        key = RT_META_TYPE(m) == 2 ? 1 : 0;
+                    }
+                }
+                const unsigned m0 = __ballot_sync(FULL, key == 0), m1 = __ballot_sync(FULL, key == 1), m2 = __ballot_sync(FULL, key == 2);
+                if (key == 0) B[L::LOPAQUE * P + n_opq + __popc(m0 & lt)] = (unsigned char)pid;
+                if (key == 1) B[L::LGLASS * P + n_gls + __popc(m1 & lt)] = (unsigned char)pid;
+                if (key == 2) B[L::LEND * P + n_end + __popc(m2 & lt)] = (unsigned char)pid;     // miss: sky is added in END
+                n_opq += __popc(m0); n_gls += __popc(m1); n_end += __popc(m2);
             }
             n_q = 0;
             __syncwarp();

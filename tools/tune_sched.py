@@ -22,11 +22,12 @@ shapes = [int(x) for x in os.environ.get("SHAPES", "1,2,3,4").split(",")]
 ths = [int(x) for x in os.environ.get("THS", "1,8,12,16,20,24,28,32").split(",")]
 thl = [int(x) for x in os.environ.get("THL", "33").split(",")]
 sls = [int(x) for x in os.environ.get("SLICES", "0").split(",")]
+thn = [int(x) for x in os.environ.get("THN", "0").split(",")]
 for shape in shapes:
     for t in ths:
         for l in thl:
-            for sl in sls:
-                ms, st = run(VAR, sched=t | (l << 8) | (shape << 16), slices=sl)
+            for sl, tn in [(a, b) for a in sls for b in thn]:
+                ms, st = run(VAR, sched=t | (l << 8) | (shape << 16) | (tn << 20), slices=sl)
                 img = ctx.readback(spp, want_sum=False)["rgb8"]
                 same = float((np.abs(img.astype(int) - ref.astype(int)).max(-1) <= 1).mean())
-                print(f"shape {shape} th_s {t:2d} th_l {l:2d} slices {st['slices']:2d} ms {ms:8.3f} Msamples/s {st['samples']/ms/1e3:8.1f} Mrays/s {st['rays']/ms/1e3:8.1f} same_image {same}", flush=True)
+                print(f"shape {shape} th_s {t:2d} th_l {l:2d} th_n {tn} slices {st['slices']:2d} ms {ms:8.3f} Msamples/s {st['samples']/ms/1e3:8.1f} Mrays/s {st['rays']/ms/1e3:8.1f} same_image {same}", flush=True)
