@@ -127,6 +127,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--precision", default="f32", choices=["f32", "f64"])
     ap.add_argument("--combine", default="nccl", choices=["nccl", "ipc"])
+    ap.add_argument("--variant", default="wavefront", choices=["wavefront", "megakernel", "lockstep"])
     ap.add_argument("--spp", type=int, default=SPP, help="override spp (a non-default value is NOT the headline config)")
     ap.add_argument("--ref-spp", type=int, default=1, help="spp of the CPU sample per step for --impl reference / cpu_baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -152,6 +153,8 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     prec = rt.F32 if args.precision == "f32" else rt.F64
+    variant = {"wavefront": rt.WAVEFRONT, "megakernel": rt.MEGAKERNEL, "lockstep": rt.MEGA_LOCKSTEP}[args.variant]
+    kernel_name = {"wavefront": "render_pool_kernel", "megakernel": "render_sched_kernel", "lockstep": "render_mega_kernel"}[args.variant]
 
     ctx = rt.Context(local)
     s, m = rt.scene_rtiow()
@@ -168,7 +171,7 @@ def main():
         torch.cuda.synchronize()
 
     # warm-up render so buffers exist, then set up the combine
-    sharding.render_sharded(ctx, cam, rank, world, prec)
+    sharding.render_sharded(ctx, cam, rank, world, prec, variant=variant)
     ctx.synchronize()
     acc = sharding.alias_accum_tensor(ctx) if world > 1 else None
     if world > 1 and args.combine == "ipc":
@@ -180,7 +183,7 @@ def main():
         """one frame; returns nothing, everything is enqueued on ctx's stream"""
         if e2e:
             ctx.upload_scene(s, m)                                   # H2D: the world, every step
-        sharding.render_sharded(ctx, cam, rank, world, prec)
+        sharding.render_sharded(ctx, cam, rank, world, prec, variant=variant)
         if world > 1:
             if args.combine == "nccl":
                 with torch.cuda.stream(stream):
@@ -231,8 +234,8 @@ def main():
     # untimed: the fast mode against parity mode on this very frame (north_star image tolerance)
     check = None
     if rank == 0 and world == 1 and not args.no_check and args.precision == "f32":
-        ctx.render(cam, precision=rt.F32, seed=0); a = ctx.readback(args.spp, want_sum=False)["rgb8"]
-        ctx.render(cam, precision=rt.F64, seed=0); b = ctx.readback(args.spp, want_sum=False)["rgb8"]
+        ctx.render(cam, precision=rt.F32, seed=0, variant=variant); a = ctx.readback(args.spp, want_sum=False)["rgb8"]
+        ctx.render(cam, precision=rt.F64, seed=0, variant=rt.MEGAKERNEL); b = ctx.readback(args.spp, want_sum=False)["rgb8"]
         d = np.abs(a.astype(int) - b.astype(int)).max(-1)
         mse = float(np.mean((a.astype(float) - b.astype(float)) ** 2))
         check = {"f32_vs_f64_psnr_db": 99.0 if mse == 0 else 10 * np.log10(255.0 ** 2 / mse),
@@ -254,12 +257,12 @@ def main():
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": args.precision, "data": "synthetic",
             "config": {"workload": WORKLOAD if args.spp == SPP else f"NOT the headline config: spp={args.spp}",
-                       "variant": "megakernel", "bvh": "host SAH, whole scene staged in shared memory", "seed": 0,
+                       "variant": args.variant, "bvh": "host SAH, whole scene staged in shared memory", "seed": 0,
                        "parallelism": f"sample-range sharding x{world}, combine={args.combine if world > 1 else 'none'}",
                        "l2": "256 MB buffer written between timed iterations (L2 flushed); scene inputs are 55 KB"},
             "mrays_per_s": rays / ms / 1e3, "rays_per_sample": rays / samples,
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak,
-                         "traffic": None, "kernel": "render_mega_kernel", "kernel_ms": kms,
+                         "traffic": None, "kernel": kernel_name, "kernel_ms": kms,
                          "note": f"algorithmic {F_RAY:.0f} flop/ray x {rank_rays:.3e} rays per launch (SURVEY 8d); peak = 148 SMs x 128 "
                                  f"FP32 lanes x 2 x {sm_mhz:.0f} MHz observed under load (not in MEASURED_PEAKS.json); L2-side figure "
                                  f"{rank_rays * B_RAY / (kms * 1e-3) / 1e9:.0f} GB/s algorithmic ({B_RAY:.0f} B/ray)"},

@@ -1,10 +1,203 @@
-// rt_lbvh.cu -- GPU LBVH builder (placeholder body until the Morton/Karras kernels land).
+// rt_lbvh.cu -- GPU LBVH builder.  The reference's bvh.h has no builder (src/bvh.h:12-14 "To be
+// implemented later"); only the traversal contract (:16-24) exists, so the tree below is judged by
+// closest-hit parity, not by its shape.
+//
+//   1. centroid bounds            block reduction + ordered-int atomics
+//   2. 63-bit Morton codes        21 bits per axis on the centroid bounds (the outsized spheres are kept
+//                                 out of the tree by rt_upload_scene, so the grid is not wasted on them)
+//   3. radix sort (key, index)    cub::DeviceRadixSort
+//   4. hierarchy                  Karras 2012: one thread per inner node, common-prefix length with the
+//                                 index as tie-break for duplicate codes
+//   5. refit + emit               bottom-up from the leaves, the second thread to arrive at a node (atomic
+//                                 flag) unites its children and writes the 64-byte traversal record
+//                                 (rt_trace.cuh layout: boxes of BOTH children + refs); depth rides along
 #include "rt_lbvh.h"
+
+#include <cub/cub.cuh>
 
 namespace rt {
 
-cudaError_t build_lbvh_gpu(const HostBox*, int, float4*, int*, int*, int*, cudaStream_t) {
-    return cudaErrorNotSupported;
+namespace {
+
+__device__ __forceinline__ int f2ord(float f) { const int i = __float_as_int(f); return i >= 0 ? i : i ^ 0x7fffffff; }
+__device__ __forceinline__ float ord2f(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
+
+struct Bounds { int lo[3], hi[3]; };    // ordered-int encoded
+
+__global__ void lbvh_init_bounds(Bounds* b) {
+    if (threadIdx.x < 3) { b->lo[threadIdx.x] = 0x7fffffff; b->hi[threadIdx.x] = int(0x80000000); }
+}
+
+__global__ void __launch_bounds__(256) lbvh_centroid_bounds(const HostBox* __restrict__ boxes, int n, Bounds* out) {
+    float lo[3] = { INFINITY, INFINITY, INFINITY }, hi[3] = { -INFINITY, -INFINITY, -INFINITY };
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const HostBox b = boxes[i];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { const float c = 0.5f * (b.lo[a] + b.hi[a]); lo[a] = fminf(lo[a], c); hi[a] = fmaxf(hi[a], c); }
+    }
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        for (int o = 16; o > 0; o >>= 1) {
+            lo[a] = fminf(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], o));
+            hi[a] = fmaxf(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], o));
+        }
+        if ((threadIdx.x & 31) == 0) { atomicMin(&out->lo[a], f2ord(lo[a])); atomicMax(&out->hi[a], f2ord(hi[a])); }
+    }
+}
+
+__device__ __forceinline__ unsigned long long spread21(unsigned long long v) {    // 21 bits -> every third bit
+    v &= 0x1fffffull;
+    v = (v | v << 32) & 0x1f00000000ffffull;
+    v = (v | v << 16) & 0x1f0000ff0000ffull;
+    v = (v | v << 8) & 0x100f00f00f00f00full;
+    v = (v | v << 4) & 0x10c30c30c30c30c3ull;
+    v = (v | v << 2) & 0x1249249249249249ull;
+    return v;
+}
+
+__global__ void __launch_bounds__(256) lbvh_morton(const HostBox* __restrict__ boxes, int n, const Bounds* __restrict__ bounds,
+                                                   unsigned long long* __restrict__ keys, int* __restrict__ vals) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const HostBox b = boxes[i];
+    unsigned long long code = 0;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const float lo = ord2f(bounds->lo[a]), hi = ord2f(bounds->hi[a]);
+        const float c = 0.5f * (b.lo[a] + b.hi[a]);
+        const float ext = hi - lo;
+        float u = ext > 0.0f ? (c - lo) / ext : 0.0f;
+        u = fminf(fmaxf(u, 0.0f), 1.0f);
+        const unsigned long long q = (unsigned long long)fminf(u * 2097152.0f, 2097151.0f);
+        code |= spread21(q) << (2 - a);
+    }
+    keys[i] = code; vals[i] = i;
+}
+
+// common-prefix length of sorted keys i and j (-1 outside the array); duplicates fall back to the index
+__device__ __forceinline__ int delta(const unsigned long long* __restrict__ keys, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    const unsigned long long a = keys[i], b = keys[j];
+    if (a == b) return 64 + __clz(i ^ j);
+    return __clzll(a ^ b);
+}
+
+// children: >= 0 inner node, < 0 leaf ~(slot << 3)  (one sphere per leaf)
+__global__ void __launch_bounds__(256) lbvh_hierarchy(const unsigned long long* __restrict__ keys, int n,
+                                                      int* __restrict__ left, int* __restrict__ right,
+                                                      int* __restrict__ parent_inner, int* __restrict__ parent_leaf) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    const int d = delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1) >= 0 ? 1 : -1;
+    const int dmin = delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (delta(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int t = lmax >> 1; t >= 1; t >>= 1)
+        if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    const int j = i + l * d;
+    const int dnode = delta(keys, n, i, j);
+    int s = 0;
+    for (int div = 2, t = (l + div - 1) / div;; div <<= 1, t = (l + div - 1) / div) {
+        if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+        if (t <= 1) break;
+    }
+    const int gamma = i + s * d + min(d, 0);
+    const int lo = min(i, j), hi = max(i, j);
+    const int cl = lo == gamma ? ~(gamma << 3) : gamma;
+    const int cr = hi == gamma + 1 ? ~((gamma + 1) << 3) : gamma + 1;
+    left[i] = cl; right[i] = cr;
+    if (cl >= 0) parent_inner[cl] = i; else parent_leaf[gamma] = i;
+    if (cr >= 0) parent_inner[cr] = i; else parent_leaf[gamma + 1] = i;
+    if (i == 0) parent_inner[0] = -1;
+}
+
+struct NodeBox { float lo[3], hi[3]; int depth; };
+
+__device__ __forceinline__ void unite(NodeBox& a, const NodeBox& b) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { a.lo[k] = fminf(a.lo[k], b.lo[k]); a.hi[k] = fmaxf(a.hi[k], b.hi[k]); }
+    a.depth = max(a.depth, b.depth);
+}
+
+__global__ void __launch_bounds__(256) lbvh_refit(const HostBox* __restrict__ boxes, const int* __restrict__ vals, int n,
+                                                  const int* __restrict__ left, const int* __restrict__ right,
+                                                  const int* __restrict__ parent_inner, const int* __restrict__ parent_leaf,
+                                                  int* __restrict__ flags, NodeBox* __restrict__ nbox,
+                                                  float4* __restrict__ nodes, int* __restrict__ order, int* __restrict__ root_depth) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    order[s] = vals[s];
+    int node = parent_leaf[s];
+    while (node >= 0) {
+        if (atomicAdd(&flags[node], 1) == 0) return;            // first to arrive: the sibling subtree is not ready
+        __threadfence();
+        NodeBox cb[2];
+        const int c[2] = { left[node], right[node] };
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            if (c[k] >= 0) cb[k] = nbox[c[k]];
+            else {
+                const HostBox b = boxes[vals[(~c[k]) >> 3]];
+                for (int a = 0; a < 3; ++a) { cb[k].lo[a] = b.lo[a]; cb[k].hi[a] = b.hi[a]; }
+                cb[k].depth = 0;
+            }
+        }
+        nodes[4 * node + 0] = make_float4(cb[0].lo[0], cb[0].lo[1], cb[0].lo[2], cb[0].hi[0]);
+        nodes[4 * node + 1] = make_float4(cb[0].hi[1], cb[0].hi[2], cb[1].lo[0], cb[1].lo[1]);
+        nodes[4 * node + 2] = make_float4(cb[1].lo[2], cb[1].hi[0], cb[1].hi[1], cb[1].hi[2]);
+        nodes[4 * node + 3] = make_float4(__int_as_float(c[0]), __int_as_float(c[1]), 0.0f, 0.0f);
+        unite(cb[0], cb[1]);
+        cb[0].depth += 1;
+        nbox[node] = cb[0];
+        __threadfence();
+        if (node == 0) *root_depth = cb[0].depth;
+        node = parent_inner[node];
+    }
+}
+
+}  // namespace
+
+cudaError_t build_lbvh_gpu(const HostBox* d_boxes, int n, float4* d_nodes, int* d_order, int* root_ref, int* depth, cudaStream_t st) {
+    if (n < 2) return cudaErrorInvalidValue;
+    cudaError_t e;
+    unsigned long long *keys = nullptr, *keys_sorted = nullptr;
+    int *vals = nullptr, *vals_sorted = nullptr, *ints = nullptr;
+    NodeBox* nbox = nullptr;
+    Bounds* bounds = nullptr;
+    void* tmp = nullptr;
+    size_t tmp_bytes = 0;
+    // ints: left | right | parent_inner | parent_leaf(n) | flags | root_depth
+    const size_t ni = size_t(n - 1) * 4 + size_t(n) + 1;
+    auto cleanup = [&]() {
+        cudaFree(keys); cudaFree(keys_sorted); cudaFree(vals); cudaFree(vals_sorted); cudaFree(ints); cudaFree(nbox); cudaFree(bounds); cudaFree(tmp);
+    };
+#define LB(call) do { e = (call); if (e != cudaSuccess) { cleanup(); return e; } } while (0)
+    LB(cudaMalloc(&keys, sizeof(*keys) * n)); LB(cudaMalloc(&keys_sorted, sizeof(*keys) * n));
+    LB(cudaMalloc(&vals, sizeof(int) * n)); LB(cudaMalloc(&vals_sorted, sizeof(int) * n));
+    LB(cudaMalloc(&ints, sizeof(int) * ni)); LB(cudaMalloc(&nbox, sizeof(NodeBox) * (n - 1))); LB(cudaMalloc(&bounds, sizeof(Bounds)));
+    LB(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys_sorted, vals, vals_sorted, n, 0, 63, st));
+    LB(cudaMalloc(&tmp, tmp_bytes ? tmp_bytes : 1));
+    int* left = ints; int* right = left + (n - 1); int* parent_inner = right + (n - 1); int* parent_leaf = parent_inner + (n - 1);
+    int* flags = parent_leaf + n; int* root_depth = flags + (n - 1);
+    LB(cudaMemsetAsync(flags, 0, sizeof(int) * size_t(n), st));          // flags + root_depth
+
+    const int nb = (n + 255) / 256;
+    lbvh_init_bounds<<<1, 32, 0, st>>>(bounds);
+    lbvh_centroid_bounds<<<min(nb, 1184), 256, 0, st>>>(d_boxes, n, bounds);
+    lbvh_morton<<<nb, 256, 0, st>>>(d_boxes, n, bounds, keys, vals);
+    LB(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys_sorted, vals, vals_sorted, n, 0, 63, st));
+    lbvh_hierarchy<<<(n - 1 + 255) / 256, 256, 0, st>>>(keys_sorted, n, left, right, parent_inner, parent_leaf);
+    lbvh_refit<<<nb, 256, 0, st>>>(d_boxes, vals_sorted, n, left, right, parent_inner, parent_leaf, flags, nbox, d_nodes, d_order, root_depth);
+    LB(cudaGetLastError());
+    int h_depth = 0;
+    LB(cudaMemcpyAsync(&h_depth, root_depth, sizeof(int), cudaMemcpyDeviceToHost, st));
+    LB(cudaStreamSynchronize(st));
+#undef LB
+    cleanup();
+    if (root_ref) *root_ref = 0;
+    if (depth) *depth = h_depth;
+    return cudaSuccess;
 }
 
 }  // namespace rt

@@ -60,9 +60,10 @@ def exchange_ipc_handles(handle, group=None):
     return out
 
 
-def render_sharded(ctx, cam, rank, world, precision, seed=0, slices=0):
-    """Render this rank's sample shard of `cam` (asynchronous); returns (begin, count)."""
+def render_sharded(ctx, cam, rank, world, precision, seed=0, slices=0, variant=1):
+    """Render this rank's sample shard of `cam` (asynchronous); returns (begin, count).
+    variant: 1 = SM-resident wavefront (default), 0 = warp-scheduled megakernel, 2 = lock-step megakernel."""
     begin, count = sample_shard(cam.samples_per_pixel, rank, world)
     if count > 0:
-        ctx.render(cam, precision=precision, seed=seed, sample_begin=begin, sample_count=count, slices=slices)
+        ctx.render(cam, precision=precision, seed=seed, sample_begin=begin, sample_count=count, slices=slices, variant=variant)
     return begin, count
