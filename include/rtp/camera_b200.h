@@ -1,0 +1,123 @@
+// camera_b200.h -- B200Impl::Camera, the drop-in for CPUImpl::Camera (src/camera_cpu.h:4-28).
+//
+//     CPUImpl::Camera cam;  ...fields...;  cam.render(world);          // reference, src/main.cpp:55-70
+//     B200Impl::Camera cam; ...fields...;  cam.render(world);          // this repository
+//
+// render() walks `world` into POD arrays (hittable::describe), hands them to librt_b200.so through
+// the C ABI (rt_upload_scene / rt_render / rt_readback, include/rt_b200.h) and writes the P3 stream the
+// reference prints (src/camera.h:35,45) to std::cout.  camera::render is non-virtual in the reference
+// (src/camera.h:32), so hiding it here is what a statically typed caller -- all that exist -- binds to.
+// Errors surface as std::runtime_error (the reference has no error path at all); there is no CPU
+// fallback: without a CUDA device rt_create fails and render() throws.
+#ifndef RTP_CAMERA_B200_H
+#define RTP_CAMERA_B200_H
+
+#include <string>
+
+#include "camera.h"
+
+namespace B200Impl {
+
+class Camera : public camera {
+  public:
+    // knobs the reference does not have
+    uint64_t seed = 0;                    // Philox key (the reference's global mt19937 has no seed knob)
+    int precision = RT_F32;               // RT_F64 = parity mode (bit-identical to the harness build of the reference)
+    int variant = RT_WAVEFRONT;           // RT_MEGAKERNEL | RT_WAVEFRONT | RT_MEGA_LOCKSTEP
+    int device = 0;
+    int bvh_builder = RT_BVH_SAH_HOST;    // RT_BVH_LBVH_GPU for large scenes
+
+    Camera() {}
+    Camera(const Camera&) = delete;
+    Camera& operator=(const Camera&) = delete;
+    ~Camera() override { if (ctx_) rt_destroy(ctx_); }
+
+    // camera::render(world), src/camera.h:32-50
+    void render(const hittable& world) {
+        initialize();
+        upload(world);
+        const rt_camera c = pod();
+        rt_render_opts o = {};
+        o.abi = RT_ABI_VERSION; o.precision = precision; o.variant = variant; o.seed = seed;
+        check(rt_render(ctx_, &c, &o), "rt_render");
+        std::string ppm(size_t(image_width) * size_t(image_height) * 12 + 64, '\0');
+        size_t len = ppm.size();
+        check(rt_readback(ctx_, samples_per_pixel, nullptr, nullptr, &ppm[0], &len), "rt_readback");
+        std::cout.write(ppm.data(), std::streamsize(len));
+        std::clog << "\rDone.                 \n";
+    }
+
+    // camera::get_ray(i, j), src/camera.h:87-100, on the device.  The reference draws from its global
+    // sequential generator; here successive calls walk the samples 0, 1, 2, ... of the keyed stream.
+    ray get_ray(int i, int j) const {
+        ensure_ctx();
+        const rt_camera c = pod();
+        const int32_t pi = i, pj = j;
+        const uint32_t s = next_sample_++;
+        rt_ray r;
+        check(rt_gen_rays(ctx_, &c, &pi, &pj, &s, 1, seed, precision, &r), "rt_gen_rays");
+        return ray(point3(r.orig[0], r.orig[1], r.orig[2]), vec3(r.dir[0], r.dir[1], r.dir[2]), r.tm);
+    }
+
+    // CPUImpl::Camera::ray_color, src/camera_cpu.h:8-26, for ONE ray: the bounce loop is driven from the
+    // host through the parity hooks (closest hit, then scatter, both on the device).  Meant for
+    // test-style calls (tests/tests.cpp:38-42); render() runs the whole loop inside one kernel.
+    color ray_color(const ray& r_in, int depth, const hittable& world) const override {
+        upload(world);
+        rt_ray r = to_pod(r_in);
+        color throughput(1, 1, 1);
+        for (int bounce = 1; depth > 0; --depth, ++bounce) {
+            rt_hit h;
+            check(rt_trace_closest(ctx_, &r, 1, 0.001, infinity, precision, RT_TRACE_BVH, &h), "rt_trace_closest");
+            if (h.prim < 0) {                                                 // sky, src/camera_cpu.h:23-25
+                const vec3 u = unit_vector(vec3(r.dir[0], r.dir[1], r.dir[2]));
+                const double a = 0.5 * (u.y() + 1.0);
+                return throughput * ((1.0 - a) * color(1.0, 1.0, 1.0) + a * color(0.5, 0.7, 1.0));
+            }
+            const rt_material m = scene_.materials[size_t(scene_.spheres[size_t(h.prim)].material)];
+            int32_t ok = 0; double att[3]; rt_ray out;
+            check(rt_scatter(ctx_, &m, &r, &h, 1, seed + uint64_t(bounce), precision, &ok, att, &out), "rt_scatter");
+            if (!ok) return color(0, 0, 0);
+            throughput = throughput * color(att[0], att[1], att[2]);
+            r = out;
+        }
+        return color(0, 0, 0);                                                // depth exhausted, :12-13
+    }
+
+    rt_stats stats() const { rt_stats s = {}; if (ctx_) rt_get_stats(ctx_, &s); return s; }
+
+  private:
+    mutable rt_ctx* ctx_ = nullptr;
+    mutable rt_scene_builder scene_;
+    mutable const hittable* uploaded_ = nullptr;
+    mutable size_t uploaded_count_ = 0;
+    mutable uint32_t next_sample_ = 0;
+
+    static rt_ray to_pod(const ray& r) {
+        rt_ray p;
+        for (int k = 0; k < 3; ++k) { p.orig[k] = r.origin()[k]; p.dir[k] = r.direction()[k]; }
+        p.tm = r.time();
+        return p;
+    }
+    void check(int rc, const char* what) const {
+        if (rc != RT_OK) throw std::runtime_error(std::string(what) + ": " + rt_last_error(ctx_));
+    }
+    void ensure_ctx() const {
+        if (!ctx_ && rt_create(&ctx_, device) != RT_OK) throw std::runtime_error(std::string("rt_create: ") + rt_last_error(nullptr));
+    }
+    void upload(const hittable& world) const {
+        ensure_ctx();
+        rt_scene_builder b;
+        world.describe(b);
+        if (uploaded_ == &world && uploaded_count_ == b.spheres.size()) return;   // same world as last time
+        rt_bvh_opts o = {};
+        o.abi = RT_ABI_VERSION; o.builder = bvh_builder;
+        check(rt_upload_scene(ctx_, b.spheres.data(), b.spheres.size(), b.materials.data(), b.materials.size(), &o), "rt_upload_scene");
+        scene_ = std::move(b);
+        uploaded_ = &world; uploaded_count_ = scene_.spheres.size();
+    }
+};
+
+}  // namespace B200Impl
+
+#endif  // RTP_CAMERA_B200_H

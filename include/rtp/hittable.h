@@ -1,0 +1,2 @@
+// hittable.h -- same name as the reference header (src/hittable.h); the API lives in scene_api.h
+#include "scene_api.h"

@@ -1,0 +1,2 @@
+// interval.h -- same name as the reference header (src/interval.h); the API lives in scene_api.h
+#include "scene_api.h"

@@ -1,0 +1,2 @@
+// material.h -- same name as the reference header (src/material.h); the API lives in scene_api.h
+#include "scene_api.h"

@@ -1,0 +1,2 @@
+// ray.h -- same name as the reference header (src/ray.h); the API lives in scene_api.h
+#include "scene_api.h"

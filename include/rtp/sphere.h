@@ -1,0 +1,2 @@
+// sphere.h -- same name as the reference header (src/sphere.h); the API lives in scene_api.h
+#include "scene_api.h"
