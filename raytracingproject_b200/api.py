@@ -2,7 +2,7 @@
 (reference src/camera.h, src/hittable_list.h, src/sphere.h, src/material.h) over the C ABI of
 librt_b200.so.  `cam.render(world)` keeps the reference's meaning -- P3 text on stdout
 (src/camera.h:32-50) -- and runs on the GPU.  Python is only the test/bench driver; the C++
-drop-in headers are under include/rtb200/.
+drop-in headers are under include/rtp/.
 """
 import ctypes as C
 import sys
@@ -143,6 +143,13 @@ class Context:
         else:
             self._ck(self._lib.rt_readback(self._h, spp_total, L.ptr(s), L.ptr(b), None, None))
         return dict(sum=s, rgb8=b, ppm=text)
+
+    def readback_into(self, spp_total, rgb8=None, ppm=None):
+        """rt_readback into caller-owned buffers (numpy uint8 arrays, e.g. over pinned host memory): no
+        allocation or extra copy per call.  Returns the length of the P3 text written to `ppm` (0 if None)."""
+        n = C.c_size_t(ppm.nbytes if ppm is not None else 0)
+        self._ck(self._lib.rt_readback(self._h, spp_total, None, L.ptr(rgb8), L.ptr(ppm), C.byref(n) if ppm is not None else None))
+        return n.value
 
     def synchronize(self):
         self._ck(self._lib.rt_synchronize(self._h))

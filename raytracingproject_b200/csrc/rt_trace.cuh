@@ -33,22 +33,26 @@ template <typename T> struct SceneView {
 };
 
 // Slab test, src/aabb.h:35-53 with 1/d hoisted.  Returns entry distance in tnear.
-// float rays: (plane - o) * inv keeps the error relative (2 ulp + 1 ulp of the approximate
-// reciprocal in inv), covered by the 1 + 2^-20 factor.
+// float rays: t = plane * inv + noi with noi = -(o * inv) hoisted per ray -- one FFMA per plane instead of
+// FADD + FMUL.  The price is an ABSOLUTE error of ~ulp(o * inv) on every t (plus 1 ulp relative from the
+// approximate reciprocal), so the test is made conservative with a relative factor AND a per-ray additive
+// slack `delta` = 2^-22 max|o * inv| (trav_setup, which also keeps inv finite: a zero direction component
+// switches its axis off through delta).  A box can only be accepted wrongly, never rejected wrongly, and
+// acceptance of a HIT is decided by the sphere tests alone.
 __device__ __forceinline__ bool slab(float lx, float ly, float lz, float hx, float hy, float hz,
-                                     const Vec<float>& o, const Vec<float>& inv, float tmin, float tmax, float& tnear) {
-    const float t0x = (lx - o.x) * inv.x, t1x = (hx - o.x) * inv.x;
-    const float t0y = (ly - o.y) * inv.y, t1y = (hy - o.y) * inv.y;
-    const float t0z = (lz - o.z) * inv.z, t1z = (hz - o.z) * inv.z;
+                                     const Vec<float>& noi, const Vec<float>& inv, float delta, float tmin, float tmax, float& tnear) {
+    const float t0x = fmaf(lx, inv.x, noi.x), t1x = fmaf(hx, inv.x, noi.x);
+    const float t0y = fmaf(ly, inv.y, noi.y), t1y = fmaf(hy, inv.y, noi.y);
+    const float t0z = fmaf(lz, inv.z, noi.z), t1z = fmaf(hz, inv.z, noi.z);
     const float tn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), tmin));
     const float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), tmax));
     tnear = tn;
-    return tn <= tf * 1.000001f;
+    return tn <= fmaf(tf, 1.000001f, delta);
 }
 // double rays against the float boxes (exactly representable in double): the boxes' outward
 // padding (>= 2^-20 relative) dwarfs double rounding.
 __device__ __forceinline__ bool slab(float lx, float ly, float lz, float hx, float hy, float hz,
-                                     const Vec<double>& o, const Vec<double>& inv, double tmin, double tmax, double& tnear) {
+                                     const Vec<double>& o, const Vec<double>& inv, double, double tmin, double tmax, double& tnear) {
     const double t0x = (double(lx) - o.x) * inv.x, t1x = (double(hx) - o.x) * inv.x;
     const double t0y = (double(ly) - o.y) * inv.y, t1y = (double(hy) - o.y) * inv.y;
     const double t0z = (double(lz) - o.z) * inv.z, t1z = (double(hz) - o.z) * inv.z;
@@ -75,6 +79,8 @@ __device__ __forceinline__ bool leaf_sphere(const double4& a, const double4& b, 
 //   cur >= 0: inner node to visit; cur < 0 and != RT_SENTINEL: leaf to test; RT_SENTINEL: finished.
 template <typename T> struct Trav {
     Vec<T> inv;              // 1 / direction
+    Vec<T> org;              // fast mode: -(origin * inv), the additive term of the FMA slab test; parity mode: origin
+    T delta;                 // fast mode: additive slack of the slab test; parity mode: unused
     T qa;                    // fast mode: 1 / |d|^2; parity mode: |d|^2 (what each sphere test wants)
     T tbest;
     int best_id, best_slot;  // list index (tie rule) and slot (tree slot, or n_slots + k for big sphere k)
@@ -110,6 +116,19 @@ __device__ __forceinline__ void trav_setup(const SceneView<T>& sv, const Ray<T>&
     const T a_len2 = len2(r.d);
     tv.qa = sizeof(T) == 4 ? T(1) / a_len2 : a_len2;
     tv.inv = mk<T>(T(1) / r.d.x, T(1) / r.d.y, T(1) / r.d.z);
+    if (sizeof(T) == 4) {
+        // keep the reciprocals finite: with +-inf the FMA form gives plane * inf - o * inf = NaN or an infinity
+        // whose sign depends on the plane alone.  At 1e18 the axis is effectively switched off through delta
+        // (boxes are accepted conservatively, as the NaN-dropping min/max of the reference's form would)
+        const float big = 1e18f;
+        if (!(fabsf(float(tv.inv.x)) <= big)) tv.inv.x = T(copysignf(big, float(r.d.x)));
+        if (!(fabsf(float(tv.inv.y)) <= big)) tv.inv.y = T(copysignf(big, float(r.d.y)));
+        if (!(fabsf(float(tv.inv.z)) <= big)) tv.inv.z = T(copysignf(big, float(r.d.z)));
+        tv.org = mk<T>(-(r.o.x * tv.inv.x), -(r.o.y * tv.inv.y), -(r.o.z * tv.inv.z));
+        tv.delta = T(2.384185791015625e-07) * T(fmaxf(fmaxf(fabsf(float(tv.org.x)), fabsf(float(tv.org.y))), fabsf(float(tv.org.z))));
+    } else {
+        tv.org = r.o; tv.delta = T(0);
+    }
     tv.cur = sv.root_ref; tv.sp = 0;
 }
 
@@ -125,8 +144,8 @@ __device__ __forceinline__ void trav_node(const float4* __restrict__ nodes, cons
     const int cur = tv.cur;
     const float4 q0 = nodes[4 * cur + 0], q1 = nodes[4 * cur + 1], q2 = nodes[4 * cur + 2], q3 = nodes[4 * cur + 3];
     T tl, tr;
-    const bool hl = slab(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, r.o, tv.inv, tmin, tv.tbest, tl);
-    const bool hr = slab(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, r.o, tv.inv, tmin, tv.tbest, tr);
+    const bool hl = slab(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, tv.org, tv.inv, tv.delta, tmin, tv.tbest, tl);
+    const bool hr = slab(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, tv.org, tv.inv, tv.delta, tmin, tv.tbest, tr);
     const int cl = __float_as_int(q3.x), cr = __float_as_int(q3.y);
     if (hl && hr) {
         const bool left_first = tl <= tr;

@@ -152,7 +152,7 @@ render_pool_kernel(const RenderParams<T> p) {
             {
                 int head = 0, pid = 0;
                 Ray<T> ray; ray.o = mk<T>(0, 0, 0); ray.d = mk<T>(0, 0, 1); ray.tm = 0;
-                Trav<T> tv; tv.cur = RT_SENTINEL; tv.sp = 0; tv.tbest = 0; tv.best_id = -1; tv.best_slot = -1; tv.qa = 1; tv.inv = mk<T>(0, 0, 0);
+                Trav<T> tv; tv.cur = RT_SENTINEL; tv.sp = 0; tv.tbest = 0; tv.best_id = -1; tv.best_slot = -1; tv.qa = 1; tv.inv = mk<T>(0, 0, 0); tv.org = mk<T>(0, 0, 0); tv.delta = 0;
                 for (;;) {
                     const bool isN = tv.cur >= 0;
                     const bool isP = tv.cur == RT_SENTINEL;
@@ -186,15 +186,15 @@ render_pool_kernel(const RenderParams<T> p) {
                             if (tv.cur == RT_SENTINEL) { F[L::TBEST * P + pid] = tv.tbest; I[L::BEST * P + pid] = tv.best_slot; }
                         }
                     } else {
-                        // node visits, repeated while most of the lanes that started them still have a node
+                        // node visits, two per head count, repeated while most of the lanes that started them
+                        // still have a node; a lane whose walk ends hands in its result after the loop
                         int now;
                         do {
-                            if (tv.cur >= 0) {
-                                trav_node<T>(st.nodes, ray, T(0.001), tv, stack);
-                                if (tv.cur == RT_SENTINEL) { F[L::TBEST * P + pid] = tv.tbest; I[L::BEST * P + pid] = tv.best_slot; }
-                            }
+                            if (tv.cur >= 0) trav_node<T>(st.nodes, ray, T(0.001), tv, stack);
+                            if (tv.cur >= 0) trav_node<T>(st.nodes, ray, T(0.001), tv, stack);
                             now = __popc(__ballot_sync(FULL, tv.cur >= 0));
                         } while (now > 0 && now * 8 >= nN * th_n);
+                        if (isN && tv.cur == RT_SENTINEL) { F[L::TBEST * P + pid] = tv.tbest; I[L::BEST * P + pid] = tv.best_slot; }
                     }
                 }
             }

@@ -6,7 +6,7 @@ txt = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-so
 rows, fname, hdr = [], None, None
 for r in csv.reader(io.StringIO(txt)):
     if not r: continue
-    if r[0] == "File Name": fname = r[1].split("/")[-1]; continue
+    if r[0] in ("File Name", "File Path"): fname = r[1].split("/")[-1]; continue
     if r[0] == "Line No": hdr = r; continue
     if hdr is None or r[0] == "" or not r[0].isdigit(): continue
     d = dict(zip(hdr[4:], r[4:]))
@@ -19,3 +19,16 @@ print(f"total warp-inst {tot_i:.4g} thread-inst {tot_t:.4g} avg threads {tot_t/m
 rows.sort(reverse=True)
 for inst, thr, smp, f, ln, src in rows[:top]:
     print(f"{100*inst/tot_i:5.1f}% inst {100*smp/max(tot_s,1):5.1f}% smp  thr/inst {thr/max(inst,1):5.1f}  {f}:{ln}  {src}")
+# optional: group by named line ranges  CATS="name:file:lo-hi,..."
+import os
+cats = os.environ.get("CATS")
+if cats:
+    agg = {}
+    for spec in cats.split(","):
+        name, f, rng = spec.split(":"); lo, hi = map(int, rng.split("-"))
+        for inst, thr, smp, ff, ln, src in rows:
+            if ff == f and lo <= ln <= hi:
+                a = agg.setdefault(name, [0, 0, 0]); a[0] += inst; a[1] += thr; a[2] += smp
+    print("--- categories")
+    for name, (i, t, sm) in agg.items():
+        print(f"{name:24s} {100*i/tot_i:5.1f}% inst  {100*sm/max(tot_s,1):5.1f}% smp  thr/inst {t/max(i,1):5.1f}")
