@@ -147,17 +147,14 @@ __device__ __forceinline__ void trav_node(const float4* __restrict__ nodes, cons
     const bool hl = slab(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, tv.org, tv.inv, tv.delta, tmin, tv.tbest, tl);
     const bool hr = slab(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, tv.org, tv.inv, tv.delta, tmin, tv.tbest, tr);
     const int cl = __float_as_int(q3.x), cr = __float_as_int(q3.y);
-    if (hl && hr) {
-        const bool left_first = tl <= tr;
-        tv.cur = left_first ? cl : cr;
-        if (tv.sp < RT_STACK) stack[tv.sp++] = left_first ? cr : cl;
-    } else if (hl) {
-        tv.cur = cl;
-    } else if (hr) {
-        tv.cur = cr;
-    } else {
-        tv.cur = tv.sp > 0 ? stack[--tv.sp] : RT_SENTINEL;
-    }
+    // near child next, far child pushed, nothing hit -> pop: written with selects and two short predicated
+    // blocks instead of a four-way branch, so the lanes of a warp stay together through the step
+    const bool left_first = !hr || (hl && tl <= tr);
+    const int near = left_first ? cl : cr, far = left_first ? cr : cl;
+    if (hl && hr && tv.sp < RT_STACK) stack[tv.sp++] = far;
+    int next = near;
+    if (!(hl || hr)) next = tv.sp > 0 ? stack[--tv.sp] : RT_SENTINEL;
+    tv.cur = next;
 }
 
 // one leaf: its 1..8 sphere slots
