@@ -53,6 +53,9 @@ template <> cudaError_t launch_render_pool<RT_REAL>(const RenderParams<RT_REAL>&
     RT_POOL_CASE(2, 128, 640);
     RT_POOL_CASE(3, 64, 768);
     RT_POOL_CASE(4, 128, 704);
+    RT_POOL_CASE(5, 96, 768);
+    RT_POOL_CASE(6, 96, 896);
+    RT_POOL_CASE(7, 64, 1024);
     default: RT_POOL_CASE(0, 128, 256);
     }
 #undef RT_POOL_CASE

@@ -44,9 +44,9 @@ template <typename T> __host__ __device__ inline size_t staged_bytes_aligned(int
 }
 
 // SM-resident wavefront (rt_wavefront.cuh): pool of P paths per warp, one CTA of BLOCK threads per SM
-#define RT_POOL_SHAPES 5
+#define RT_POOL_SHAPES 8
 inline void pool_shape(int shape, int* paths, int* block) {
-    const int P[RT_POOL_SHAPES] = { 128, 128, 128, 64, 128 }, B[RT_POOL_SHAPES] = { 256, 512, 640, 768, 704 };
+    const int P[RT_POOL_SHAPES] = { 128, 128, 128, 64, 128, 96, 96, 64 }, B[RT_POOL_SHAPES] = { 256, 512, 640, 768, 704, 768, 896, 1024 };
     if (shape < 0 || shape >= RT_POOL_SHAPES) shape = 0;
     *paths = P[shape]; *block = B[shape];
 }
