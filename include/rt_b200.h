@@ -203,6 +203,18 @@ int rt_bench_closest(rt_ctx *ctx, const rt_camera *cam, size_t n, uint64_t seed,
 int rt_write_color(rt_ctx *ctx, const double *sums_rgb, size_t n, int samples_per_pixel, uint8_t *rgb8);
 int rt_encode_p3(rt_ctx *ctx, const uint8_t *rgb8, int width, int height, char *ppm, size_t *ppm_len);
 
+/* ---- next row 8f-3: the demo's compute shader as a CUDA kernel ---------------------------------- */
+
+/* `Sphere` of the windowed demo, src/common_objects.h:17-22 (glm::vec3 center; float radius; glm::vec4 color) */
+typedef struct { float center[3]; float radius; float color[4]; } rt_demo_sphere;
+
+/* assets/shaders/ray_tracing.comp:35-73 for every pixel of a width x height rgba8 image (host buffer,
+ * 4 bytes per pixel, row-major from y = 0): pinhole ray against the spheres by the sign of the
+ * discriminant, flat colour, background (0.5, 0, 0.25, 1).  spheres == NULL: the sphere the shader
+ * hard-codes (:49-52).  Headless: replaces imageStore into the swapchain-bound storage image and the
+ * vkCmdDispatch of src/vulkan/command_buffers.cpp:143-158 (graphics API: unavailable on this box). */
+int rt_demo_compute(rt_ctx *ctx, const rt_demo_sphere *spheres, size_t n, int width, int height, uint8_t *rgba8);
+
 /* Host SAH builder on its own (no device needed): nodes_out receives 16 floats per inner node
  * (layout in DESIGN.md), order_out the slot -> sphere index permutation.  Capacity: n-1 nodes, n slots. */
 int rt_build_bvh_host(const rt_sphere *spheres, size_t n, int max_leaf, float *nodes_out, int32_t *order_out,

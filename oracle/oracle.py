@@ -18,6 +18,8 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_ORACLE = os.path.join(HERE, "liboracle.so")
 LIB_REF = os.path.join(HERE, "_ref", "libref_harness.so")
+LIB_REF_GLSL = os.path.join(HERE, "_ref", "libref_glsl.so")
+DEMO_SPHERE = np.dtype([("center", "f4", 3), ("radius", "f4"), ("color", "f4", 4)])    # src/common_objects.h:17-22
 
 RNG_MT19937, RNG_PHILOX = 0, 1
 LAMBERTIAN, METAL, DIELECTRIC = 0, 1, 2
@@ -53,7 +55,9 @@ def build(force=False):
                                            for f in ("rt_oracle.c", "rt_oracle.h")))
     need_ref = os.path.isdir("/root/reference/src") and (
         force or not os.path.exists(LIB_REF) or
-        os.path.getmtime(LIB_REF) < os.path.getmtime(os.path.join(HERE, "ref_harness.cpp")))
+        os.path.getmtime(LIB_REF) < os.path.getmtime(os.path.join(HERE, "ref_harness.cpp")) or
+        not os.path.exists(LIB_REF_GLSL) or
+        os.path.getmtime(LIB_REF_GLSL) < os.path.getmtime(os.path.join(HERE, "glsl_harness.cpp")))
     if need or need_ref:
         subprocess.run(["make", "-C", HERE, "all"], check=True, capture_output=True)
 
@@ -97,6 +101,8 @@ def oracle():
         L.ob_get_rays.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_uint64, C.c_void_p]
         L.ob_pixel_match.argtypes = [C.c_void_p]
         L.ob_write_color.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_void_p]
+        L.o_demo_hit.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float]
+        L.o_demo_compute.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p]
         _oracle = L
     return _oracle
 
@@ -287,3 +293,47 @@ def philox(ctr, key):
     out = np.zeros(4, "u4")
     oracle().o_philox4x32_10(_p(ctr), _p(key), _p(out))
     return out
+
+
+# ---------------------------------------------- 8f-3: the demo's compute shader --
+_ref_glsl = None
+
+
+def have_ref_glsl():
+    build()
+    return os.path.exists(LIB_REF_GLSL)
+
+
+def ref_glsl():
+    """assets/shaders/ray_tracing.comp compiled as C++ (oracle/glsl_harness.cpp)."""
+    global _ref_glsl
+    if _ref_glsl is None:
+        build()
+        L = C.CDLL(LIB_REF_GLSL)
+        L.ref_demo_compute.argtypes = [C.c_int, C.c_int, C.c_void_p]
+        L.ref_demo_hit.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float]
+        _ref_glsl = L
+    return _ref_glsl
+
+
+def demo_compute(width, height, spheres=None, impl="oracle"):
+    """rgba8 image (height, width, 4) of the demo's compute stage; impl="ref" runs the shader itself
+    (hard-coded sphere only)."""
+    img = np.zeros((height, width, 4), np.uint8)
+    if impl == "ref":
+        assert spheres is None
+        ref_glsl().ref_demo_compute(width, height, _p(img))
+    else:
+        s = None if spheres is None else np.ascontiguousarray(spheres, DEMO_SPHERE)
+        if s is not None and len(s) == 0:
+            s = np.zeros(1, DEMO_SPHERE)[:0]
+        keep = np.zeros(1, DEMO_SPHERE) if s is not None and len(s) == 0 else s     # a non-NULL pointer for an empty list
+        oracle().o_demo_compute(None if s is None else _p(keep), 0 if s is None else len(s), width, height, _p(img))
+    return img
+
+
+def demo_hit(origins, directions, centers, radii, impl="oracle"):
+    """hit() of the shader (:65-73) on n rays x their spheres -> bool array"""
+    o = np.ascontiguousarray(origins, "f4"); d = np.ascontiguousarray(directions, "f4"); c = np.ascontiguousarray(centers, "f4")
+    fn = ref_glsl().ref_demo_hit if impl == "ref" else oracle().o_demo_hit
+    return np.array([bool(fn(_p(o[k]), _p(d[k]), _p(c[k]), float(radii[k]))) for k in range(len(o))])

@@ -717,3 +717,44 @@ void ob_pixel_match(double out[3]) {
 void ob_write_color(const double *sums, size_t n, int spp, uint8_t *rgb) {
     for (size_t i = 0; i < n; ++i) o_write_color(v3(sums[3 * i], sums[3 * i + 1], sums[3 * i + 2]), spp, rgb + 3 * i);
 }
+
+/* ---- the windowed demo's compute shader -------------------------------------------
+ * assets/shaders/ray_tracing.comp:35-73, float arithmetic, one rounding per operation.  The shader
+ * hard-codes one sphere (:49-52); here the `if (hit) pixel_color = sphere.color` statement (:61-63) runs
+ * once per sphere of a list laid out as src/common_objects.h:17-22, in list order (the last sphere hit
+ * gives the colour -- the shader has no depth test).  Pinned against the shader itself compiled as
+ * C++ (oracle/_ref/libref_glsl.so) in tests/test_demo_shader.py. */
+static float demo_dot(const float a[3], const float b[3]) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
+
+int o_demo_hit(const float origin[3], const float direction[3], const float center[3], float radius) {   /* :65-73 */
+    float oc[3] = { origin[0] - center[0], origin[1] - center[1], origin[2] - center[2] };
+    float a = demo_dot(direction, direction);
+    float b = 2.0f * demo_dot(direction, oc);
+    float c = demo_dot(oc, oc) - radius * radius;
+    float discriminant = b * b - 4.0f * a * c;
+    return discriminant > 0;
+}
+
+static uint8_t demo_unorm8(float v) {
+    v = v < 0.0f ? 0.0f : (v > 1.0f ? 1.0f : v);
+    return (uint8_t)nearbyintf(v * 255.0f);
+}
+
+void o_demo_compute(const o_demo_sphere *spheres, size_t n, int width, int height, uint8_t *rgba8) {
+    static const o_demo_sphere hard_coded = { {3.0f, 0.0f, 0.0f}, 1.0f, {1.0f, 0.3f, 0.7f, 1.0f} };        /* :49-52 */
+    const float position[3] = {0.0f, 0.0f, 0.0f}, forwards[3] = {0.0f, 0.0f, 1.0f}, right[3] = {1.0f, 0.0f, 0.0f}, up[3] = {0.0f, 1.0f, 0.0f};
+    if (!spheres) { spheres = &hard_coded; n = 1; }
+    for (int y = 0; y < height; ++y)
+        for (int x = 0; x < width; ++x) {
+            float hc = ((float)x * 2 - width) / width;                 /* :38 */
+            float vc = ((float)y * 2 - height) / width;                /* :39 (divided by the width too) */
+            float color[4] = {0.5f, 0.0f, 0.25f, 1.0f};                /* :41 */
+            float dir[3];
+            for (int k = 0; k < 3; ++k) dir[k] = forwards[k] + hc * right[k] + vc * up[k];       /* :57 */
+            for (size_t s = 0; s < n; ++s)
+                if (o_demo_hit(position, dir, spheres[s].center, spheres[s].radius))
+                    for (int k = 0; k < 4; ++k) color[k] = spheres[s].color[k];
+            uint8_t *t = rgba8 + ((size_t)y * width + x) * 4;
+            for (int k = 0; k < 4; ++k) t[k] = demo_unorm8(color[k]);
+        }
+}

@@ -163,6 +163,11 @@ size_t o_scene_rtiow(int g, double p_diffuse, double p_metal, uint32_t mt_seed,
                      o_sphere *s, o_material *m, size_t cap, uint64_t *draws_out /* nullable */);
 void   o_camera_rtiow(o_camera *c, int image_width, int spp, int max_depth); /* src/main.cpp:57-68 */
 
+/* assets/shaders/ray_tracing.comp restated (see rt_oracle.c) */
+typedef struct { float center[3]; float radius; float color[4]; } o_demo_sphere;   /* src/common_objects.h:17-22 */
+int    o_demo_hit(const float origin[3], const float direction[3], const float center[3], float radius);
+void   o_demo_compute(const o_demo_sphere *spheres /* NULL: the shader's own */, size_t n, int width, int height, uint8_t *rgba8);
+
 #ifdef __cplusplus
 }
 #endif

@@ -18,6 +18,7 @@ LAMBERTIAN, METAL, DIELECTRIC = 0, 1, 2
 # numpy mirrors of the POD structs (layouts asserted in rt_api.cu)
 SPHERE = np.dtype([("center1", "f8", 3), ("center_vec", "f8", 3), ("radius", "f8"),
                    ("is_moving", "i4"), ("material", "i4")])
+DEMO_SPHERE = np.dtype([("center", "f4", 3), ("radius", "f4"), ("color", "f4", 4)])    # rt_demo_sphere
 MATERIAL = np.dtype([("type", "i4"), ("pad", "i4"), ("albedo", "f8", 3), ("param", "f8")])
 RAY = np.dtype([("orig", "f8", 3), ("dir", "f8", 3), ("tm", "f8")])
 HIT = np.dtype([("p", "f8", 3), ("normal", "f8", 3), ("t", "f8"), ("front_face", "i4"), ("prim", "i4")])
@@ -75,6 +76,7 @@ SYMBOLS = {
     "rt_bench_closest": (_I, [_VP, _VP, _SZ, _U64, _I, _I, _I, _VP, _VP, _VP, _VP, _SZ]),
     "rt_write_color": (_I, [_VP, _VP, _SZ, _I, _VP]),
     "rt_encode_p3": (_I, [_VP, _VP, _I, _I, _VP, _VP]),
+    "rt_demo_compute": (_I, [_VP, _VP, _SZ, _I, _I, _VP]),
     "rt_build_bvh_host": (_I, [_VP, _SZ, _I, _VP, _VP, _VP, _VP, _VP]),
     "rt_scene_rtiow": (_SZ, [_I, _D, _D, C.c_uint32, _VP, _VP, _SZ]),
     "rt_camera_rtiow": (_I, [_VP, _I, _I, _I, _D]),

@@ -151,6 +151,15 @@ class Context:
         self._ck(self._lib.rt_readback(self._h, spp_total, None, L.ptr(rgb8), L.ptr(ppm), C.byref(n) if ppm is not None else None))
         return n.value
 
+    def demo_compute(self, width=1024, height=768, spheres=None):
+        """The windowed demo's compute stage (reference assets/shaders/ray_tracing.comp:35-73; default size
+        src/common_objects.h:8-9) into a headless (height, width, 4) rgba8 image.  spheres: DEMO_SPHERE
+        array, or None for the sphere the shader hard-codes."""
+        img = np.zeros((height, width, 4), np.uint8)
+        s = None if spheres is None else np.ascontiguousarray(spheres, L.DEMO_SPHERE)
+        self._ck(self._lib.rt_demo_compute(self._h, L.ptr(s), 0 if s is None else len(s), width, height, L.ptr(img)))
+        return img
+
     def synchronize(self):
         self._ck(self._lib.rt_synchronize(self._h))
 

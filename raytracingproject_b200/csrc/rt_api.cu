@@ -13,6 +13,7 @@
 #include <vector>
 
 #include "rt_bvh_host.h"
+#include "rt_demo.h"
 #include "rt_frame.h"
 #include "rt_kernels.cuh"
 #include "rt_lbvh.h"
@@ -810,6 +811,24 @@ extern "C" int rt_encode_p3(rt_ctx* ctx, const uint8_t* rgb8, int width, int hei
     d_b.release(); d_s.release(); d_o.release(); d_t.release();
     if (e != cudaSuccess) return cuda_fail(ctx, e, "rt_encode_p3");
     return rc;
+}
+
+extern "C" int rt_demo_compute(rt_ctx* ctx, const rt_demo_sphere* spheres, size_t n, int width, int height, uint8_t* rgba8) {
+    static_assert(sizeof(rt_demo_sphere) == sizeof(DemoSphere), "rt_demo_sphere layout");
+    if (!ctx || !rgba8 || width < 1 || height < 1 || (long long)width * height > (1ll << 30)) return RT_E_INVALID;
+    CK(cudaSetDevice(ctx->device));
+    const rt_demo_sphere hard_coded = { { 3.0f, 0.0f, 0.0f }, 1.0f, { 1.0f, 0.3f, 0.7f, 1.0f } };   // ray_tracing.comp:49-52
+    if (!spheres) { spheres = &hard_coded; n = 1; }
+    const size_t bytes = size_t(width) * height * 4;
+    DevBuf<DemoSphere> d_s; DevBuf<unsigned char> d_img;
+    CK(d_s.resize(std::max<size_t>(1, n))); CK(d_img.resize(bytes));
+    cudaError_t e = n ? cudaMemcpyAsync(d_s.p, spheres, n * sizeof(DemoSphere), cudaMemcpyHostToDevice, ctx->stream) : cudaSuccess;
+    if (e == cudaSuccess) e = launch_demo_compute(d_s.p, int(n), width, height, d_img.p, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(rgba8, d_img.p, bytes, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    d_s.release(); d_img.release();
+    if (e != cudaSuccess) return cuda_fail(ctx, e, "rt_demo_compute");
+    return RT_OK;
 }
 
 extern "C" int rt_build_bvh_host(const rt_sphere* spheres, size_t n, int max_leaf, float* nodes_out, int32_t* order_out,

@@ -63,3 +63,19 @@ gr, _ = O.get_rays(cam, pi, pj, sm, seed=5, impl="ref")
 np.savez_compressed(os.path.join(OUT, "ref_get_rays.npz"), px_i=pi, px_j=pj, sample=sm, rays=gr)
 for f in sorted(os.listdir(OUT)):
     print(f, os.path.getsize(os.path.join(OUT, f)))
+
+# 8f-3: the demo's compute shader itself (compiled as C++, oracle/glsl_harness.cpp): a small image whole,
+# the settings-size image (src/common_objects.h:8-9) by its sha256, and hit() on random rays / spheres
+import hashlib
+small = O.demo_compute(160, 120, impl="ref")
+full = O.demo_compute(1024, 768, impl="ref")
+rg = np.random.default_rng(11)
+n = 4096
+org = (rg.standard_normal((n, 3)) * 0.5).astype("f4")
+dirs = rg.standard_normal((n, 3)).astype("f4")
+cen = (rg.standard_normal((n, 3)) * 3).astype("f4")
+rad = rg.uniform(0.2, 2.5, n).astype("f4")
+flag = O.demo_hit(org, dirs, cen, rad, impl="ref")
+np.savez_compressed(os.path.join(OUT, "ref_demo_shader.npz"), small=small, full_sha256=np.frombuffer(hashlib.sha256(full.tobytes()).digest(), np.uint8),
+                    full_hit_pixels=np.int64((full[..., 0] == 255).sum()), origins=org, directions=dirs, centers=cen, radii=rad, hit=flag)
+print("demo shader:", small.shape, int((full[..., 0] == 255).sum()), "hit pixels at 1024x768;", int(flag.sum()), "of", n, "random rays hit")
