@@ -1,6 +1,7 @@
 // final_scene.cpp -- a caller written against the reference's API (the program of src/main.cpp:11-71,
 // restated): the only B200-specific lines are the camera type and the optional knobs read from argv.
-//   usage: final_scene [image_width spp max_depth [f32|f64]]  > image.ppm
+//   usage: final_scene [image_width spp max_depth [f32|f64 [p3|p6|pfm [passes]]]]  > image.ppm
+//          (passes > 1: the samples are rendered in that many progressive passes with a preview after each)
 //          final_scene --dump-scene > scene.bin      (the exported POD arrays, no GPU needed; used by tests)
 #include <cstdlib>
 #include <cstring>
@@ -66,6 +67,23 @@ int main(int argc, char** argv) {
     cam.focus_dist = 10.0;
     if (argc > 4 && !std::strcmp(argv[4], "f64")) cam.precision = RT_F64;
 
-    cam.render(world);
+    if (argc > 5 && !std::strcmp(argv[5], "p6")) cam.output_format = RT_IMG_P6;
+    if (argc > 5 && !std::strcmp(argv[5], "pfm")) cam.output_format = RT_IMG_PFM;
+    const int passes = argc > 6 ? std::atoi(argv[6]) : 1;
+    if (passes <= 1) {
+        cam.render(world);
+        return 0;
+    }
+    // progressive: equal sample ranges into one buffer, the frame so far resolved on the device after each
+    for (int k = 0, first = 0; k < passes; ++k) {
+        const int count = (cam.samples_per_pixel * (k + 1)) / passes - first;
+        if (count <= 0) continue;
+        cam.render_pass(world, first, count);
+        first += count;
+        cam.preview();
+        std::clog << "\rSamples so far: " << first << ' ' << std::flush;
+    }
+    cam.write_image(std::cout, cam.samples_per_pixel);
+    std::clog << "\rDone.                 \n";
     return 0;
 }

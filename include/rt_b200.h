@@ -156,6 +156,26 @@ int rt_render(rt_ctx *ctx, const rt_camera *cam, const rt_render_opts *opts);
  * spp_total = divisor used by write_color (0 = samples rendered into the buffer so far). */
 int rt_readback(rt_ctx *ctx, int spp_total, double *sum_rgb, uint8_t *rgb8, char *ppm, size_t *ppm_len);
 
+/* ---- next row 8f-2: output formats next to P3, progressive preview ------------------------------ *
+ * Progressive accumulation itself is rt_render with accumulate = 1 over further sample ranges
+ * (sample_begin / sample_count): the streams are keyed by (pixel, sample), so any split of [0, spp)
+ * into passes sums the same samples.  These two read the buffer between passes. */
+enum { RT_IMG_P3 = 0,      /* the text camera::render prints (src/camera.h:35, src/color.h:32-34) */
+       RT_IMG_P6 = 1,      /* "P6\nW H\n255\n" + the same write_color bytes, 3 per pixel */
+       RT_IMG_PFM = 2 };   /* "PF\nW H\n-1.0\n" + float32 mean radiance (pixel_color / spp, src/color.h:20-23,
+                              before gamma and clamp), little endian, rows bottom to top */
+
+/* write_color for every pixel in one of the formats above.  buf == NULL: *len = bytes needed.
+ * Otherwise *len in = capacity, out = bytes written.  Synchronises. */
+int rt_readback_image(rt_ctx *ctx, int spp_total, int format, void *buf, size_t *len);
+
+/* The frame as write_color bytes + alpha 255 (4 bytes per pixel, row-major) in a DEVICE buffer the
+ * context owns: the compute-side substitute for the image start_interactive_loop would present
+ * (src/graphical_environment.h:31; window and swapchain: unavailable on this box).  Asynchronous
+ * on the context's stream unless host_rgba8 (optional, W*H*4 bytes) is given.  *dev_rgba8 stays
+ * valid until the next rt_preview with another image size, or rt_destroy. */
+int rt_preview(rt_ctx *ctx, int spp_total, void **dev_rgba8, uint8_t *host_rgba8);
+
 int rt_image_size(const rt_camera *cam, int *width, int *height);   /* src/camera.h:53-54 */
 int rt_synchronize(rt_ctx *ctx);
 int rt_get_stats(rt_ctx *ctx, rt_stats *out);

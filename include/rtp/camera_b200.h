@@ -26,6 +26,7 @@ class Camera : public camera {
     int variant = RT_WAVEFRONT;           // RT_MEGAKERNEL | RT_WAVEFRONT | RT_MEGA_LOCKSTEP
     int device = 0;
     int bvh_builder = RT_BVH_SAH_HOST;    // RT_BVH_LBVH_GPU for large scenes
+    int output_format = RT_IMG_P3;        // RT_IMG_P6 / RT_IMG_PFM: binary image on std::cout instead of the P3 text
 
     Camera() {}
     Camera(const Camera&) = delete;
@@ -40,11 +41,35 @@ class Camera : public camera {
         rt_render_opts o = {};
         o.abi = RT_ABI_VERSION; o.precision = precision; o.variant = variant; o.seed = seed;
         check(rt_render(ctx_, &c, &o), "rt_render");
-        std::string ppm(size_t(image_width) * size_t(image_height) * 12 + 64, '\0');
-        size_t len = ppm.size();
-        check(rt_readback(ctx_, samples_per_pixel, nullptr, nullptr, &ppm[0], &len), "rt_readback");
-        std::cout.write(ppm.data(), std::streamsize(len));
+        write_image(std::cout, samples_per_pixel);
         std::clog << "\rDone.                 \n";
+    }
+
+    // Progressive use (the compute-side stand-in for start_interactive_loop,
+    // src/graphical_environment.h:31): render samples [first, first + count) into the accumulation buffer
+    // (first == 0 starts a new frame), then look at the frame so far -- preview() resolves it into a
+    // device rgba8 buffer (and optionally a host copy), write_image() streams it in output_format.
+    void render_pass(const hittable& world, int first, int count) {
+        initialize();
+        upload(world);
+        const rt_camera c = pod();
+        rt_render_opts o = {};
+        o.abi = RT_ABI_VERSION; o.precision = precision; o.variant = variant; o.seed = seed;
+        o.sample_begin = first; o.sample_count = count; o.accumulate = first > 0;
+        check(rt_render(ctx_, &c, &o), "rt_render");
+    }
+    void* preview(uint8_t* host_rgba8 = nullptr) const {
+        void* dev = nullptr;
+        check(rt_preview(ctx_, 0, &dev, host_rgba8), "rt_preview");
+        return dev;
+    }
+    void write_image(std::ostream& out, int spp_total = 0) const {
+        size_t len = 0;
+        if (output_format == RT_IMG_P3) len = size_t(image_width) * size_t(image_height) * 12 + 64;
+        else check(rt_readback_image(ctx_, spp_total, output_format, nullptr, &len), "rt_readback_image");
+        std::string buf(len, '\0');
+        check(rt_readback_image(ctx_, spp_total, output_format, &buf[0], &len), "rt_readback_image");
+        out.write(buf.data(), std::streamsize(len));
     }
 
     // camera::get_ray(i, j), src/camera.h:87-100, on the device.  The reference draws from its global

@@ -218,6 +218,20 @@ def ppm_p3(rgb8):
     return buf.raw[:n]
 
 
+def ppm_p6(rgb8):
+    """binary PPM of the write_color bytes"""
+    h, w = rgb8.shape[:2]
+    return b"P6\n%d %d\n255\n" % (w, h) + np.ascontiguousarray(rgb8, np.uint8).tobytes()
+
+
+def pfm(sums, spp):
+    """PFM of the mean radiance pixel_color * (1.0 / spp) (src/color.h:20-23, before gamma): float32 little
+    endian, rows bottom to top"""
+    h, w = sums.shape[:2]
+    mean = (np.asarray(sums, np.float64) * (1.0 / spp)).astype("<f4")
+    return b"PF\n%d %d\n-1.0\n" % (w, h) + np.ascontiguousarray(mean[::-1]).tobytes()
+
+
 def closest_hit(spheres, rays, tmin=0.001, tmax=np.inf, impl="oracle", use_bvh=False):
     spheres = np.ascontiguousarray(spheres)
     rays = np.ascontiguousarray(rays)

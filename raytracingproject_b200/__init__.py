@@ -2,7 +2,7 @@
 hittable_list / sphere / material API of ShuvalovIvan/RayTracingProject.  Only the reference's
 CPU path-tracing hot path is in scope."""
 from ._lib import (ABI, F32, F64, MEGAKERNEL, WAVEFRONT, MEGA_LOCKSTEP, TRACE_BVH, TRACE_BRUTE, BVH_SAH_HOST, BVH_LBVH_GPU,
-                   LAMBERTIAN, METAL, DIELECTRIC, SPHERE, MATERIAL, DEMO_SPHERE, RAY, HIT, LIB_PATH, SYMBOLS, lib)
+                   LAMBERTIAN, METAL, DIELECTRIC, SPHERE, MATERIAL, DEMO_SPHERE, IMG_P3, IMG_P6, IMG_PFM, RAY, HIT, LIB_PATH, SYMBOLS, lib)
 from .api import (Camera, Context, Dielectric, HittableList, Lambertian, Metal, RtError, Sphere,
                   build_bvh_host, camera_rtiow, scene_rtiow)
 

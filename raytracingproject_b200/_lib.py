@@ -18,6 +18,7 @@ LAMBERTIAN, METAL, DIELECTRIC = 0, 1, 2
 # numpy mirrors of the POD structs (layouts asserted in rt_api.cu)
 SPHERE = np.dtype([("center1", "f8", 3), ("center_vec", "f8", 3), ("radius", "f8"),
                    ("is_moving", "i4"), ("material", "i4")])
+IMG_P3, IMG_P6, IMG_PFM = 0, 1, 2
 DEMO_SPHERE = np.dtype([("center", "f4", 3), ("radius", "f4"), ("color", "f4", 4)])    # rt_demo_sphere
 MATERIAL = np.dtype([("type", "i4"), ("pad", "i4"), ("albedo", "f8", 3), ("param", "f8")])
 RAY = np.dtype([("orig", "f8", 3), ("dir", "f8", 3), ("tm", "f8")])
@@ -62,6 +63,8 @@ SYMBOLS = {
     "rt_upload_scene": (_I, [_VP, _VP, _SZ, _VP, _SZ, _VP]),
     "rt_render": (_I, [_VP, _VP, _VP]),
     "rt_readback": (_I, [_VP, _I, _VP, _VP, _VP, _VP]),
+    "rt_readback_image": (_I, [_VP, _I, _I, _VP, _VP]),
+    "rt_preview": (_I, [_VP, _I, _VP, _VP]),
     "rt_image_size": (_I, [_VP, _VP, _VP]),
     "rt_synchronize": (_I, [_VP]),
     "rt_get_stats": (_I, [_VP, _VP]),

@@ -151,6 +151,21 @@ class Context:
         self._ck(self._lib.rt_readback(self._h, spp_total, None, L.ptr(rgb8), L.ptr(ppm), C.byref(n) if ppm is not None else None))
         return n.value
 
+    def readback_image(self, fmt, spp_total=0):
+        """The frame as file bytes: IMG_P3 (the reference's stdout), IMG_P6 or IMG_PFM (rt_readback_image)."""
+        n = C.c_size_t(0)
+        self._ck(self._lib.rt_readback_image(self._h, spp_total, fmt, None, C.byref(n)))
+        buf = np.empty(n.value, np.uint8)
+        self._ck(self._lib.rt_readback_image(self._h, spp_total, fmt, L.ptr(buf), C.byref(n)))
+        return buf[:n.value].tobytes()
+
+    def preview(self, spp_total=0, copy=True):
+        """rt_preview: (device pointer, (H, W, 4) rgba8 host copy or None)."""
+        p = C.c_void_p()
+        img = np.empty((self.height, self.width, 4), np.uint8) if copy else None
+        self._ck(self._lib.rt_preview(self._h, spp_total, C.byref(p), L.ptr(img)))
+        return p.value, img
+
     def demo_compute(self, width=1024, height=768, spheres=None):
         """The windowed demo's compute stage (reference assets/shaders/ray_tracing.comp:35-73; default size
         src/common_objects.h:8-9) into a headless (height, width, 4) rgba8 image.  spheres: DEMO_SPHERE

@@ -71,6 +71,8 @@ struct rt_ctx {
     DevBuf<unsigned long long> ray_counter;
     DevBuf<unsigned char> rgb8;
     DevBuf<double> sum;
+    DevBuf<float> pfm;                      // 8f-2 views of the resolved frame
+    DevBuf<uchar4> rgba8;
     DevBuf<char> text;
     DevBuf<unsigned> enc_sums;
     DevBuf<unsigned long long> enc_offsets;   // [blocks] + total at the end
@@ -465,8 +467,11 @@ extern "C" int rt_render(rt_ctx* ctx, const rt_camera* cam, const rt_render_opts
     slices = std::max(1, std::min(slices, std::max(1, sample_count)));
     const size_t elem = opts->precision == RT_F32 ? sizeof(float4) : sizeof(double4);
 
-    const bool same = ctx->W == W && ctx->H == H && ctx->precision == opts->precision && ctx->slices == slices;
-    if (opts->accumulate && !same) return fail(ctx, RT_E_STATE, "rt_render: accumulate needs the same image, precision and slice count as the buffer");
+    // a progressive pass may use fewer slices than the buffer holds (it adds into the first ones; resolve sums all)
+    if (opts->accumulate && opts->slices <= 0 && ctx->slices > 0) slices = std::min(slices, ctx->slices);
+    const bool fits = ctx->W == W && ctx->H == H && ctx->precision == opts->precision && slices <= ctx->slices;
+    const bool same = fits && (opts->accumulate || slices == ctx->slices);
+    if (opts->accumulate && !fits) return fail(ctx, RT_E_STATE, "rt_render: accumulate needs the same image and precision as the buffer, and no more slices than it holds");
     if (!same) {
         CK(ctx->accum.resize(size_t(slices) * W * H * elem));
         ctx->W = W; ctx->H = H; ctx->precision = opts->precision; ctx->slices = slices;
@@ -525,6 +530,62 @@ extern "C" int rt_readback(rt_ctx* ctx, int spp_total, double* sum_rgb, uint8_t*
     float ms = 0;
     if (cudaEventElapsedTime(&ms, ctx->ev[2], ctx->ev[3]) == cudaSuccess) ctx->stats.resolve_ms = ms;
     ctx->stats.kernel_launches = (ctx->render_timed ? 1 : 0) + launches;
+    return RT_OK;
+}
+
+// ---------------------------------------------------------------- 8f-2: more output formats --
+static int resolve_views(rt_ctx* ctx, int spp_total, const FrameViews& v) {
+    const size_t npix = size_t(ctx->W) * ctx->H;
+    CK(ctx->rgb8.resize(npix * 3 + 16));
+    const double scale = spp_total > 0 ? 1.0 / spp_total : 0.0;
+    if (ctx->precision == RT_F32)
+        CK(launch_resolve<float4>(reinterpret_cast<const float4*>(ctx->accum.p), ctx->slices, ctx->peers, npix, scale,
+                                  nullptr, ctx->rgb8.p, nullptr, ctx->stream, v));
+    else
+        CK(launch_resolve<double4>(reinterpret_cast<const double4*>(ctx->accum.p), ctx->slices, ctx->peers, npix, scale,
+                                   nullptr, ctx->rgb8.p, nullptr, ctx->stream, v));
+    return RT_OK;
+}
+
+extern "C" int rt_readback_image(rt_ctx* ctx, int spp_total, int format, void* buf, size_t* len) {
+    if (!ctx || !len) return RT_E_INVALID;
+    if (ctx->W == 0 || !ctx->accum.p) return fail(ctx, RT_E_STATE, "rt_readback_image: nothing rendered");
+    if (format == RT_IMG_P3) return rt_readback(ctx, spp_total, nullptr, nullptr, static_cast<char*>(buf), len);
+    if (format != RT_IMG_P6 && format != RT_IMG_PFM) return fail(ctx, RT_E_INVALID, "rt_readback_image: unknown format");
+    CK(cudaSetDevice(ctx->device));
+    const size_t npix = size_t(ctx->W) * ctx->H;
+    char hdr[64];
+    const int hl = format == RT_IMG_P6 ? std::snprintf(hdr, sizeof hdr, "P6\n%d %d\n255\n", ctx->W, ctx->H)
+                                       : std::snprintf(hdr, sizeof hdr, "PF\n%d %d\n-1.0\n", ctx->W, ctx->H);
+    const size_t body = format == RT_IMG_P6 ? npix * 3 : npix * 3 * sizeof(float);
+    const size_t need = size_t(hl) + body;
+    if (!buf) { *len = need; return RT_OK; }
+    if (*len < need) { *len = need; return fail(ctx, RT_E_INVALID, "rt_readback_image: buffer too small"); }
+    FrameViews v{nullptr, nullptr, ctx->W, ctx->H};
+    if (format == RT_IMG_PFM) { CK(ctx->pfm.resize(npix * 3)); v.pfm = ctx->pfm.p; }
+    int rc = resolve_views(ctx, spp_total, v);
+    if (rc != RT_OK) return rc;
+    std::memcpy(buf, hdr, size_t(hl));
+    CK(cudaMemcpyAsync(static_cast<char*>(buf) + hl, format == RT_IMG_P6 ? static_cast<const void*>(ctx->rgb8.p) : static_cast<const void*>(ctx->pfm.p),
+                       body, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    *len = need;
+    return RT_OK;
+}
+
+extern "C" int rt_preview(rt_ctx* ctx, int spp_total, void** dev_rgba8, uint8_t* host_rgba8) {
+    if (!ctx) return RT_E_INVALID;
+    if (ctx->W == 0 || !ctx->accum.p) return fail(ctx, RT_E_STATE, "rt_preview: nothing rendered");
+    CK(cudaSetDevice(ctx->device));
+    const size_t npix = size_t(ctx->W) * ctx->H;
+    CK(ctx->rgba8.resize(npix));
+    int rc = resolve_views(ctx, spp_total, FrameViews{nullptr, ctx->rgba8.p, ctx->W, ctx->H});
+    if (rc != RT_OK) return rc;
+    if (dev_rgba8) *dev_rgba8 = ctx->rgba8.p;
+    if (host_rgba8) {
+        CK(cudaMemcpyAsync(host_rgba8, ctx->rgba8.p, npix * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+    }
     return RT_OK;
 }
 

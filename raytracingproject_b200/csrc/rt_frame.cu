@@ -21,7 +21,7 @@ __device__ __forceinline__ unsigned char write_color_byte(double sum, double sca
 // loads cross NVLink inside this kernel (fused reduce + resolve).
 template <typename Q>
 __global__ void resolve_kernel(const Q* __restrict__ accum, int slices, PeerList peers, size_t n_pixels, double scale,
-                               double* __restrict__ sum_out, unsigned char* __restrict__ rgb8, Q* __restrict__ reduced_out) {
+                               double* __restrict__ sum_out, unsigned char* __restrict__ rgb8, Q* __restrict__ reduced_out, FrameViews views) {
     const size_t g = (size_t(blockIdx.x) * blockDim.x + threadIdx.x) * 4;
     if (g >= n_pixels) return;
     double s[4][4];
@@ -50,11 +50,18 @@ __global__ void resolve_kernel(const Q* __restrict__ accum, int slices, PeerList
             b[3 * k + 1] = write_color_byte(s[k][1], sc);
             b[3 * k + 2] = write_color_byte(s[k][2], sc);
             if (sum_out) { sum_out[3 * (g + k) + 0] = s[k][0]; sum_out[3 * (g + k) + 1] = s[k][1]; sum_out[3 * (g + k) + 2] = s[k][2]; }
+            if (views.pfm) {
+                const size_t y = (g + k) / size_t(views.width), x = (g + k) - y * size_t(views.width);
+                float* o = views.pfm + 3 * ((size_t(views.height) - 1 - y) * size_t(views.width) + x);
+                o[0] = float(s[k][0] * sc); o[1] = float(s[k][1] * sc); o[2] = float(s[k][2] * sc);
+            }
             if (reduced_out) { Q v; v.x = decltype(v.x)(s[k][0]); v.y = decltype(v.x)(s[k][1]); v.z = decltype(v.x)(s[k][2]); v.w = decltype(v.x)(s[k][3]); reduced_out[g + k] = v; }
         } else {
             b[3 * k] = b[3 * k + 1] = b[3 * k + 2] = 0;
         }
     }
+    if (views.rgba8)
+        for (int k = 0; k < np; ++k) views.rgba8[g + k] = make_uchar4(b[3 * k], b[3 * k + 1], b[3 * k + 2], 255);
     if (rgb8) {
         if (np == 4) {
             unsigned int* dst = reinterpret_cast<unsigned int*>(rgb8 + 3 * g);      // g % 4 == 0 -> 12-byte groups, 4-aligned
@@ -69,14 +76,14 @@ __global__ void resolve_kernel(const Q* __restrict__ accum, int slices, PeerList
 
 template <typename Q>
 cudaError_t launch_resolve(const Q* accum, int slices, const PeerList& peers, size_t n_pixels, double scale,
-                           double* sum_out, unsigned char* rgb8, Q* reduced_out, cudaStream_t st) {
+                           double* sum_out, unsigned char* rgb8, Q* reduced_out, cudaStream_t st, const FrameViews& views) {
     if (n_pixels == 0) return cudaSuccess;
     const size_t threads = (n_pixels + 3) / 4;
-    resolve_kernel<Q><<<unsigned((threads + 255) / 256), 256, 0, st>>>(accum, slices, peers, n_pixels, scale, sum_out, rgb8, reduced_out);
+    resolve_kernel<Q><<<unsigned((threads + 255) / 256), 256, 0, st>>>(accum, slices, peers, n_pixels, scale, sum_out, rgb8, reduced_out, views);
     return cudaGetLastError();
 }
-template cudaError_t launch_resolve<float4>(const float4*, int, const PeerList&, size_t, double, double*, unsigned char*, float4*, cudaStream_t);
-template cudaError_t launch_resolve<double4>(const double4*, int, const PeerList&, size_t, double, double*, unsigned char*, double4*, cudaStream_t);
+template cudaError_t launch_resolve<float4>(const float4*, int, const PeerList&, size_t, double, double*, unsigned char*, float4*, cudaStream_t, const FrameViews&);
+template cudaError_t launch_resolve<double4>(const double4*, int, const PeerList&, size_t, double, double*, unsigned char*, double4*, cudaStream_t, const FrameViews&);
 
 // ------------------------------------------------------------------------- P3 encoder --
 // "r g b\n" with variable-width decimals (src/color.h:32-34) needs a prefix sum of line lengths:

@@ -17,9 +17,15 @@ struct PeerList {
 
 struct EncodeHeader { int len; char text[48]; };     // "P3\n<W> <H>\n255\n" (src/camera.h:35)
 
+// optional extra views of the resolved frame, written by the same pass:
+//   pfm    3 floats per pixel, the mean radiance (sum / spp, before gamma), rows bottom-to-top as a PFM file stores them
+//   rgba8  the write_color bytes + alpha 255, 4 bytes per pixel: the headless stand-in for a presentable image
+struct FrameViews { float* pfm; uchar4* rgba8; int width, height; };
+
 template <typename Q>
 cudaError_t launch_resolve(const Q* accum, int slices, const PeerList& peers, size_t n_pixels, double scale,
-                           double* sum_out, unsigned char* rgb8, Q* reduced_out, cudaStream_t st);
+                           double* sum_out, unsigned char* rgb8, Q* reduced_out, cudaStream_t st,
+                           const FrameViews& views = FrameViews{nullptr, nullptr, 0, 0});
 
 int encode_blocks(size_t n_pixels);
 cudaError_t launch_encode_p3(const unsigned char* rgb8, size_t n_pixels, const EncodeHeader& hdr, unsigned* block_sums,

@@ -76,3 +76,23 @@ def test_cpp_render_fast_mode_within_tolerance(exe):
     g = golden("ref_c1_philox_seed0.npz")["rgb8"]
     d = np.abs(img.astype(int) - g.astype(int)).max(-1)
     assert (d <= 1).mean() >= 0.999
+
+
+@pytest.mark.gpu
+def test_cpp_binary_formats_and_progressive_passes(exe, O):
+    """8f-2 through the C++ camera: P6 carries the bytes of the P3 text; four progressive passes end on the same
+    image (sum order differs in the last bit only); PFM holds the mean radiance whose write_color is that image."""
+    g = golden("ref_c1_philox_seed0.npz")["rgb8"]
+    p6 = subprocess.run([exe, "400", "10", "50", "f64", "p6"], capture_output=True, check=True).stdout
+    assert p6 == O.ppm_p6(g)
+    prog = subprocess.run([exe, "400", "10", "50", "f64", "p6", "4"], capture_output=True, check=True)
+    assert b"Samples so far: 10" in prog.stderr
+    hl = len(b"P6\n400 225\n255\n")
+    a = np.frombuffer(prog.stdout[hl:], np.uint8).astype(int); b = g.reshape(-1).astype(int)
+    assert prog.stdout[:hl] == p6[:hl] and np.abs(a - b).max() <= 1 and (a != b).mean() < 1e-3
+    pfm = subprocess.run([exe, "400", "10", "50", "f64", "pfm"], capture_output=True, check=True).stdout
+    hl = len(b"PF\n400 225\n-1.0\n")
+    assert pfm[:hl] == b"PF\n400 225\n-1.0\n" and len(pfm) == hl + 400 * 225 * 12
+    mean = np.frombuffer(pfm[hl:], "<f4").reshape(225, 400, 3)[::-1].astype(np.float64)
+    byte = (256 * np.clip(np.sqrt(mean), 0.0, 0.999)).astype(int)
+    assert (np.abs(byte - g.astype(int)) <= 1).all() and (byte != g).mean() < 1e-3      # float rounding can cross a byte boundary
