@@ -112,7 +112,7 @@ typedef struct {
     int32_t  accumulate;     /* 0: overwrite the accumulation buffer, 1: add to it (progressive) */
     uint64_t seed;           /* Philox key; stream = (pixel, sample, stage), see DESIGN.md */
     int32_t  slices;         /* sample slices per pixel rendered by different warps (0 = auto) */
-    int32_t  sched;          /* tuning: th_s | th_l << 8 of the warp scheduler (0 = defaults) */
+    int32_t  sched;          /* tuning: th_s | th_l << 8 | shape+1 << 16 | th_n << 20 of the warp scheduler (0 = defaults) */
 } rt_render_opts;
 
 typedef struct {
@@ -179,6 +179,9 @@ int rt_preview(rt_ctx *ctx, int spp_total, void **dev_rgba8, uint8_t *host_rgba8
 int rt_image_size(const rt_camera *cam, int *width, int *height);   /* src/camera.h:53-54 */
 int rt_synchronize(rt_ctx *ctx);
 int rt_get_stats(rt_ctx *ctx, rt_stats *out);
+/* profiling aid: counters of the wavefront kernel's scheduler when the library was built with
+ * -DRT_POOL_STATS (zeros otherwise); out[0] = rays of the last render */
+int rt_debug_counters(rt_ctx *ctx, uint64_t out[32]);
 
 /* ---- multi-GPU plumbing (one process per GPU) -------------------------------- */
 

@@ -183,6 +183,11 @@ class Context:
         self._ck(self._lib.rt_get_stats(self._h, C.byref(st)))
         return {k: getattr(st, k) for k, _ in st._fields_ if k != "pad"}
 
+    def debug_counters(self):
+        out = np.zeros(32, np.uint64)
+        self._ck(self._lib.rt_debug_counters(self._h, L.ptr(out)))
+        return out
+
     def accum_buffer(self):
         p, n, e = C.c_void_p(), C.c_size_t(), C.c_int()
         self._ck(self._lib.rt_accum_buffer(self._h, C.byref(p), C.byref(n), C.byref(e)))

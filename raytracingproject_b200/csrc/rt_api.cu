@@ -207,7 +207,7 @@ int rt_create(rt_ctx** out, int device) {
     ctx->smem_per_sm = prop.sharedMemPerMultiprocessor;
     for (auto& ev : ctx->ev) cudaEventCreate(&ev);
     ctx->job_counter.resize(1);
-    ctx->ray_counter.resize(1);
+    ctx->ray_counter.resize(32);      // [0] rays; [1..] scheduler counters of a -DRT_POOL_STATS build
     *out = ctx;
     return RT_OK;
 }
@@ -385,8 +385,8 @@ template <typename T> int pool_shape_for(const rt_ctx* c, int sched, bool* stage
     const size_t scene = staged_bytes_aligned<T>(c->n_nodes, c->n_slots);
     const size_t budget = c->smem_optin;
     auto need = [&](int sh) { int P, B; pool_shape(sh, &P, &B); return size_t(B / 32) * pool_warp_bytes<T>(P); };
-    *staged = c->n_slots > 0 && scene + need(shape) + 8 * 1024 <= budget;
-    if (!*staged && c->n_slots > 0 && scene + need(0) + 8 * 1024 <= budget) { shape = 0; *staged = true; }
+    *staged = c->n_slots > 0 && scene + need(shape) <= budget;
+    if (!*staged && c->n_slots > 0 && scene + need(0) <= budget) { shape = 0; *staged = true; }
     if (!*staged && need(shape) > budget) shape = 0;
     return shape;
 }
@@ -416,7 +416,7 @@ int render_impl(rt_ctx* ctx, const rt_camera& cam, const rt_render_opts& o, int 
     }
     ctx->stats.scene_in_smem = staged;
     CK(cudaMemsetAsync(ctx->job_counter.p, 0, sizeof(unsigned int), ctx->stream));
-    CK(cudaMemsetAsync(ctx->ray_counter.p, 0, sizeof(unsigned long long), ctx->stream));
+    CK(cudaMemsetAsync(ctx->ray_counter.p, 0, 32 * sizeof(unsigned long long), ctx->stream));
     CK(cudaEventRecord(ctx->ev[0], ctx->stream));
     // section thresholds: o.sched = th_s | th_l << 8 (0 = defaults, tuned on B200: see DESIGN.md)
     p.th_s = (o.sched & 0xff) ? (o.sched & 0xff) : (o.variant == RT_WAVEFRONT ? 24 : 28);
@@ -586,6 +586,16 @@ extern "C" int rt_preview(rt_ctx* ctx, int spp_total, void** dev_rgba8, uint8_t*
         CK(cudaMemcpyAsync(host_rgba8, ctx->rgba8.p, npix * 4, cudaMemcpyDeviceToHost, ctx->stream));
         CK(cudaStreamSynchronize(ctx->stream));
     }
+    return RT_OK;
+}
+
+// profiling aid: the TRACE-stage scheduler counters a -DRT_POOL_STATS build of rt_wavefront.cuh collects
+// (all zero in a normal build); out[0] = rays.  Not part of the reference-facing surface.
+extern "C" int rt_debug_counters(rt_ctx* ctx, uint64_t out[32]) {
+    if (!ctx || !out) return RT_E_INVALID;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpy(out, ctx->ray_counter.p, 32 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
     return RT_OK;
 }
 

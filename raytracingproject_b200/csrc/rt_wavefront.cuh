@@ -55,6 +55,12 @@ render_pool_kernel(const RenderParams<T> p) {
     const int njobs = p.tiles_x * p.tiles_y * p.slices;
     const int th_p = p.th_s, th_l = p.th_l, th_n = p.th_n;
     unsigned long long my_rays = 0;
+#ifdef RT_POOL_STATS
+    unsigned long long stat[24] = {};            // TRACE-stage scheduler counters (profiling build only), see tools/pool_stats.py
+#define RT_STAT(k, v) (stat[k] += (unsigned long long)(v))
+#else
+#define RT_STAT(k, v) ((void)0)
+#endif
     int stack[RT_STACK];
 
     for (;;) {
@@ -161,10 +167,12 @@ render_pool_kernel(const RenderParams<T> p) {
                     const int nP = __popc(mP), nL = 32 - nN - nP;
                     const int avail = n_q - head;
                     if (nP == 32 && avail == 0) break;
+                    RT_STAT(0, 1); RT_STAT(1, nN); RT_STAT(2, nL); RT_STAT(3, nP); RT_STAT(4, avail > 0);
 
                     if (avail > 0 && (nP >= th_p || (nN | nL) == 0)) {
                         // ---- pull: idle lanes take the next rays of the queue
                         const int rank = __popc(mP & lt);
+                        RT_STAT(5, 1); RT_STAT(6, min(nP, avail)); RT_STAT(7, nN + nL);
                         if (isP && rank < avail) {
                             pid = B[L::QUEUE * P + head + rank];
                             ray.o = mk<T>(F[L::OX * P + pid], F[L::OY * P + pid], F[L::OZ * P + pid]);
@@ -181,6 +189,7 @@ render_pool_kernel(const RenderParams<T> p) {
                         }
                         head += min(nP, avail);
                     } else if (nL >= th_l || nL > nN) {
+                        RT_STAT(8, 1); RT_STAT(9, nL); RT_STAT(10, nN); RT_STAT(11, nP);
                         if (!isN && !isP) {
                             trav_leaf<T>(st.sa, st.sb, st.meta, ray, T(0.001), tv, stack);
                             if (tv.cur == RT_SENTINEL) { F[L::TBEST * P + pid] = tv.tbest; I[L::BEST * P + pid] = tv.best_slot; }
@@ -188,8 +197,10 @@ render_pool_kernel(const RenderParams<T> p) {
                     } else {
                         // node visits, two per head count, repeated while most of the lanes that started them
                         // still have a node; a lane whose walk ends hands in its result after the loop
-                        int now;
+                        int now = nN;
+                        RT_STAT(12, 1); RT_STAT(13, nN); RT_STAT(14, nL); RT_STAT(15, nP);
                         do {
+                            RT_STAT(16, 1); RT_STAT(17, now);
                             if (tv.cur >= 0) trav_node<T>(st.nodes, ray, T(0.001), tv, stack);
                             if (tv.cur >= 0) trav_node<T>(st.nodes, ray, T(0.001), tv, stack);
                             now = __popc(__ballot_sync(FULL, tv.cur >= 0));
@@ -270,6 +281,9 @@ render_pool_kernel(const RenderParams<T> p) {
     }
     for (int o = 16; o > 0; o >>= 1) my_rays += __shfl_xor_sync(FULL, my_rays, o);
     if (lane == 0 && my_rays) atomicAdd(p.ray_counter, my_rays);
+#ifdef RT_POOL_STATS
+    if (lane == 0) for (int k = 0; k < 24; ++k) if (stat[k]) atomicAdd(p.ray_counter + 1 + k, stat[k]);
+#endif
 }
 
 }  // namespace rt
