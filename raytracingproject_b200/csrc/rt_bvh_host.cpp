@@ -170,9 +170,10 @@ void build_bvh_sah(const std::vector<HostBox>& boxes, int max_leaf, HostBVH& out
         const TmpNode& L = b.nodes[nd.left];
         const TmpNode& R = b.nodes[nd.right];
         float* f = &out.nodes[q * 16];
-        f[0] = L.box.lo[0]; f[1] = L.box.lo[1]; f[2] = L.box.lo[2]; f[3] = L.box.hi[0];
-        f[4] = L.box.hi[1]; f[5] = L.box.hi[2]; f[6] = R.box.lo[0]; f[7] = R.box.lo[1];
-        f[8] = R.box.lo[2]; f[9] = R.box.hi[0]; f[10] = R.box.hi[1]; f[11] = R.box.hi[2];
+        // record layout (rt_trace.cuh): xy of the left box | xy of the right box | z of both | refs
+        f[0] = L.box.lo[0]; f[1] = L.box.lo[1]; f[2] = L.box.hi[0]; f[3] = L.box.hi[1];
+        f[4] = R.box.lo[0]; f[5] = R.box.lo[1]; f[6] = R.box.hi[0]; f[7] = R.box.hi[1];
+        f[8] = L.box.lo[2]; f[9] = R.box.lo[2]; f[10] = L.box.hi[2]; f[11] = R.box.hi[2];
         const int lref = L.left >= 0 ? inner_id[nd.left] : leaf_ref(L.first, L.count);
         const int rref = R.left >= 0 ? inner_id[nd.right] : leaf_ref(R.first, R.count);
         std::memcpy(&f[12], &lref, 4);

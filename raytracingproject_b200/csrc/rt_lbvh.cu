@@ -149,9 +149,9 @@ __global__ void __launch_bounds__(256) lbvh_refit(const HostBox* __restrict__ bo
                 cb[k].depth = 0;
             }
         }
-        nodes[4 * node + 0] = make_float4(cb[0].lo[0], cb[0].lo[1], cb[0].lo[2], cb[0].hi[0]);
-        nodes[4 * node + 1] = make_float4(cb[0].hi[1], cb[0].hi[2], cb[1].lo[0], cb[1].lo[1]);
-        nodes[4 * node + 2] = make_float4(cb[1].lo[2], cb[1].hi[0], cb[1].hi[1], cb[1].hi[2]);
+        nodes[4 * node + 0] = make_float4(cb[0].lo[0], cb[0].lo[1], cb[0].hi[0], cb[0].hi[1]);     // record layout: rt_trace.cuh
+        nodes[4 * node + 1] = make_float4(cb[1].lo[0], cb[1].lo[1], cb[1].hi[0], cb[1].hi[1]);
+        nodes[4 * node + 2] = make_float4(cb[0].lo[2], cb[1].lo[2], cb[0].hi[2], cb[1].hi[2]);
         nodes[4 * node + 3] = make_float4(__int_as_float(c[0]), __int_as_float(c[1]), 0.0f, 0.0f);
         unite(cb[0], cb[1]);
         cb[0].depth += 1;

@@ -13,8 +13,9 @@ namespace rt {
 #define RT_STACK 64
 
 // Node record (one per inner node, 64 B = 4 x float4), boxes of BOTH children, padded outwards:
-//   q0 = (Lmin.x, Lmin.y, Lmin.z, Lmax.x)   q1 = (Lmax.y, Lmax.z, Rmin.x, Rmin.y)
-//   q2 = (Rmin.z, Rmax.x, Rmax.y, Rmax.z)   q3 = (bits left_ref, bits right_ref, -, -)
+//   q0 = (Lmin.x, Lmin.y, Lmax.x, Lmax.y)   q1 = (Rmin.x, Rmin.y, Rmax.x, Rmax.y)
+//   q2 = (Lmin.z, Rmin.z, Lmax.z, Rmax.z)   q3 = (bits left_ref, bits right_ref, -, -)
+// -- every aligned pair of floats is one operand of a packed FFMA2 of the slab test (node_boxes below).
 // child ref >= 0: inner node index; < 0: leaf, ~ref = first_slot << 3 | (count - 1).
 template <typename T> struct SceneView {
     typedef typename Quad<T>::type Q;
@@ -32,27 +33,57 @@ template <typename T> struct SceneView {
     int off_sa, off_sb, off_sc, off_meta;   // byte offsets of the staged copies in shared memory (nodes at 0)
 };
 
-// Slab test, src/aabb.h:35-53 with 1/d hoisted.  Returns entry distance in tnear.
-// float rays: t = plane * inv + noi with noi = -(o * inv) hoisted per ray -- one FFMA per plane instead of
-// FADD + FMUL.  The price is an ABSOLUTE error of ~ulp(o * inv) on every t (plus 1 ulp relative from the
-// approximate reciprocal), so the test is made conservative with a relative factor AND a per-ray additive
-// slack `delta` = 2^-22 max|o * inv| (trav_setup, which also keeps inv finite: a zero direction component
-// switches its axis off through delta).  A box can only be accepted wrongly, never rejected wrongly, and
-// acceptance of a HIT is decided by the sphere tests alone.
-__device__ __forceinline__ bool slab(float lx, float ly, float lz, float hx, float hy, float hz,
-                                     const Vec<float>& noi, const Vec<float>& inv, float delta, float tmin, float tmax, float& tnear) {
-    const float t0x = fmaf(lx, inv.x, noi.x), t1x = fmaf(hx, inv.x, noi.x);
-    const float t0y = fmaf(ly, inv.y, noi.y), t1y = fmaf(hy, inv.y, noi.y);
-    const float t0z = fmaf(lz, inv.z, noi.z), t1z = fmaf(hz, inv.z, noi.z);
-    const float tn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fmaxf(fminf(t0z, t1z), tmin));
-    const float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fminf(fmaxf(t0z, t1z), tmax));
-    tnear = tn;
-    return tn <= fmaf(tf, 1.000001f, delta);
+// Slab test of BOTH child boxes of a node, src/aabb.h:35-53 with 1/d hoisted.
+//
+// float rays: t = plane * inv + noi with noi = -(o * inv) hoisted per ray -- an FMA per plane instead of
+// FADD + FMUL.  The near / far plane of an axis is known from the sign of the direction, so the reciprocal
+// is kept split into its positive part p and negative part q (one of them is 0; the product with the zero
+// part is exact): near = l*p + (h*q + noi), far = h*p + (l*q + noi), and no min / max per axis is needed.
+// The planes of a record are laid out so that every such FMA is one half of a PACKED fp32 FMA of sm_100a
+// (fma.rn.f32x2 = FFMA2: two lanes of one 64-bit register pair, one issue slot): 12 FFMA2 + 8 min / max
+// per node where the min / max form took 12 FFMA + 20 FMNMX.  This kernel is bound by issue slots.
+// The price of the hoisted noi is an ABSOLUTE error of ~ulp(o * inv) on every t (plus 1 ulp relative from
+// the approximate reciprocal), so the test is made conservative with a relative factor AND a per-ray
+// additive slack `delta` = 2^-22 max|o * inv| (trav_setup, which also keeps inv finite: a zero direction
+// component switches its axis off through delta).  A box can only be accepted wrongly, never rejected
+// wrongly, and acceptance of a HIT is decided by the sphere tests alone.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void unpack2(f32x2 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+
+// per-ray constants of the slab test
+template <typename T> struct SlabRay;
+template <> struct SlabRay<float> {
+    f32x2 pxy, qxy, oxy, pzz, qzz, ozz;       // (p.x, p.y) (q.x, q.y) (noi.x, noi.y) (p.z, p.z) (q.z, q.z) (noi.z, noi.z)
+    float delta;
+};
+template <> struct SlabRay<double> {
+    Vec<double> o, inv;                        // parity mode: the reference's form, (plane - o) * inv
+};
+
+__device__ __forceinline__ void node_boxes(const float4& q0, const float4& q1, const float4& q2, const SlabRay<float>& s,
+                                           float tmin, float tmax, bool& hl, bool& hr, float& tl, float& tr) {
+    const f32x2 Ll = pack2(q0.x, q0.y), Lh = pack2(q0.z, q0.w), Rl = pack2(q1.x, q1.y), Rh = pack2(q1.z, q1.w);
+    const f32x2 Zl = pack2(q2.x, q2.y), Zh = pack2(q2.z, q2.w);
+    float lnx, lny, lfx, lfy, rnx, rny, rfx, rfy, lnz, rnz, lfz, rfz;
+    unpack2(fma2(Ll, s.pxy, fma2(Lh, s.qxy, s.oxy)), lnx, lny);
+    unpack2(fma2(Lh, s.pxy, fma2(Ll, s.qxy, s.oxy)), lfx, lfy);
+    unpack2(fma2(Rl, s.pxy, fma2(Rh, s.qxy, s.oxy)), rnx, rny);
+    unpack2(fma2(Rh, s.pxy, fma2(Rl, s.qxy, s.oxy)), rfx, rfy);
+    unpack2(fma2(Zl, s.pzz, fma2(Zh, s.qzz, s.ozz)), lnz, rnz);
+    unpack2(fma2(Zh, s.pzz, fma2(Zl, s.qzz, s.ozz)), lfz, rfz);
+    tl = fmaxf(fmaxf(lnx, lny), fmaxf(lnz, tmin));
+    tr = fmaxf(fmaxf(rnx, rny), fmaxf(rnz, tmin));
+    const float fl = fminf(fminf(lfx, lfy), fminf(lfz, tmax)), fr = fminf(fminf(rfx, rfy), fminf(rfz, tmax));
+    hl = tl <= fmaf(fl, 1.000001f, s.delta);
+    hr = tr <= fmaf(fr, 1.000001f, s.delta);
 }
+
 // double rays against the float boxes (exactly representable in double): the boxes' outward
 // padding (>= 2^-20 relative) dwarfs double rounding.
 __device__ __forceinline__ bool slab(float lx, float ly, float lz, float hx, float hy, float hz,
-                                     const Vec<double>& o, const Vec<double>& inv, double, double tmin, double tmax, double& tnear) {
+                                     const Vec<double>& o, const Vec<double>& inv, double tmin, double tmax, double& tnear) {
     const double t0x = (double(lx) - o.x) * inv.x, t1x = (double(hx) - o.x) * inv.x;
     const double t0y = (double(ly) - o.y) * inv.y, t1y = (double(hy) - o.y) * inv.y;
     const double t0z = (double(lz) - o.z) * inv.z, t1z = (double(hz) - o.z) * inv.z;
@@ -60,6 +91,11 @@ __device__ __forceinline__ bool slab(float lx, float ly, float lz, float hx, flo
     const double tf = fmin(fmin(fmax(t0x, t1x), fmax(t0y, t1y)), fmin(fmax(t0z, t1z), tmax));
     tnear = tn;
     return tn <= tf;
+}
+__device__ __forceinline__ void node_boxes(const float4& q0, const float4& q1, const float4& q2, const SlabRay<double>& s,
+                                           double tmin, double tmax, bool& hl, bool& hr, double& tl, double& tr) {
+    hl = slab(q0.x, q0.y, q2.x, q0.z, q0.w, q2.z, s.o, s.inv, tmin, tmax, tl);
+    hr = slab(q1.x, q1.y, q2.y, q1.z, q1.w, q2.w, s.o, s.inv, tmin, tmax, tr);
 }
 
 __device__ __forceinline__ bool leaf_sphere(const float4& a, const float4& b, const Ray<float>& r, float a_len2, float inv_a,
@@ -78,13 +114,12 @@ __device__ __forceinline__ bool leaf_sphere(const double4& a, const double4& b, 
 // trace_closest() below simply runs them to completion for one ray.
 //   cur >= 0: inner node to visit; cur < 0 and != RT_SENTINEL: leaf to test; RT_SENTINEL: finished.
 template <typename T> struct Trav {
-    Vec<T> inv;              // 1 / direction
-    Vec<T> org;              // fast mode: -(origin * inv), the additive term of the FMA slab test; parity mode: origin
-    T delta;                 // fast mode: additive slack of the slab test; parity mode: unused
+    SlabRay<T> slab;         // per-ray constants of the box test
     T qa;                    // fast mode: 1 / |d|^2; parity mode: |d|^2 (what each sphere test wants)
     T tbest;
     int best_id, best_slot;  // list index (tie rule) and slot (tree slot, or n_slots + k for big sphere k)
     int cur, sp;
+    int tos;                 // copy of stack[sp - 1]: a pop takes it from the register and reloads it off the critical path
 };
 
 // big spheres first, in double in both modes (the r = 1000 ground sphere): a tight t_max for the
@@ -110,26 +145,41 @@ __device__ __forceinline__ void trav_big(const SceneView<T>& sv, const Ray<T>& r
     }
 }
 
+// per-ray constants of the box test
+__device__ __forceinline__ void slab_setup(const Ray<float>& r, SlabRay<float>& s) {
+    Vec<float> inv = mk<float>(1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z);
+    // keep the reciprocals finite: with +-inf the FMA form gives plane * inf - o * inf = NaN or an infinity
+    // whose sign depends on the plane alone.  At 1e18 the axis is effectively switched off through delta
+    // (boxes are accepted conservatively, as the NaN-dropping min/max of the reference's form would)
+    const float big = 1e18f;
+    if (!(fabsf(inv.x) <= big)) inv.x = copysignf(big, r.d.x);
+    if (!(fabsf(inv.y) <= big)) inv.y = copysignf(big, r.d.y);
+    if (!(fabsf(inv.z) <= big)) inv.z = copysignf(big, r.d.z);
+    const Vec<float> noi = mk<float>(-(r.o.x * inv.x), -(r.o.y * inv.y), -(r.o.z * inv.z));
+    s.delta = 2.384185791015625e-07f * fmaxf(fmaxf(fabsf(noi.x), fabsf(noi.y)), fabsf(noi.z));
+    const bool nx = inv.x < 0.0f, ny = inv.y < 0.0f, nz = inv.z < 0.0f;
+    s.pxy = pack2(nx ? 0.0f : inv.x, ny ? 0.0f : inv.y);
+    s.qxy = pack2(nx ? inv.x : 0.0f, ny ? inv.y : 0.0f);
+    s.oxy = pack2(noi.x, noi.y);
+    s.pzz = pack2(nz ? 0.0f : inv.z, nz ? 0.0f : inv.z);
+    s.qzz = pack2(nz ? inv.z : 0.0f, nz ? inv.z : 0.0f);
+    s.ozz = pack2(noi.z, noi.z);
+}
+__device__ __forceinline__ void slab_setup(const Ray<double>& r, SlabRay<double>& s) {
+    s.o = r.o;
+    s.inv = mk<double>(1.0 / r.d.x, 1.0 / r.d.y, 1.0 / r.d.z);
+}
+template <typename T> __device__ __forceinline__ void slab_clear(SlabRay<T>& s);
+template <> __device__ __forceinline__ void slab_clear<float>(SlabRay<float>& s) { s.pxy = s.qxy = s.oxy = s.pzz = s.qzz = s.ozz = 0ull; s.delta = 0.0f; }
+template <> __device__ __forceinline__ void slab_clear<double>(SlabRay<double>& s) { s.o = mk<double>(0, 0, 0); s.inv = mk<double>(0, 0, 0); }
+
 // per-ray constants of the tree walk; tbest / best_id / best_slot are already set (trav_big)
 template <typename T>
 __device__ __forceinline__ void trav_setup(const SceneView<T>& sv, const Ray<T>& r, Trav<T>& tv) {
     const T a_len2 = len2(r.d);
     tv.qa = sizeof(T) == 4 ? T(1) / a_len2 : a_len2;
-    tv.inv = mk<T>(T(1) / r.d.x, T(1) / r.d.y, T(1) / r.d.z);
-    if (sizeof(T) == 4) {
-        // keep the reciprocals finite: with +-inf the FMA form gives plane * inf - o * inf = NaN or an infinity
-        // whose sign depends on the plane alone.  At 1e18 the axis is effectively switched off through delta
-        // (boxes are accepted conservatively, as the NaN-dropping min/max of the reference's form would)
-        const float big = 1e18f;
-        if (!(fabsf(float(tv.inv.x)) <= big)) tv.inv.x = T(copysignf(big, float(r.d.x)));
-        if (!(fabsf(float(tv.inv.y)) <= big)) tv.inv.y = T(copysignf(big, float(r.d.y)));
-        if (!(fabsf(float(tv.inv.z)) <= big)) tv.inv.z = T(copysignf(big, float(r.d.z)));
-        tv.org = mk<T>(-(r.o.x * tv.inv.x), -(r.o.y * tv.inv.y), -(r.o.z * tv.inv.z));
-        tv.delta = T(2.384185791015625e-07) * T(fmaxf(fmaxf(fabsf(float(tv.org.x)), fabsf(float(tv.org.y))), fabsf(float(tv.org.z))));
-    } else {
-        tv.org = r.o; tv.delta = T(0);
-    }
-    tv.cur = sv.root_ref; tv.sp = 0;
+    slab_setup(r, tv.slab);
+    tv.cur = sv.root_ref; tv.sp = 0; tv.tos = RT_SENTINEL;
 }
 
 template <typename T>
@@ -144,16 +194,20 @@ __device__ __forceinline__ void trav_node(const float4* __restrict__ nodes, cons
     const int cur = tv.cur;
     const float4 q0 = nodes[4 * cur + 0], q1 = nodes[4 * cur + 1], q2 = nodes[4 * cur + 2], q3 = nodes[4 * cur + 3];
     T tl, tr;
-    const bool hl = slab(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, tv.org, tv.inv, tv.delta, tmin, tv.tbest, tl);
-    const bool hr = slab(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, tv.org, tv.inv, tv.delta, tmin, tv.tbest, tr);
+    bool hl, hr;
+    node_boxes(q0, q1, q2, tv.slab, tmin, tv.tbest, hl, hr, tl, tr);
     const int cl = __float_as_int(q3.x), cr = __float_as_int(q3.y);
     // near child next, far child pushed, nothing hit -> pop: written with selects and two short predicated
     // blocks instead of a four-way branch, so the lanes of a warp stay together through the step
     const bool left_first = !hr || (hl && tl <= tr);
     const int near = left_first ? cl : cr, far = left_first ? cr : cl;
-    if (hl && hr && tv.sp < RT_STACK) stack[tv.sp++] = far;
+    if (hl && hr && tv.sp < RT_STACK) { stack[tv.sp++] = far; tv.tos = far; }
     int next = near;
-    if (!(hl || hr)) next = tv.sp > 0 ? stack[--tv.sp] : RT_SENTINEL;
+    if (!(hl || hr)) {                      // pop: the top of the stack is in a register (RT_SENTINEL when the stack is empty)
+        next = tv.tos;
+        if (tv.sp > 0) --tv.sp;
+        tv.tos = tv.sp > 0 ? stack[tv.sp - 1] : RT_SENTINEL;
+    }
     tv.cur = next;
 }
 
@@ -172,7 +226,9 @@ __device__ __forceinline__ void trav_leaf(const typename Quad<T>::type* __restri
             tv.tbest = t; tv.best_id = id; tv.best_slot = slot;
         }
     }
-    tv.cur = tv.sp > 0 ? stack[--tv.sp] : RT_SENTINEL;
+    tv.cur = tv.tos;
+    if (tv.sp > 0) --tv.sp;
+    tv.tos = tv.sp > 0 ? stack[tv.sp - 1] : RT_SENTINEL;
 }
 
 // Closest hit in (tmin, tmax).  slot_out: tree slot, n_slots + k for big sphere k, or -1.

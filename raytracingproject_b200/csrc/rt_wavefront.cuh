@@ -158,7 +158,7 @@ render_pool_kernel(const RenderParams<T> p) {
             {
                 int head = 0, pid = 0;
                 Ray<T> ray; ray.o = mk<T>(0, 0, 0); ray.d = mk<T>(0, 0, 1); ray.tm = 0;
-                Trav<T> tv; tv.cur = RT_SENTINEL; tv.sp = 0; tv.tbest = 0; tv.best_id = -1; tv.best_slot = -1; tv.qa = 1; tv.inv = mk<T>(0, 0, 0); tv.org = mk<T>(0, 0, 0); tv.delta = 0;
+                Trav<T> tv; tv.cur = RT_SENTINEL; tv.sp = 0; tv.tos = RT_SENTINEL; tv.tbest = 0; tv.best_id = -1; tv.best_slot = -1; tv.qa = 1; slab_clear<T>(tv.slab);
                 for (;;) {
                     const bool isN = tv.cur >= 0;
                     const bool isP = tv.cur == RT_SENTINEL;

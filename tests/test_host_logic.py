@@ -73,8 +73,9 @@ def _check_bvh(spheres, b):
             return depth
         f = nodes[ref]
         refs = f[12:14].view("i4")
-        l = visit(int(refs[0]), np.maximum(blo, f[[0, 1, 2]]), np.minimum(bhi, f[[3, 4, 5]]), depth + 1)
-        r_ = visit(int(refs[1]), np.maximum(blo, f[[6, 7, 8]]), np.minimum(bhi, f[[9, 10, 11]]), depth + 1)
+        # record: xy of the left box (lo, hi) | xy of the right box | z of both (lo L, lo R, hi L, hi R) | refs
+        l = visit(int(refs[0]), np.maximum(blo, f[[0, 1, 8]]), np.minimum(bhi, f[[2, 3, 10]]), depth + 1)
+        r_ = visit(int(refs[1]), np.maximum(blo, f[[4, 5, 9]]), np.minimum(bhi, f[[6, 7, 11]]), depth + 1)
         return max(l, r_)
 
     d = visit(root, np.full(3, -np.inf), np.full(3, np.inf), 1)
