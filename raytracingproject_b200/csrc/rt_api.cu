@@ -386,7 +386,13 @@ template <typename T> int pool_shape_for(const rt_ctx* c, int sched, bool* stage
     const size_t budget = c->smem_optin;
     auto need = [&](int sh) { int P, B; pool_shape(sh, &P, &B); return size_t(B / 32) * pool_warp_bytes<T>(P); };
     *staged = c->n_slots > 0 && scene + need(shape) <= budget;
-    if (!*staged && c->n_slots > 0 && scene + need(0) <= budget) { shape = 0; *staged = true; }
+    if (!*staged && c->n_slots > 0) {                 // fewer warps, most first, until scene + pools fit
+        const int by_warps[] = { 3, 5, 4, 2, 1, 0 };
+        for (int sh : by_warps) {
+            int P, B, P0, B0; pool_shape(sh, &P, &B); pool_shape(shape, &P0, &B0);
+            if (B < B0 && scene + need(sh) <= budget) { shape = sh; *staged = true; break; }
+        }
+    }
     if (!*staged && need(shape) > budget) shape = 0;
     return shape;
 }
@@ -438,6 +444,12 @@ extern "C" int rt_render(rt_ctx* ctx, const rt_camera* cam, const rt_render_opts
     if (cam->image_width < 1 || !(cam->aspect_ratio > 0)) return fail(ctx, RT_E_INVALID, "rt_render: bad image size");
     if (opts->precision != RT_F32 && opts->precision != RT_F64) return fail(ctx, RT_E_INVALID, "rt_render: bad precision");
     if (opts->variant != RT_MEGAKERNEL && opts->variant != RT_MEGA_LOCKSTEP && opts->variant != RT_WAVEFRONT) return fail(ctx, RT_E_INVALID, "rt_render: variant not built");
+    // the wavefront pool keeps a path's sample index and remaining depth in 16 bits: beyond that the
+    // warp-scheduled megakernel (same arithmetic, same image) takes the call
+    rt_render_opts eff = *opts;
+    if (eff.variant == RT_WAVEFRONT && (cam->max_depth > 65535 ||
+        (eff.sample_count > 0 ? eff.sample_count : cam->samples_per_pixel) > 65535)) { eff.variant = RT_MEGAKERNEL; eff.sched = 0; }
+    opts = &eff;
     CK(cudaSetDevice(ctx->device));
     const int W = cam->image_width, H = image_height_of(*cam);
     if ((long long)W * H >= (1ll << 32)) return fail(ctx, RT_E_INVALID, "rt_render: image too large for the 32-bit pixel key");

@@ -27,9 +27,10 @@ namespace rt {
 
 template <typename T, int P> struct Pool {
     enum { OX, OY, OZ, TM, DX, DY, DZ, TR, TG, TB, TBEST, NF };        // T arrays [P]
-    enum { BEST, SAMPLE, DEPTH, NI };                                   // int arrays [P]
+    enum { BEST, NI };                                                  // int arrays [P]
+    enum { SAMPLE, DEPTH, NH };                                         // 16-bit arrays [P]: sample index relative to the job's first, bounces left
     enum { QUEUE, LOPAQUE, LGLASS, LEND, NL };                          // byte lists [P]
-    static constexpr int bytes = NF * P * int(sizeof(T)) + NI * P * 4 + NL * P;
+    static constexpr int bytes = NF * P * int(sizeof(T)) + NI * P * 4 + NH * P * 2 + NL * P;
     static constexpr int tile_w = 16, tile_h = P / 16;
     static_assert(P % 32 == 0 && P <= 128, "pool: path id is 7 bits, lists are filled 32 at a time");
 };
@@ -49,7 +50,8 @@ render_pool_kernel(const RenderParams<T> p) {
     unsigned char* wb = smem + (STAGED ? staged_bytes_aligned<T>(sv.n_nodes, sv.n_slots) : 0) + size_t(warp) * L::bytes;
     T* const F = reinterpret_cast<T*>(wb);
     int* const I = reinterpret_cast<int*>(F + L::NF * P);
-    unsigned char* const B = reinterpret_cast<unsigned char*>(I + L::NI * P);
+    unsigned short* const S = reinterpret_cast<unsigned short*>(I + L::NI * P);
+    unsigned char* const B = reinterpret_cast<unsigned char*>(S + L::NH * P);
 
     const int W = p.cam.image_width, H = p.cam.image_height;
     const int njobs = p.tiles_x * p.tiles_y * p.slices;
@@ -86,7 +88,7 @@ render_pool_kernel(const RenderParams<T> p) {
                 v.w += decltype(v.x)(s_end - s_begin);
                 *dst = v;
             }
-            I[L::SAMPLE * P + k] = s_begin; I[L::DEPTH * P + k] = 0;
+            S[L::SAMPLE * P + k] = 0; S[L::DEPTH * P + k] = 0;
             const bool start = in_image && s_begin < s_end && p.max_depth > 0;    // max_depth <= 0: black (src/camera_cpu.h:12-13)
             const unsigned m = __ballot_sync(FULL, start);
             if (start) B[L::LEND * P + n_end + __popc(m & lt)] = (unsigned char)(k | 0x80);   // 0x80: nothing to add
@@ -114,7 +116,7 @@ render_pool_kernel(const RenderParams<T> p) {
                         v.x += decltype(v.x)(c.x); v.y += decltype(v.x)(c.y); v.z += decltype(v.x)(c.z);
                         *dst = v;
                     }
-                    const int s = I[L::SAMPLE * P + pid];
+                    const int s = s_begin + int(S[L::SAMPLE * P + pid]);
                     if (s < s_end) {
                         Philox rng; rng.init(p.seed);
                         rng.set(uint32_t(j) * uint32_t(W) + uint32_t(i), uint32_t(s), 0u);
@@ -122,7 +124,7 @@ render_pool_kernel(const RenderParams<T> p) {
                         F[L::OX * P + pid] = ray.o.x; F[L::OY * P + pid] = ray.o.y; F[L::OZ * P + pid] = ray.o.z; F[L::TM * P + pid] = ray.tm;
                         F[L::DX * P + pid] = ray.d.x; F[L::DY * P + pid] = ray.d.y; F[L::DZ * P + pid] = ray.d.z;
                         F[L::TR * P + pid] = T(1); F[L::TG * P + pid] = T(1); F[L::TB * P + pid] = T(1);
-                        I[L::SAMPLE * P + pid] = s + 1; I[L::DEPTH * P + pid] = p.max_depth;
+                        S[L::SAMPLE * P + pid] = (unsigned short)(s + 1 - s_begin); S[L::DEPTH * P + pid] = (unsigned short)p.max_depth;
                         push = true;
                     }
                 }
@@ -250,8 +252,8 @@ render_pool_kernel(const RenderParams<T> p) {
                         ray.d = mk<T>(F[L::DX * P + pid], F[L::DY * P + pid], F[L::DZ * P + pid]);
                         ray.tm = F[L::TM * P + pid];
                         T t = F[L::TBEST * P + pid];
-                        const int slot = I[L::BEST * P + pid], s = I[L::SAMPLE * P + pid];
-                        int depth = I[L::DEPTH * P + pid];
+                        const int slot = I[L::BEST * P + pid], s = s_begin + int(S[L::SAMPLE * P + pid]);
+                        int depth = S[L::DEPTH * P + pid];
                         const Surface<T> sf = surface_at<T>(sv, st.sa, st.sb, st.sc, st.meta, ray, t, slot);
                         Philox rng; rng.init(p.seed);
                         rng.set(uint32_t(j) * uint32_t(W) + uint32_t(i), uint32_t(s - 1), uint32_t(p.max_depth - depth + 1));   // b-th hit: stage b
@@ -266,7 +268,7 @@ render_pool_kernel(const RenderParams<T> p) {
                             F[L::OX * P + pid] = ray.o.x; F[L::OY * P + pid] = ray.o.y; F[L::OZ * P + pid] = ray.o.z;
                             F[L::DX * P + pid] = ray.d.x; F[L::DY * P + pid] = ray.d.y; F[L::DZ * P + pid] = ray.d.z;
                             F[L::TR * P + pid] *= att.x; F[L::TG * P + pid] *= att.y; F[L::TB * P + pid] *= att.z;
-                            I[L::DEPTH * P + pid] = depth;
+                            S[L::DEPTH * P + pid] = (unsigned short)depth;
                         }
                     }
                     const unsigned mc = __ballot_sync(FULL, cont), me = __ballot_sync(FULL, ended);
