@@ -372,3 +372,23 @@ def test_errors_are_reported(ctx, rt):
     with pytest.raises(rt.RtError, match="material index"):
         c2.upload_scene(bad, m)
     c2.close()
+
+
+def test_wavefront_beyond_16_bit_sample_or_depth_counts(ctx_scene, rt, O, scene):
+    """The wavefront pool keeps a path's sample index and remaining depth in 16 bits; calls beyond that are rendered
+    by the warp-scheduled megakernel behind the same entry point: same image as the oracle either way."""
+    s, m = scene
+    for width, spp, depth in ((6, 66000, 4), (48, 3, 70000)):
+        cam = rt.camera_rtiow(width, spp, depth)
+        ctx_scene.render(cam, precision=rt.F64, seed=12, variant=rt.WAVEFRONT)
+        out = ctx_scene.readback(spp)
+        ref = O.render(s, m, O.camera_rtiow(width, spp, depth), rng_mode=O.RNG_PHILOX, seed=12, use_bvh=True)
+        assert ctx_scene.stats()["rays"] == ref["rays"]
+        assert np.array_equal(out["rgb8"], ref["rgb8"])
+        assert np.allclose(out["sum"], ref["sum"], rtol=1e-12, atol=1e-12)
+    # just below the limit the pool itself runs (65535 samples in one slice)
+    cam = rt.camera_rtiow(2, 65535, 2)
+    ctx_scene.render(cam, precision=rt.F64, seed=1, variant=rt.WAVEFRONT)
+    out = ctx_scene.readback(65535)
+    ref = O.render(s, m, O.camera_rtiow(2, 65535, 2), rng_mode=O.RNG_PHILOX, seed=1, use_bvh=True)
+    assert np.array_equal(out["rgb8"], ref["rgb8"]) and ctx_scene.stats()["rays"] == ref["rays"]
