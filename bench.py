@@ -269,7 +269,7 @@ def main():
                          # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of this kernel on this workload, from the
                          # ncu --set full capture profiles/r1_wavefront_c3_500spp_ncu_summary.txt (66.5 MB + 175.1 MB); the
                          # bounce loop itself reads nothing from HBM (scene staged on chip), this is the accumulator traffic
-                         "traffic": 241.5e6 if (args.variant == "wavefront" and world == 1 and args.spp == SPP and args.precision == "f32") else None,
+                         "traffic": 107.8e6 if (args.variant == "wavefront" and world == 1 and args.spp == SPP and args.precision == "f32") else None,
                          "kernel": kernel_name, "kernel_ms": kms,
                          "note": f"algorithmic {F_RAY:.0f} flop/ray x {rank_rays:.3e} rays per launch (SURVEY 8d); peak = 148 SMs x 128 "
                                  f"FP32 lanes x 2 x {sm_mhz:.0f} MHz observed under load (not in MEASURED_PEAKS.json); L2-side figure "
