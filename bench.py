@@ -256,6 +256,8 @@ def main():
         fp32_peak = 148 * 128 * 2 * sm_mhz * 1e6 / 1e12               # TFLOP/s at the clock seen under load
         achieved = rank_rays * F_RAY / (kms * 1e-3) / 1e12
         e2e_ms = sum(e2e_times) / len(e2e_times)
+        if os.environ.get("RT_BENCH_DEBUG"):
+            print("device-resident step ms:", [round(t, 3) for t in times], " e2e step ms:", [round(t, 3) for t in e2e_times], file=sys.stderr)
         line = {
             "metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
