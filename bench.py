@@ -30,6 +30,18 @@ WORKLOAD = "C3: RTiOW final scene (485 spheres, main.cpp generator), 1920x1080, 
 F_RAY = 528.0            # algorithmic flops per ray at N = 485: 48*ceil(log2 N) + 96
 B_RAY = 608.0            # algorithmic L2 bytes per ray at N = 485: 64*ceil(log2 N) + 32
 
+# The other BASELINE.json configs, run through the same step / sharding / timing code with --config
+# (SURVEY.md 8d "C3 / C4 / C5 inputs").  The default (c3) is the headline config of the bench contract.
+#   name: (workload text, width, height, spp, generator half-width g, p_diffuse, p_metal, BVH builder)
+CONFIGS = {
+    "c3": (WORKLOAD, 1920, 1080, 500, 11, 0.8, 0.95, "sah"),
+    "c4": ("C4: 80 % glass/metal final-scene generator (diffuse < 0.2 <= metal < 0.6 <= glass), 1920x1080, 1000 spp, max_depth 50",
+           1920, 1080, 1000, 11, 0.2, 0.6, "sah"),
+    "c5-10k": ("C5: 10 k random spheres (g = 50), 3840x2160, 64 spp, max_depth 50", 3840, 2160, 64, 50, 0.8, 0.95, "lbvh"),
+    "c5-100k": ("C5: 100 k random spheres (g = 159), 3840x2160, 64 spp, max_depth 50", 3840, 2160, 64, 159, 0.8, 0.95, "lbvh"),
+    "c5-1m": ("C5: 1 M random spheres (g = 500), 3840x2160, 64 spp, max_depth 50", 3840, 2160, 64, 500, 0.8, 0.95, "lbvh"),
+}
+
 
 def peaks():
     p = {}
@@ -128,7 +140,8 @@ def main():
     ap.add_argument("--precision", default="f32", choices=["f32", "f64"])
     ap.add_argument("--combine", default="nccl", choices=["nccl", "ipc"])
     ap.add_argument("--variant", default="wavefront", choices=["wavefront", "megakernel", "lockstep"])
-    ap.add_argument("--spp", type=int, default=SPP, help="override spp (a non-default value is NOT the headline config)")
+    ap.add_argument("--config", default="c3", choices=sorted(CONFIGS), help="BASELINE.json config (default c3 = the headline one)")
+    ap.add_argument("--spp", type=int, default=0, help="override spp (a non-default value is NOT the named config)")
     ap.add_argument("--ref-spp", type=int, default=1, help="spp of the CPU sample per step for --impl reference / cpu_baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-check", action="store_true", help="skip the untimed f32-vs-f64 image check")
@@ -156,11 +169,17 @@ def main():
     variant = {"wavefront": rt.WAVEFRONT, "megakernel": rt.MEGAKERNEL, "lockstep": rt.MEGA_LOCKSTEP}[args.variant]
     kernel_name = {"wavefront": "render_pool_kernel", "megakernel": "render_sched_kernel", "lockstep": "render_mega_kernel"}[args.variant]
 
+    workload, W, H, cfg_spp, g, p_diffuse, p_metal, builder = CONFIGS[args.config]
+    headline = args.config == "c3"
+    args.spp = args.spp or cfg_spp
+    builder_id = rt.BVH_LBVH_GPU if builder == "lbvh" else rt.BVH_SAH_HOST
     ctx = rt.Context(local)
-    s, m = rt.scene_rtiow()
-    ctx.upload_scene(s, m)
-    cam = rt.camera_rtiow(WIDTH, args.spp, DEPTH)
-    W, H = WIDTH, 1080
+    s, m = rt.scene_rtiow(g, p_diffuse, p_metal)
+    ctx.upload_scene(s, m, builder=builder_id)
+    cam = rt.camera_rtiow(W, args.spp, DEPTH, scale=g / 11.0)
+    n_spheres = len(s)
+    levels = max(1, int(np.ceil(np.log2(n_spheres))))
+    f_ray, b_ray = 48.0 * levels + 96.0, 64.0 * levels + 32.0          # SURVEY.md 8d, per ray at this N
     stream = torch.cuda.ExternalStream(ctx.stream(), device=torch.device("cuda", local))
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")      # > 126 MB L2
     begin, count = sharding.sample_shard(args.spp, rank, world)
@@ -186,7 +205,7 @@ def main():
     def step(e2e):
         """one frame; returns nothing, everything is enqueued on ctx's stream"""
         if e2e:
-            ctx.upload_scene(s, m)                                   # H2D: the world, every step
+            ctx.upload_scene(s, m, builder=builder_id)               # H2D: the world, every step (BVH build included)
         sharding.render_sharded(ctx, cam, rank, world, prec, variant=variant)
         if world > 1:
             if args.combine == "nccl":
@@ -237,7 +256,7 @@ def main():
 
     # untimed: the fast mode against parity mode on this very frame (north_star image tolerance)
     check = None
-    if rank == 0 and world == 1 and not args.no_check and args.precision == "f32":
+    if rank == 0 and world == 1 and not args.no_check and args.precision == "f32" and headline:
         ctx.render(cam, precision=rt.F32, seed=0, variant=variant); a = ctx.readback(args.spp, want_sum=False)["rgb8"]
         ctx.render(cam, precision=rt.F64, seed=0, variant=rt.MEGAKERNEL); b = ctx.readback(args.spp, want_sum=False)["rgb8"]
         d = np.abs(a.astype(int) - b.astype(int)).max(-1)
@@ -254,7 +273,8 @@ def main():
         rank_rays = rays / world
         sm_mhz = (clocks or {}).get("sm_mhz") or pk.get("sm_max_mhz", 1965.0)
         fp32_peak = 148 * 128 * 2 * sm_mhz * 1e6 / 1e12               # TFLOP/s at the clock seen under load
-        achieved = rank_rays * F_RAY / (kms * 1e-3) / 1e12
+        achieved = rank_rays * f_ray / (kms * 1e-3) / 1e12
+        st_scene = ctx.stats()
         e2e_ms = sum(e2e_times) / len(e2e_times)
         if os.environ.get("RT_BENCH_DEBUG"):
             print("device-resident step ms:", [round(t, 3) for t in times], " e2e step ms:", [round(t, 3) for t in e2e_times], file=sys.stderr)
@@ -262,20 +282,23 @@ def main():
             "metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": args.precision, "data": "synthetic",
-            "config": {"workload": WORKLOAD if args.spp == SPP else f"NOT the headline config: spp={args.spp}",
-                       "variant": args.variant, "bvh": "host SAH, whole scene staged in shared memory", "seed": 0,
+            "config": {"workload": workload if args.spp == cfg_spp else f"NOT the named config: {args.config} at spp={args.spp}",
+                       "variant": args.variant, "n_spheres": n_spheres,
+                       "bvh": ("host SAH" if builder == "sah" else "GPU Morton LBVH") + f", depth {st_scene['bvh_depth']}, " +
+                              ("whole scene staged in shared memory" if st_scene["scene_in_smem"] else "nodes and spheres in global memory (L2 / HBM)"),
+                       "seed": 0,
                        "parallelism": f"sample-range sharding x{world}, combine={args.combine if world > 1 else 'none'}",
-                       "l2": "256 MB buffer written between timed iterations (L2 flushed); scene inputs are 55 KB"},
+                       "l2": f"256 MB buffer written between timed iterations (L2 flushed); scene inputs are {(s.nbytes + m.nbytes) / 1e3:.0f} KB"},
             "mrays_per_s": rays / ms / 1e3, "rays_per_sample": rays / samples,
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak,
                          # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of this kernel on this workload, from the
                          # ncu --set full capture profiles/r1_wavefront_c3_500spp_ncu_summary.txt (13.4 MB + 94.3 MB); the
                          # bounce loop itself reads nothing from HBM (scene staged on chip), this is the accumulator traffic
-                         "traffic": 107.8e6 if (args.variant == "wavefront" and world == 1 and args.spp == SPP and args.precision == "f32") else None,
+                         "traffic": 107.8e6 if (headline and args.variant == "wavefront" and world == 1 and args.spp == SPP and args.precision == "f32") else None,
                          "kernel": kernel_name, "kernel_ms": kms,
-                         "note": f"algorithmic {F_RAY:.0f} flop/ray x {rank_rays:.3e} rays per launch (SURVEY 8d); peak = 148 SMs x 128 "
+                         "note": f"algorithmic {f_ray:.0f} flop/ray x {rank_rays:.3e} rays per launch (SURVEY 8d); peak = 148 SMs x 128 "
                                  f"FP32 lanes x 2 x {sm_mhz:.0f} MHz observed under load (not in MEASURED_PEAKS.json); L2-side figure "
-                                 f"{rank_rays * B_RAY / (kms * 1e-3) / 1e9:.0f} GB/s algorithmic ({B_RAY:.0f} B/ray)"},
+                                 f"{rank_rays * b_ray / (kms * 1e-3) / 1e9:.0f} GB/s algorithmic ({b_ray:.0f} B/ray)"},
             "e2e": {"value": samples / e2e_ms / 1e3, "unit": "Msamples/s", "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": int(s.nbytes + m.nbytes + 104),
                     "d2h_bytes_per_step": int(W * H * 3 + (e2e_out["ppm_len"] if e2e_out else 0)),
@@ -284,7 +307,7 @@ def main():
         }
         if check:
             line["image_check"] = check
-        if not args.no_cpu_baseline and world == 1:
+        if not args.no_cpu_baseline and world == 1 and headline:
             cb = cpu_reference_run(max(1, args.ref_spp), os.cpu_count() or 1)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
         print(json.dumps(line), flush=True)
