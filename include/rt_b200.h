@@ -95,7 +95,7 @@ typedef struct {
 typedef struct {
     uint32_t abi;            /* RT_ABI_VERSION */
     int32_t  builder;        /* RT_BVH_SAH_HOST | RT_BVH_LBVH_GPU */
-    int32_t  max_leaf;       /* spheres per leaf, 1..8 (0 = default 4) */
+    int32_t  max_leaf;       /* spheres per leaf, 1..8 (0 = default: 4 for the host SAH builder, 1 for the GPU LBVH) */
     int32_t  pad;
     double   big_radius;     /* spheres with radius >= this are kept out of the tree and tested first,
                                 in double (the r = 1000 ground sphere; SURVEY.md 7 hard parts 1, 5).

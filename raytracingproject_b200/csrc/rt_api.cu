@@ -259,6 +259,7 @@ extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_s
     if (n_spheres >= (size_t(1) << 28)) return fail(ctx, RT_E_INVALID, "rt_upload_scene: too many spheres");
     const int builder = opts ? opts->builder : RT_BVH_SAH_HOST;
     const int max_leaf = (opts && opts->max_leaf > 0) ? std::min(opts->max_leaf, 8) : 4;
+    const int lbvh_leaf = (opts && opts->max_leaf > 0) ? std::min(opts->max_leaf, 8) : RT_LBVH_DEFAULT_LEAF;
     double big_radius = (opts && opts->big_radius != 0.0) ? opts->big_radius : 100.0;
     if (big_radius < 0) big_radius = INFINITY;
     CK(cudaSetDevice(ctx->device));
@@ -293,7 +294,7 @@ extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_s
         CK(d_boxes.resize(n_tree)); CK(d_order.resize(n_tree)); CK(ctx->nodes.resize(size_t(n_tree - 1) * 4));
         CK(cudaMemcpyAsync(d_boxes.p, boxes.data(), sizeof(HostBox) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
         int root = RT_SENTINEL, depth = 0;
-        cudaError_t e = build_lbvh_gpu(d_boxes.p, n_tree, ctx->nodes.p, d_order.p, &root, &depth, ctx->stream);
+        cudaError_t e = build_lbvh_gpu(d_boxes.p, n_tree, lbvh_leaf, ctx->nodes.p, d_order.p, &root, &depth, ctx->stream);
         if (e != cudaSuccess) { d_boxes.release(); d_order.release(); return cuda_fail(ctx, e, "build_lbvh_gpu"); }
         order.resize(n_tree);
         CK(cudaMemcpyAsync(order.data(), d_order.p, sizeof(int) * n_tree, cudaMemcpyDeviceToHost, ctx->stream));
@@ -393,6 +394,9 @@ template <typename T> int pool_shape_for(const rt_ctx* c, int sched, bool* stage
             if (B < B0 && scene + need(sh) <= budget) { shape = sh; *staged = true; break; }
         }
     }
+    // a scene that stays in global memory is walked at L2 latency: the walk is bound by dependent fetches, not
+    // by issue slots, and the shared memory the scene does not use buys more warps (32 x 128-path pools)
+    if (!*staged && v == 0 && need(RT_POOL_UNSTAGED_SHAPE(T)) <= budget) shape = RT_POOL_UNSTAGED_SHAPE(T);
     if (!*staged && need(shape) > budget) shape = 0;
     return shape;
 }

@@ -56,6 +56,8 @@ template <> cudaError_t launch_render_pool<RT_REAL>(const RenderParams<RT_REAL>&
     RT_POOL_CASE(5, 128, 736);
     RT_POOL_CASE(6, 96, 896);
     RT_POOL_CASE(7, 64, 1024);
+    RT_POOL_CASE(8, 128, 896);
+    RT_POOL_CASE(9, 128, 1024);
     default: RT_POOL_CASE(0, 128, 256);
     }
 #undef RT_POOL_CASE

@@ -44,14 +44,15 @@ template <typename T> __host__ __device__ inline size_t staged_bytes_aligned(int
 }
 
 // SM-resident wavefront (rt_wavefront.cuh): pool of P paths per warp, one CTA of BLOCK threads per SM
-#define RT_POOL_SHAPES 8
+#define RT_POOL_SHAPES 10
 inline void pool_shape(int shape, int* paths, int* block) {
-    const int P[RT_POOL_SHAPES] = { 128, 128, 128, 128, 128, 128, 96, 64 }, B[RT_POOL_SHAPES] = { 256, 512, 640, 768, 704, 736, 896, 1024 };
+    const int P[RT_POOL_SHAPES] = { 128, 128, 128, 128, 128, 128, 96, 64, 128, 128 }, B[RT_POOL_SHAPES] = { 256, 512, 640, 768, 704, 736, 896, 1024, 896, 1024 };
     if (shape < 0 || shape >= RT_POOL_SHAPES) shape = 0;
     *paths = P[shape]; *block = B[shape];
 }
 template <typename T> inline size_t pool_warp_bytes(int paths) { return size_t(paths) * (11 * sizeof(T) + 4 + 2 * 2 + 4); }
 #define RT_POOL_DEFAULT_SHAPE(T) (sizeof(T) == 4 ? 3 : 0)
+#define RT_POOL_UNSTAGED_SHAPE(T) (sizeof(T) == 4 ? 9 : 0)
 template <typename T> cudaError_t launch_render_pool(const RenderParams<T>& p, int shape, bool staged, int sm_count, cudaStream_t st);
 
 template <typename T> cudaError_t launch_render_mega(const RenderParams<T>& p, bool staged, size_t smem_bytes, int sm_count, cudaStream_t st);

@@ -10,7 +10,11 @@
 //                                 index as tie-break for duplicate codes
 //   5. refit + emit               bottom-up from the leaves, the second thread to arrive at a node (atomic
 //                                 flag) unites its children and writes the 64-byte traversal record
-//                                 (rt_trace.cuh layout: boxes of BOTH children + refs); depth rides along
+//                                 (rt_trace.cuh layout: boxes of BOTH children + refs); depth rides along.
+//                                 A subtree of <= max_leaf spheres is one contiguous range of sorted slots, so
+//                                 the parent refers to it as ONE leaf (first slot, count): the walk over a
+//                                 tree in global memory is bound by dependent fetches, and this cuts the last
+//                                 one or two levels of them (its own records are still written, never reached)
 #include "rt_lbvh.h"
 
 #include <cub/cub.cuh>
@@ -91,7 +95,8 @@ __device__ __forceinline__ int delta(const unsigned long long* __restrict__ keys
 // children: >= 0 inner node, < 0 leaf ~(slot << 3)  (one sphere per leaf)
 __global__ void __launch_bounds__(256) lbvh_hierarchy(const unsigned long long* __restrict__ keys, int n,
                                                       int* __restrict__ left, int* __restrict__ right,
-                                                      int* __restrict__ parent_inner, int* __restrict__ parent_leaf) {
+                                                      int* __restrict__ parent_inner, int* __restrict__ parent_leaf,
+                                                      int2* __restrict__ range) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n - 1) return;
     const int d = delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1) >= 0 ? 1 : -1;
@@ -113,6 +118,7 @@ __global__ void __launch_bounds__(256) lbvh_hierarchy(const unsigned long long* 
     const int cl = lo == gamma ? ~(gamma << 3) : gamma;
     const int cr = hi == gamma + 1 ? ~((gamma + 1) << 3) : gamma + 1;
     left[i] = cl; right[i] = cr;
+    range[i] = make_int2(lo, hi - lo + 1);
     if (cl >= 0) parent_inner[cl] = i; else parent_leaf[gamma] = i;
     if (cr >= 0) parent_inner[cr] = i; else parent_leaf[gamma + 1] = i;
     if (i == 0) parent_inner[0] = -1;
@@ -129,6 +135,7 @@ __device__ __forceinline__ void unite(NodeBox& a, const NodeBox& b) {
 __global__ void __launch_bounds__(256) lbvh_refit(const HostBox* __restrict__ boxes, const int* __restrict__ vals, int n,
                                                   const int* __restrict__ left, const int* __restrict__ right,
                                                   const int* __restrict__ parent_inner, const int* __restrict__ parent_leaf,
+                                                  const int2* __restrict__ range, int max_leaf,
                                                   int* __restrict__ flags, NodeBox* __restrict__ nbox,
                                                   float4* __restrict__ nodes, int* __restrict__ order, int* __restrict__ root_depth) {
     const int s = blockIdx.x * blockDim.x + threadIdx.x;
@@ -139,11 +146,14 @@ __global__ void __launch_bounds__(256) lbvh_refit(const HostBox* __restrict__ bo
         if (atomicAdd(&flags[node], 1) == 0) return;            // first to arrive: the sibling subtree is not ready
         __threadfence();
         NodeBox cb[2];
-        const int c[2] = { left[node], right[node] };
+        int c[2] = { left[node], right[node] };
 #pragma unroll
         for (int k = 0; k < 2; ++k) {
-            if (c[k] >= 0) cb[k] = nbox[c[k]];
-            else {
+            if (c[k] >= 0) {
+                cb[k] = nbox[c[k]];
+                const int2 r = range[c[k]];
+                if (r.y <= max_leaf) { c[k] = ~((r.x << 3) | (r.y - 1)); cb[k].depth = 0; }     // small subtree -> one leaf
+            } else {
                 const HostBox b = boxes[vals[(~c[k]) >> 3]];
                 for (int a = 0; a < 3; ++a) { cb[k].lo[a] = b.lo[a]; cb[k].hi[a] = b.hi[a]; }
                 cb[k].depth = 0;
@@ -164,8 +174,10 @@ __global__ void __launch_bounds__(256) lbvh_refit(const HostBox* __restrict__ bo
 
 }  // namespace
 
-cudaError_t build_lbvh_gpu(const HostBox* d_boxes, int n, float4* d_nodes, int* d_order, int* root_ref, int* depth, cudaStream_t st) {
+cudaError_t build_lbvh_gpu(const HostBox* d_boxes, int n, int max_leaf, float4* d_nodes, int* d_order, int* root_ref, int* depth, cudaStream_t st) {
     if (n < 2) return cudaErrorInvalidValue;
+    max_leaf = max_leaf < 1 ? 1 : (max_leaf > 8 ? 8 : max_leaf);
+    int2* range = nullptr;
     cudaError_t e;
     unsigned long long *keys = nullptr, *keys_sorted = nullptr;
     int *vals = nullptr, *vals_sorted = nullptr, *ints = nullptr;
@@ -176,12 +188,13 @@ cudaError_t build_lbvh_gpu(const HostBox* d_boxes, int n, float4* d_nodes, int* 
     // ints: left | right | parent_inner | parent_leaf(n) | flags | root_depth
     const size_t ni = size_t(n - 1) * 4 + size_t(n) + 1;
     auto cleanup = [&]() {
-        cudaFree(keys); cudaFree(keys_sorted); cudaFree(vals); cudaFree(vals_sorted); cudaFree(ints); cudaFree(nbox); cudaFree(bounds); cudaFree(tmp);
+        cudaFree(keys); cudaFree(keys_sorted); cudaFree(vals); cudaFree(vals_sorted); cudaFree(ints); cudaFree(nbox); cudaFree(bounds); cudaFree(tmp); cudaFree(range);
     };
 #define LB(call) do { e = (call); if (e != cudaSuccess) { cleanup(); return e; } } while (0)
     LB(cudaMalloc(&keys, sizeof(*keys) * n)); LB(cudaMalloc(&keys_sorted, sizeof(*keys) * n));
     LB(cudaMalloc(&vals, sizeof(int) * n)); LB(cudaMalloc(&vals_sorted, sizeof(int) * n));
     LB(cudaMalloc(&ints, sizeof(int) * ni)); LB(cudaMalloc(&nbox, sizeof(NodeBox) * (n - 1))); LB(cudaMalloc(&bounds, sizeof(Bounds)));
+    LB(cudaMalloc(&range, sizeof(int2) * (n - 1)));
     LB(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys_sorted, vals, vals_sorted, n, 0, 63, st));
     LB(cudaMalloc(&tmp, tmp_bytes ? tmp_bytes : 1));
     int* left = ints; int* right = left + (n - 1); int* parent_inner = right + (n - 1); int* parent_leaf = parent_inner + (n - 1);
@@ -193,8 +206,8 @@ cudaError_t build_lbvh_gpu(const HostBox* d_boxes, int n, float4* d_nodes, int* 
     lbvh_centroid_bounds<<<min(nb, 1184), 256, 0, st>>>(d_boxes, n, bounds);
     lbvh_morton<<<nb, 256, 0, st>>>(d_boxes, n, bounds, keys, vals);
     LB(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys_sorted, vals, vals_sorted, n, 0, 63, st));
-    lbvh_hierarchy<<<(n - 1 + 255) / 256, 256, 0, st>>>(keys_sorted, n, left, right, parent_inner, parent_leaf);
-    lbvh_refit<<<nb, 256, 0, st>>>(d_boxes, vals_sorted, n, left, right, parent_inner, parent_leaf, flags, nbox, d_nodes, d_order, root_depth);
+    lbvh_hierarchy<<<(n - 1 + 255) / 256, 256, 0, st>>>(keys_sorted, n, left, right, parent_inner, parent_leaf, range);
+    lbvh_refit<<<nb, 256, 0, st>>>(d_boxes, vals_sorted, n, left, right, parent_inner, parent_leaf, range, max_leaf, flags, nbox, d_nodes, d_order, root_depth);
     LB(cudaGetLastError());
     int h_depth = 0;
     LB(cudaMemcpyAsync(&h_depth, root_depth, sizeof(int), cudaMemcpyDeviceToHost, st));
