@@ -17,6 +17,7 @@
 #include "rt_frame.h"
 #include "rt_kernels.cuh"
 #include "rt_lbvh.h"
+#include "rt_scene.h"
 
 using namespace rt;
 
@@ -43,6 +44,10 @@ template <typename T> struct DevBuf {
         return e;
     }
     void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+    DevBuf() = default;
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+    ~DevBuf() { release(); }             // scratch buffers on an early error return
 };
 
 }  // namespace
@@ -279,41 +284,13 @@ extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_s
         if (std::fabs(spheres[i].radius) >= big_radius && big_ids.size() < 16) big_ids.push_back(int(i));
         else tree_ids.push_back(int(i));
     }
-    std::vector<HostBox> boxes(tree_ids.size());
-    for (size_t k = 0; k < tree_ids.size(); ++k) {
-        const rt_sphere& s = spheres[tree_ids[k]];
-        boxes[k] = sphere_box(s.center1, s.center_vec, s.radius, s.is_moving != 0);
-    }
-
-    const auto t_build = std::chrono::steady_clock::now();
-    HostBVH bvh;
-    std::vector<int> order;               // slot -> index into tree_ids
     const int n_tree = int(tree_ids.size());
-    if (builder == RT_BVH_LBVH_GPU && n_tree >= 2) {
-        DevBuf<HostBox> d_boxes; DevBuf<int> d_order;
-        CK(d_boxes.resize(n_tree)); CK(d_order.resize(n_tree)); CK(ctx->nodes.resize(size_t(n_tree - 1) * 4));
-        CK(cudaMemcpyAsync(d_boxes.p, boxes.data(), sizeof(HostBox) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
-        int root = RT_SENTINEL, depth = 0;
-        cudaError_t e = build_lbvh_gpu(d_boxes.p, n_tree, lbvh_leaf, ctx->nodes.p, d_order.p, &root, &depth, ctx->stream);
-        if (e != cudaSuccess) { d_boxes.release(); d_order.release(); return cuda_fail(ctx, e, "build_lbvh_gpu"); }
-        order.resize(n_tree);
-        CK(cudaMemcpyAsync(order.data(), d_order.p, sizeof(int) * n_tree, cudaMemcpyDeviceToHost, ctx->stream));
-        CK(cudaStreamSynchronize(ctx->stream));
-        d_boxes.release(); d_order.release();
-        if (depth > RT_STACK) return fail(ctx, RT_E_INVALID, "rt_upload_scene: LBVH deeper than the traversal stack");
-        ctx->root_ref = root; ctx->depth = depth; ctx->n_nodes = n_tree - 1;
-    } else {
-        build_bvh_sah(boxes, max_leaf, bvh);
-        order = bvh.order;
-        if (bvh.depth > RT_STACK) return fail(ctx, RT_E_INVALID, "rt_upload_scene: BVH deeper than the traversal stack");
-        ctx->root_ref = bvh.root_ref; ctx->depth = bvh.depth; ctx->n_nodes = bvh.n_inner;
-        CK(ctx->nodes.resize(std::max<size_t>(1, size_t(bvh.n_inner) * 4)));
-        if (bvh.n_inner)
-            CK(cudaMemcpyAsync(ctx->nodes.p, bvh.nodes.data(), bvh.nodes.size() * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
-    }
-    ctx->build_ms = ms_since(t_build);
+    const size_t nt = std::max(1, n_tree), nb = std::max<size_t>(1, big_ids.size());
+    CK(ctx->sa32.resize(nt)); CK(ctx->sb32.resize(nt)); CK(ctx->sc32.resize(nt));
+    CK(ctx->sa64.resize(nt)); CK(ctx->sb64.resize(nt)); CK(ctx->sc64.resize(nt)); CK(ctx->meta.resize(nt));
+    CK(ctx->big_a.resize(nb)); CK(ctx->big_b.resize(nb)); CK(ctx->big_c.resize(nb)); CK(ctx->big_meta.resize(nb));
 
-    // SoA slots in leaf order
+    // SoA slots (host form): a = (center1, r), b = (center_vec, r^2), c = (albedo, param), meta
     auto fill = [&](const std::vector<int>& ids, std::vector<double4>& a, std::vector<double4>& b, std::vector<double4>& c, std::vector<int>& m) {
         a.resize(ids.size()); b.resize(ids.size()); c.resize(ids.size()); m.resize(ids.size());
         for (size_t k = 0; k < ids.size(); ++k) {
@@ -328,37 +305,78 @@ extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_s
             m[k] = (ids[k] << 3) | (mov ? 4 : 0) | mt.type;
         }
     };
-    std::vector<int> slot_ids(n_tree);
-    for (int k = 0; k < n_tree; ++k) slot_ids[k] = tree_ids[order[k]];
-    std::vector<double4> a64, b64, c64, ba, bb, bc;
-    std::vector<int> meta, bmeta;
-    fill(slot_ids, a64, b64, c64, meta);
-    fill(big_ids, ba, bb, bc, bmeta);
-    std::vector<float4> a32(n_tree), b32(n_tree), c32(n_tree);
-    for (int k = 0; k < n_tree; ++k) {
-        a32[k] = make_float4(float(a64[k].x), float(a64[k].y), float(a64[k].z), float(a64[k].w));
-        const float r = a32[k].w;
-        b32[k] = make_float4(float(b64[k].x), float(b64[k].y), float(b64[k].z), r * r);
-        c32[k] = make_float4(float(c64[k].x), float(c64[k].y), float(c64[k].z), float(c64[k].w));
+
+    const auto t_build = std::chrono::steady_clock::now();
+    if (builder == RT_BVH_LBVH_GPU && n_tree >= 2) {
+        // Device path (large scenes): the caller's AoS arrays go to the device as they are; boxes, tree and
+        // the SoA slots in leaf order are made there (rt_scene.cu) -- no per-sphere host loop after the split
+        DevBuf<rt_sphere> d_sph; DevBuf<rt_material> d_mat; DevBuf<int> d_ids; DevBuf<HostBox> d_boxes; DevBuf<int> d_order;
+        CK(d_sph.resize(n_spheres)); CK(d_mat.resize(n_materials)); CK(d_ids.resize(n_tree));
+        CK(d_boxes.resize(n_tree)); CK(d_order.resize(n_tree)); CK(ctx->nodes.resize(size_t(n_tree - 1) * 4));
+        CK(cudaMemcpyAsync(d_sph.p, spheres, sizeof(rt_sphere) * n_spheres, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(d_mat.p, materials, sizeof(rt_material) * n_materials, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(d_ids.p, tree_ids.data(), sizeof(int) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
+        cudaError_t e = launch_scene_boxes(d_sph.p, d_ids.p, n_tree, d_boxes.p, ctx->stream);
+        int root = RT_SENTINEL, depth = 0;
+        if (e == cudaSuccess) e = build_lbvh_gpu(d_boxes.p, n_tree, lbvh_leaf, ctx->nodes.p, d_order.p, &root, &depth, ctx->stream);
+        if (e == cudaSuccess) e = launch_scene_fill(d_sph.p, d_mat.p, d_ids.p, d_order.p, n_tree, ctx->sa32.p, ctx->sb32.p, ctx->sc32.p,
+                                                    ctx->sa64.p, ctx->sb64.p, ctx->sc64.p, ctx->meta.p, ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        d_sph.release(); d_mat.release(); d_ids.release(); d_boxes.release(); d_order.release();
+        if (e != cudaSuccess) return cuda_fail(ctx, e, "rt_upload_scene: device scene build");
+        if (depth > RT_STACK) return fail(ctx, RT_E_INVALID, "rt_upload_scene: LBVH deeper than the traversal stack");
+        ctx->root_ref = root; ctx->depth = depth; ctx->n_nodes = n_tree - 1;
+        ctx->build_ms = ms_since(t_build);
+    } else {
+        std::vector<HostBox> boxes(tree_ids.size());
+        for (size_t k = 0; k < tree_ids.size(); ++k) {
+            const rt_sphere& s = spheres[tree_ids[k]];
+            boxes[k] = sphere_box(s.center1, s.center_vec, s.radius, s.is_moving != 0);
+        }
+        HostBVH bvh;
+        build_bvh_sah(boxes, max_leaf, bvh);
+        if (bvh.depth > RT_STACK) return fail(ctx, RT_E_INVALID, "rt_upload_scene: BVH deeper than the traversal stack");
+        ctx->root_ref = bvh.root_ref; ctx->depth = bvh.depth; ctx->n_nodes = bvh.n_inner;
+        CK(ctx->nodes.resize(std::max<size_t>(1, size_t(bvh.n_inner) * 4)));
+        if (bvh.n_inner)
+            CK(cudaMemcpyAsync(ctx->nodes.p, bvh.nodes.data(), bvh.nodes.size() * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+        ctx->build_ms = ms_since(t_build);
+
+        // SoA slots in leaf order
+        std::vector<int> slot_ids(n_tree);
+        for (int k = 0; k < n_tree; ++k) slot_ids[k] = tree_ids[bvh.order[k]];
+        std::vector<double4> a64, b64, c64;
+        std::vector<int> meta;
+        fill(slot_ids, a64, b64, c64, meta);
+        std::vector<float4> a32(n_tree), b32(n_tree), c32(n_tree);
+        for (int k = 0; k < n_tree; ++k) {
+            a32[k] = make_float4(float(a64[k].x), float(a64[k].y), float(a64[k].z), float(a64[k].w));
+            const float r = a32[k].w;
+            b32[k] = make_float4(float(b64[k].x), float(b64[k].y), float(b64[k].z), r * r);
+            c32[k] = make_float4(float(c64[k].x), float(c64[k].y), float(c64[k].z), float(c64[k].w));
+        }
+        if (n_tree) {
+            CK(cudaMemcpyAsync(ctx->sa32.p, a32.data(), sizeof(float4) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
+            CK(cudaMemcpyAsync(ctx->sb32.p, b32.data(), sizeof(float4) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
+            CK(cudaMemcpyAsync(ctx->sc32.p, c32.data(), sizeof(float4) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
+            CK(cudaMemcpyAsync(ctx->sa64.p, a64.data(), sizeof(double4) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
+            CK(cudaMemcpyAsync(ctx->sb64.p, b64.data(), sizeof(double4) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
+            CK(cudaMemcpyAsync(ctx->sc64.p, c64.data(), sizeof(double4) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
+            CK(cudaMemcpyAsync(ctx->meta.p, meta.data(), sizeof(int) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
+            CK(cudaStreamSynchronize(ctx->stream));               // the staging vectors go out of scope
+        }
     }
-    const size_t nt = std::max(1, n_tree), nb = std::max<size_t>(1, big_ids.size());
-    CK(ctx->sa32.resize(nt)); CK(ctx->sb32.resize(nt)); CK(ctx->sc32.resize(nt));
-    CK(ctx->sa64.resize(nt)); CK(ctx->sb64.resize(nt)); CK(ctx->sc64.resize(nt)); CK(ctx->meta.resize(nt));
-    CK(ctx->big_a.resize(nb)); CK(ctx->big_b.resize(nb)); CK(ctx->big_c.resize(nb)); CK(ctx->big_meta.resize(nb));
-    if (n_tree) {
-        CK(cudaMemcpyAsync(ctx->sa32.p, a32.data(), sizeof(float4) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
-        CK(cudaMemcpyAsync(ctx->sb32.p, b32.data(), sizeof(float4) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
-        CK(cudaMemcpyAsync(ctx->sc32.p, c32.data(), sizeof(float4) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
-        CK(cudaMemcpyAsync(ctx->sa64.p, a64.data(), sizeof(double4) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
-        CK(cudaMemcpyAsync(ctx->sb64.p, b64.data(), sizeof(double4) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
-        CK(cudaMemcpyAsync(ctx->sc64.p, c64.data(), sizeof(double4) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
-        CK(cudaMemcpyAsync(ctx->meta.p, meta.data(), sizeof(int) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
-    }
-    if (!big_ids.empty()) {
-        CK(cudaMemcpyAsync(ctx->big_a.p, ba.data(), sizeof(double4) * ba.size(), cudaMemcpyHostToDevice, ctx->stream));
-        CK(cudaMemcpyAsync(ctx->big_b.p, bb.data(), sizeof(double4) * bb.size(), cudaMemcpyHostToDevice, ctx->stream));
-        CK(cudaMemcpyAsync(ctx->big_c.p, bc.data(), sizeof(double4) * bc.size(), cudaMemcpyHostToDevice, ctx->stream));
-        CK(cudaMemcpyAsync(ctx->big_meta.p, bmeta.data(), sizeof(int) * bmeta.size(), cudaMemcpyHostToDevice, ctx->stream));
+    {
+        std::vector<double4> ba, bb, bc;
+        std::vector<int> bmeta;
+        fill(big_ids, ba, bb, bc, bmeta);
+        if (!big_ids.empty()) {
+            CK(cudaMemcpyAsync(ctx->big_a.p, ba.data(), sizeof(double4) * ba.size(), cudaMemcpyHostToDevice, ctx->stream));
+            CK(cudaMemcpyAsync(ctx->big_b.p, bb.data(), sizeof(double4) * bb.size(), cudaMemcpyHostToDevice, ctx->stream));
+            CK(cudaMemcpyAsync(ctx->big_c.p, bc.data(), sizeof(double4) * bc.size(), cudaMemcpyHostToDevice, ctx->stream));
+            CK(cudaMemcpyAsync(ctx->big_meta.p, bmeta.data(), sizeof(int) * bmeta.size(), cudaMemcpyHostToDevice, ctx->stream));
+            CK(cudaStreamSynchronize(ctx->stream));
+        }
     }
     CK(cudaStreamSynchronize(ctx->stream));
     ctx->n_spheres = int(n_spheres); ctx->n_slots = n_tree; ctx->n_big = int(big_ids.size());
@@ -883,7 +901,7 @@ extern "C" int rt_encode_p3(rt_ctx* ctx, const uint8_t* rgb8, int width, int hei
     hdr.len = std::snprintf(hdr.text, sizeof hdr.text, "P3\n%d %d\n255\n", width, height);
     const int nb = encode_blocks(npix);
     DevBuf<unsigned char> d_b; DevBuf<unsigned> d_s; DevBuf<unsigned long long> d_o; DevBuf<char> d_t;
-    CK(d_b.resize(3 * npix)); CK(d_s.resize(nb + 1)); CK(d_o.resize(nb + 2)); CK(d_t.resize(npix * 12 + 64));
+    CK(d_b.resize(3 * npix + 16)); CK(d_s.resize(nb + 1)); CK(d_o.resize(nb + 2)); CK(d_t.resize(npix * 12 + 64));
     CK(cudaMemcpyAsync(d_b.p, rgb8, 3 * npix, cudaMemcpyHostToDevice, ctx->stream));
     unsigned long long len = 0;
     cudaError_t e = launch_encode_p3(d_b.p, npix, hdr, d_s.p, d_o.p, d_o.p + nb + 1, d_t.p, ctx->stream);

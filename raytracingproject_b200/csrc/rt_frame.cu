@@ -116,11 +116,26 @@ __device__ __forceinline__ unsigned block_exclusive_scan(unsigned v, unsigned* w
     return base + x - v;
 }
 
+// the ENC_PPT = 4 pixels of a thread are 12 consecutive bytes at a 4-byte aligned address: three 32-bit loads
+// (a warp reads 384 contiguous bytes) instead of twelve byte loads.  The caller's rgb8 buffer is padded by
+// >= 12 bytes, so the last thread may read past pixel n_pixels - 1; it never uses those bytes.
+__device__ __forceinline__ void load_pixels(const unsigned char* __restrict__ rgb8, size_t p0, unsigned char px[12]) {
+    const unsigned* w = reinterpret_cast<const unsigned*>(rgb8 + 3 * p0);
+    const unsigned a = w[0], b = w[1], c = w[2];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { px[k] = (unsigned char)(a >> (8 * k)); px[4 + k] = (unsigned char)(b >> (8 * k)); px[8 + k] = (unsigned char)(c >> (8 * k)); }
+}
+
 __global__ void __launch_bounds__(ENC_BLOCK) encode_count_kernel(const unsigned char* __restrict__ rgb8, size_t n_pixels, unsigned* __restrict__ block_sums) {
     __shared__ unsigned warp_sums[ENC_BLOCK / 32];
     const size_t p0 = size_t(blockIdx.x) * ENC_TILE + size_t(threadIdx.x) * ENC_PPT;
     unsigned len = 0;
-    for (int k = 0; k < ENC_PPT; ++k) if (p0 + k < n_pixels) len += line_len(rgb8 + 3 * (p0 + k));
+    if (p0 < n_pixels) {
+        unsigned char px[12];
+        load_pixels(rgb8, p0, px);
+#pragma unroll
+        for (int k = 0; k < ENC_PPT; ++k) if (p0 + k < n_pixels) len += line_len(px + 3 * k);
+    }
     unsigned total;
     block_exclusive_scan(len, warp_sums, total);
     if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
@@ -151,26 +166,47 @@ __device__ __forceinline__ int put_number(char* dst, unsigned v) {
     return n;
 }
 
+// The block's text is staged in shared memory at the SAME 16-byte misalignment its destination has, so that
+// every aligned 16-byte chunk of the destination is an aligned 16-byte chunk of the stage: the body goes out
+// as 128-bit stores (512 contiguous bytes per warp instruction), only the ragged head and tail byte by byte.
 __global__ void __launch_bounds__(ENC_BLOCK) encode_write_kernel(const unsigned char* __restrict__ rgb8, size_t n_pixels,
                                                                    const unsigned long long* __restrict__ block_offsets,
                                                                    char* __restrict__ text, EncodeHeader hdr) {
     __shared__ unsigned warp_sums[ENC_BLOCK / 32];
-    __shared__ char stage[ENC_TILE * 12];
+    __shared__ __align__(16) char stage[ENC_TILE * 12 + 16];
     const size_t p0 = size_t(blockIdx.x) * ENC_TILE + size_t(threadIdx.x) * ENC_PPT;
+    unsigned char px[12];
     unsigned len = 0;
-    for (int k = 0; k < ENC_PPT; ++k) if (p0 + k < n_pixels) len += line_len(rgb8 + 3 * (p0 + k));
+    if (p0 < n_pixels) {
+        load_pixels(rgb8, p0, px);
+#pragma unroll
+        for (int k = 0; k < ENC_PPT; ++k) if (p0 + k < n_pixels) len += line_len(px + 3 * k);
+    }
     unsigned total;
-    unsigned off = block_exclusive_scan(len, warp_sums, total);
-    for (int k = 0; k < ENC_PPT; ++k) {
-        if (p0 + k >= n_pixels) break;
-        const unsigned char* px = rgb8 + 3 * (p0 + k);
-        off += put_number(stage + off, px[0]); stage[off++] = ' ';
-        off += put_number(stage + off, px[1]); stage[off++] = ' ';
-        off += put_number(stage + off, px[2]); stage[off++] = '\n';
+    char* dst = text + block_offsets[blockIdx.x];
+    const unsigned mis = unsigned(reinterpret_cast<unsigned long long>(dst) & 15ull);
+    unsigned off = mis + block_exclusive_scan(len, warp_sums, total);
+    if (p0 < n_pixels) {
+#pragma unroll
+        for (int k = 0; k < ENC_PPT; ++k) {
+            if (p0 + k >= n_pixels) break;
+            off += put_number(stage + off, px[3 * k + 0]); stage[off++] = ' ';
+            off += put_number(stage + off, px[3 * k + 1]); stage[off++] = ' ';
+            off += put_number(stage + off, px[3 * k + 2]); stage[off++] = '\n';
+        }
     }
     __syncthreads();
-    char* dst = text + block_offsets[blockIdx.x];
-    for (unsigned i = threadIdx.x; i < total; i += ENC_BLOCK) dst[i] = stage[i];
+    const unsigned begin = mis, end = mis + total;
+    const unsigned c0 = (begin + 15u) >> 4, c1 = end >> 4;              // full 16-byte chunks [c0, c1)
+    char* dst0 = dst - mis;                                             // 16-byte aligned
+    if (c0 < c1) {
+        for (unsigned c = c0 + threadIdx.x; c < c1; c += ENC_BLOCK)
+            reinterpret_cast<uint4*>(dst0)[c] = reinterpret_cast<const uint4*>(stage)[c];
+        for (unsigned i = begin + threadIdx.x; i < c0 * 16u; i += ENC_BLOCK) dst0[i] = stage[i];
+        for (unsigned i = c1 * 16u + threadIdx.x; i < end; i += ENC_BLOCK) dst0[i] = stage[i];
+    } else {
+        for (unsigned i = begin + threadIdx.x; i < end; i += ENC_BLOCK) dst0[i] = stage[i];
+    }
     if (blockIdx.x == 0 && threadIdx.x < hdr.len) text[threadIdx.x] = hdr.text[threadIdx.x];   // "P3\nW H\n255\n"
 }
 

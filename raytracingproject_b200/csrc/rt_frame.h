@@ -28,6 +28,7 @@ cudaError_t launch_resolve(const Q* accum, int slices, const PeerList& peers, si
                            const FrameViews& views = FrameViews{nullptr, nullptr, 0, 0});
 
 int encode_blocks(size_t n_pixels);
+// rgb8 must be readable up to 12 bytes past its last pixel (32-bit loads of 4-pixel groups)
 cudaError_t launch_encode_p3(const unsigned char* rgb8, size_t n_pixels, const EncodeHeader& hdr, unsigned* block_sums,
                              unsigned long long* block_offsets, unsigned long long* total_len, char* text, cudaStream_t st);
 

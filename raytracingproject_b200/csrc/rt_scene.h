@@ -1,0 +1,21 @@
+// rt_scene.h -- device-side scene preparation for large worlds (GPU LBVH path of rt_upload_scene):
+// sphere boxes and the tagged SoA slots in leaf order, made from the caller's AoS arrays on the device.
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include "../../include/rt_b200.h"
+#include "rt_bvh_host.h"
+
+namespace rt {
+
+// boxes[k] = sphere_box(spheres[ids[k]]) -- bit-identical to the host function (rt_bvh_host.cpp)
+cudaError_t launch_scene_boxes(const rt_sphere* spheres, const int* ids, int n, HostBox* boxes, cudaStream_t st);
+
+// slot s holds sphere ids[order[s]]: a = (center1, r), b = (center_vec, r^2), c = (albedo, param), in double and
+// float, meta = list_index << 3 | moving << 2 | material tag -- the same values the host fill of rt_upload_scene writes
+cudaError_t launch_scene_fill(const rt_sphere* spheres, const rt_material* materials, const int* ids, const int* order, int n,
+                              float4* a32, float4* b32, float4* c32, double4* a64, double4* b64, double4* c64, int* meta,
+                              cudaStream_t st);
+
+}  // namespace rt
