@@ -192,7 +192,7 @@ def main():
     # warm-up render so buffers exist, then set up the combine
     sharding.render_sharded(ctx, cam, rank, world, prec, variant=variant)
     ctx.synchronize()
-    acc = sharding.alias_accum_tensor(ctx) if world > 1 else None
+    acc = sharding.alias_accum_tensor(ctx, layers=1) if world > 1 else None      # layer 0: the rank's partial sum after fold_slices
     if world > 1 and args.combine == "ipc":
         handles = sharding.exchange_ipc_handles(ctx.ipc_export())
         if rank == 0:
@@ -208,6 +208,7 @@ def main():
             ctx.upload_scene(s, m, builder=builder_id)               # H2D: the world, every step (BVH build included)
         sharding.render_sharded(ctx, cam, rank, world, prec, variant=variant)
         if world > 1:
+            ctx.fold_slices()                                        # one [H][W] layer per rank crosses NVLink, not `slices` of them
             if args.combine == "nccl":
                 with torch.cuda.stream(stream):
                     sharding.reduce_partials(acc, dst=0)

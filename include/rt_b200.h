@@ -187,8 +187,14 @@ int rt_debug_counters(rt_ctx *ctx, uint64_t out[32]);
 
 /* Device pointer / geometry of the accumulation buffer so the host framework can reduce it
  * across ranks (NCCL) or map it into a peer (CUDA IPC).  elem_bytes 4 (RT_F32, float4 per
- * pixel) or 8 (RT_F64, double4 per pixel); n_elems = W*H*4. */
+ * pixel) or 8 (RT_F64, double4 per pixel); n_elems = slices*W*H*4
+ * (layer-major: the first W*H*4 elements are layer 0). */
 int rt_accum_buffer(rt_ctx *ctx, void **dev_ptr, size_t *n_elems, int *elem_bytes);
+/* Sums the sample layers (rt_render_opts.slices) of the accumulation buffer into layer 0 and zeroes
+ * the others, on the context's stream: after it the first W*H*4 elements are this rank's whole partial
+ * sum, so one layer per rank crosses NVLink in the combine.  Every rank of a combine calls it (the
+ * fused resolve then reads layer 0 of each peer only).  The next rt_render ends the folded state. */
+int rt_fold_slices(rt_ctx *ctx);
 int rt_stream(rt_ctx *ctx, void **cuda_stream);
 /* CUDA IPC handle (64 bytes) of the accumulation buffer, and the fused peer reduce + resolve:
  * rank 0 reads every peer's partial buffer over NVLink inside the resolve kernel. */

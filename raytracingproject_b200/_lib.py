@@ -71,6 +71,7 @@ SYMBOLS = {
     "rt_get_stats": (_I, [_VP, _VP]),
     "rt_accum_buffer": (_I, [_VP, _VP, _VP, _VP]),
     "rt_stream": (_I, [_VP, _VP]),
+    "rt_fold_slices": (_I, [_VP]),
     "rt_ipc_export": (_I, [_VP, _VP]),
     "rt_ipc_open_peers": (_I, [_VP, _VP, _I]),
     "rt_ipc_close_peers": (_I, [_VP]),

@@ -193,6 +193,10 @@ class Context:
         self._ck(self._lib.rt_accum_buffer(self._h, C.byref(p), C.byref(n), C.byref(e)))
         return p.value, n.value, e.value
 
+    def fold_slices(self):
+        """Sum the sample layers into layer 0 (asynchronous); the combine then moves one layer per rank."""
+        self._ck(self._lib.rt_fold_slices(self._h))
+
     def stream(self):
         p = C.c_void_p()
         self._ck(self._lib.rt_stream(self._h, C.byref(p)))

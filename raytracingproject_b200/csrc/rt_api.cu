@@ -69,6 +69,7 @@ struct rt_ctx {
 
     // frame
     int W = 0, H = 0, slices = 0, precision = -1;
+    bool folded = false;                    // rt_fold_slices ran since the last render: only layer 0 (here and in the peers) holds data
     long long samples_in_buffer = 0;
     DevBuf<unsigned char> accum;            // Quad<T>[slices][H][W]
     DevBuf<unsigned char> reduced;          // Quad<T>[H][W] (after peer reduce, for rt_accum_buffer consumers)
@@ -95,6 +96,13 @@ namespace {
 int fail(rt_ctx* c, int code, const std::string& msg) { if (c) c->err = msg; else g_create_error = msg; return code; }
 int cuda_fail(rt_ctx* c, cudaError_t e, const char* what) {
     return fail(c, RT_E_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+// layers the resolve pass has to read: all of them, or layer 0 alone after rt_fold_slices (every rank folds)
+int live_slices(const rt_ctx* c) { return c->folded ? 1 : c->slices; }
+PeerList live_peers(const rt_ctx* c) {
+    PeerList p = c->peers;
+    if (c->folded) for (int i = 0; i < p.n; ++i) p.slices[i] = 1;
+    return p;
 }
 #define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return cuda_fail(ctx, e_, #call); } while (0)
 
@@ -466,11 +474,11 @@ extern "C" int rt_render(rt_ctx* ctx, const rt_camera* cam, const rt_render_opts
     if (cam->image_width < 1 || !(cam->aspect_ratio > 0)) return fail(ctx, RT_E_INVALID, "rt_render: bad image size");
     if (opts->precision != RT_F32 && opts->precision != RT_F64) return fail(ctx, RT_E_INVALID, "rt_render: bad precision");
     if (opts->variant != RT_MEGAKERNEL && opts->variant != RT_MEGA_LOCKSTEP && opts->variant != RT_WAVEFRONT) return fail(ctx, RT_E_INVALID, "rt_render: variant not built");
-    // the wavefront pool keeps a path's sample index and remaining depth in 16 bits: beyond that the
+    // the wavefront pool keeps a path's sample index in 15 bits and its remaining depth in 16: beyond that the
     // warp-scheduled megakernel (same arithmetic, same image) takes the call
     rt_render_opts eff = *opts;
     if (eff.variant == RT_WAVEFRONT && (cam->max_depth > 65535 ||
-        (eff.sample_count > 0 ? eff.sample_count : cam->samples_per_pixel) > 65535)) { eff.variant = RT_MEGAKERNEL; eff.sched = 0; }
+        (eff.sample_count > 0 ? eff.sample_count : cam->samples_per_pixel) > 32767)) { eff.variant = RT_MEGAKERNEL; eff.sched = 0; }
     opts = &eff;
     CK(cudaSetDevice(ctx->device));
     const int W = cam->image_width, H = image_height_of(*cam);
@@ -511,6 +519,7 @@ extern "C" int rt_render(rt_ctx* ctx, const rt_camera* cam, const rt_render_opts
         ctx->W = W; ctx->H = H; ctx->precision = opts->precision; ctx->slices = slices;
     }
     if (!opts->accumulate) ctx->samples_in_buffer = 0;
+    ctx->folded = false;
     int rc = opts->precision == RT_F32 ? render_impl<float>(ctx, *cam, *opts, sample_begin, sample_count, slices)
                                        : render_impl<double>(ctx, *cam, *opts, sample_begin, sample_count, slices);
     if (rc != RT_OK) return rc;
@@ -534,10 +543,10 @@ extern "C" int rt_readback(rt_ctx* ctx, int spp_total, double* sum_rgb, uint8_t*
     CK(cudaEventRecord(ctx->ev[2], ctx->stream));
     int launches = 1;
     if (ctx->precision == RT_F32)
-        CK(launch_resolve<float4>(reinterpret_cast<const float4*>(ctx->accum.p), ctx->slices, ctx->peers, npix, scale,
+        CK(launch_resolve<float4>(reinterpret_cast<const float4*>(ctx->accum.p), live_slices(ctx), live_peers(ctx), npix, scale,
                                   sum_rgb ? ctx->sum.p : nullptr, ctx->rgb8.p, nullptr, ctx->stream));
     else
-        CK(launch_resolve<double4>(reinterpret_cast<const double4*>(ctx->accum.p), ctx->slices, ctx->peers, npix, scale,
+        CK(launch_resolve<double4>(reinterpret_cast<const double4*>(ctx->accum.p), live_slices(ctx), live_peers(ctx), npix, scale,
                                    sum_rgb ? ctx->sum.p : nullptr, ctx->rgb8.p, nullptr, ctx->stream));
     unsigned long long text_len = 0;
     if (ppm || (ppm_len && !ppm)) {
@@ -573,10 +582,10 @@ static int resolve_views(rt_ctx* ctx, int spp_total, const FrameViews& v) {
     CK(ctx->rgb8.resize(npix * 3 + 16));
     const double scale = spp_total > 0 ? 1.0 / spp_total : 0.0;
     if (ctx->precision == RT_F32)
-        CK(launch_resolve<float4>(reinterpret_cast<const float4*>(ctx->accum.p), ctx->slices, ctx->peers, npix, scale,
+        CK(launch_resolve<float4>(reinterpret_cast<const float4*>(ctx->accum.p), live_slices(ctx), live_peers(ctx), npix, scale,
                                   nullptr, ctx->rgb8.p, nullptr, ctx->stream, v));
     else
-        CK(launch_resolve<double4>(reinterpret_cast<const double4*>(ctx->accum.p), ctx->slices, ctx->peers, npix, scale,
+        CK(launch_resolve<double4>(reinterpret_cast<const double4*>(ctx->accum.p), live_slices(ctx), live_peers(ctx), npix, scale,
                                    nullptr, ctx->rgb8.p, nullptr, ctx->stream, v));
     return RT_OK;
 }
@@ -655,6 +664,17 @@ extern "C" int rt_accum_buffer(rt_ctx* ctx, void** dev_ptr, size_t* n_elems, int
     if (dev_ptr) *dev_ptr = ctx->accum.p;
     if (n_elems) *n_elems = size_t(ctx->slices) * ctx->W * ctx->H * 4;
     if (elem_bytes) *elem_bytes = ctx->precision == RT_F32 ? 4 : 8;
+    return RT_OK;
+}
+
+extern "C" int rt_fold_slices(rt_ctx* ctx) {
+    if (!ctx) return RT_E_INVALID;
+    if (!ctx->accum.p) return fail(ctx, RT_E_STATE, "rt_fold_slices: nothing rendered");
+    CK(cudaSetDevice(ctx->device));
+    const size_t npix = size_t(ctx->W) * ctx->H;
+    if (ctx->precision == RT_F32) CK(launch_fold<float4>(reinterpret_cast<float4*>(ctx->accum.p), ctx->slices, npix, ctx->stream));
+    else CK(launch_fold<double4>(reinterpret_cast<double4*>(ctx->accum.p), ctx->slices, npix, ctx->stream));
+    ctx->folded = true;
     return RT_OK;
 }
 

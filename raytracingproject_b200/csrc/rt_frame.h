@@ -27,6 +27,9 @@ cudaError_t launch_resolve(const Q* accum, int slices, const PeerList& peers, si
                            double* sum_out, unsigned char* rgb8, Q* reduced_out, cudaStream_t st,
                            const FrameViews& views = FrameViews{nullptr, nullptr, 0, 0});
 
+// sums the sample layers of the accumulation buffer into layer 0 and zeroes the others (before a multi-GPU combine)
+template <typename Q> cudaError_t launch_fold(Q* accum, int slices, size_t n_pixels, cudaStream_t st);
+
 int encode_blocks(size_t n_pixels);
 // rgb8 must be readable up to 12 bytes past its last pixel (32-bit loads of 4-pixel groups)
 cudaError_t launch_encode_p3(const unsigned char* rgb8, size_t n_pixels, const EncodeHeader& hdr, unsigned* block_sums,

@@ -50,7 +50,7 @@ inline void pool_shape(int shape, int* paths, int* block) {
     if (shape < 0 || shape >= RT_POOL_SHAPES) shape = 0;
     *paths = P[shape]; *block = B[shape];
 }
-template <typename T> inline size_t pool_warp_bytes(int paths) { return size_t(paths) * (11 * sizeof(T) + 4 + 2 * 2 + 4); }
+template <typename T> inline size_t pool_warp_bytes(int paths) { return size_t(paths) * (11 * sizeof(T) + 4 + 2 * 2 + 4) + 32; }   // + the warp's two job descriptors
 #define RT_POOL_DEFAULT_SHAPE(T) (sizeof(T) == 4 ? 3 : 0)
 #define RT_POOL_UNSTAGED_SHAPE(T) (sizeof(T) == 4 ? 9 : 0)
 template <typename T> cudaError_t launch_render_pool(const RenderParams<T>& p, int shape, bool staged, int sm_count, cudaStream_t st);

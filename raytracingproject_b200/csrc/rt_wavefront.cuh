@@ -11,6 +11,12 @@
 //   pool slot  = one pixel of the warp's 16 x (P/16) tile (x one sample slice): samples of a pixel
 //                are walked in order by its slot, so the per-pixel sum has the reference's order
 //                (src/camera.h:41-44) and needs no atomics
+//   jobs       a job = one tile x one sample slice.  A warp keeps TWO jobs open (a ring of two
+//                descriptors in shared memory): a slot whose pixel has no samples left in the older
+//                job moves on to the same pixel position of the newer one at once, and when every
+//                slot has joined the newer job the next job of the frame is fetched into the place
+//                of the older one.  The pool does not drain between jobs (a drain is several rounds
+//                at a fraction of the lanes)
 //   TRACE      lanes PULL rays from the trace queue; node / leaf / pull sections are scheduled per
 //                warp like in render_sched_kernel, but a lane whose ray ends pulls the next ray at
 //                once (cheap: 9 LDS + 4 divisions) instead of waiting for a shade section
@@ -28,9 +34,10 @@ namespace rt {
 template <typename T, int P> struct Pool {
     enum { OX, OY, OZ, TM, DX, DY, DZ, TR, TG, TB, TBEST, NF };        // T arrays [P]
     enum { BEST, NI };                                                  // int arrays [P]
-    enum { SAMPLE, DEPTH, NH };                                         // 16-bit arrays [P]: sample index relative to the job's first, bounces left
+    enum { SAMPLE, DEPTH, NH };                                         // 16-bit arrays [P]: ring entry << 15 | next sample relative to the job's first (0x7fff: done with that job); bounces left
     enum { QUEUE, LOPAQUE, LGLASS, LEND, NL };                          // byte lists [P]
-    static constexpr int bytes = NF * P * int(sizeof(T)) + NI * P * 4 + NH * P * 2 + NL * P;
+    static constexpr int ring_bytes = 32;                               // two job descriptors (int4), after the lists
+    static constexpr int bytes = NF * P * int(sizeof(T)) + NI * P * 4 + NH * P * 2 + NL * P + ring_bytes;
     static constexpr int tile_w = 16, tile_h = P / 16;
     static_assert(P % 32 == 0 && P <= 128, "pool: path id is 7 bits, lists are filled 32 at a time");
 };
@@ -53,8 +60,11 @@ render_pool_kernel(const RenderParams<T> p) {
     unsigned short* const S = reinterpret_cast<unsigned short*>(I + L::NI * P);
     unsigned char* const B = reinterpret_cast<unsigned char*>(S + L::NH * P);
 
+    int4* const ring = reinterpret_cast<int4*>(B + L::NL * P);   // job descriptors: (bx | by << 16, s_begin, s_end, slice)
+
     const int W = p.cam.image_width, H = p.cam.image_height;
     const int njobs = p.tiles_x * p.tiles_y * p.slices;
+    const size_t layer = size_t(H) * size_t(W);
     const int th_p = p.th_s, th_l = p.th_l, th_n = p.th_n;
     unsigned long long my_rays = 0;
 #ifdef RT_POOL_STATS
@@ -65,76 +75,103 @@ render_pool_kernel(const RenderParams<T> p) {
 #endif
     int stack[RT_STACK];
 
-    for (;;) {
-        int job = 0;
-        if (lane == 0) job = int(atomicAdd(p.job_counter, 1u));
-        job = __shfl_sync(FULL, job, 0);
-        if (job >= njobs) break;
-        const int slice = job % p.slices, tile = job / p.slices;
-        const int bx = (tile % p.tiles_x) * L::tile_w, by = (tile / p.tiles_x) * L::tile_h;
-        const int s_begin = p.sample_begin + int((long long)p.sample_count * slice / p.slices);
-        const int s_end = p.sample_begin + int((long long)p.sample_count * (slice + 1) / p.slices);
-        Q* const acc_base = p.accum + size_t(slice) * size_t(H) * size_t(W);
+    // Ring state (warp-uniform).  Every slot goes through every job of its warp, in order: `newest` is the
+    // entry fetched last, `joined` the number of slots that have moved into it.  A slot in the other (older)
+    // entry joins the newest when its pixel there is finished; a slot that finishes the newest waits in the
+    // END list.  Once all P slots have joined the newest job nobody needs the older entry any more and the
+    // next job of the frame is fetched into it.  Start: all slots "done" with a dummy job in entry 1.
+    int newest = 1, joined = P;
+    bool exhausted = false;
+    if (lane == 0) { ring[0] = make_int4(0, 0, 0, 0); ring[1] = make_int4(0, 0, 0, 0); }
+    for (int k = lane; k < P; k += 32) {
+        S[L::SAMPLE * P + k] = (unsigned short)0xffff; S[L::DEPTH * P + k] = 0;
+        B[L::LEND * P + k] = (unsigned char)(k | 0x80);               // 0x80: nothing to add
+    }
+    int n_q = 0, n_end = P, n_opq = 0, n_gls = 0;
+    __syncwarp();
 
-        int n_q = 0, n_end = 0, n_opq = 0, n_gls = 0;
-        // every pixel of the tile: set up the accumulator, queue the first sample
-        for (int k = lane; k < P; k += 32) {
-            const int i = bx + (k & 15), j = by + (k >> 4);
-            const bool in_image = i < W && j < H;
-            if (in_image) {
-                Q* dst = acc_base + size_t(j) * size_t(W) + size_t(i);
-                Q v;
-                if (p.accumulate) { v = *dst; } else { v.x = 0; v.y = 0; v.z = 0; v.w = 0; }
-                v.w += decltype(v.x)(s_end - s_begin);
-                *dst = v;
-            }
-            S[L::SAMPLE * P + k] = 0; S[L::DEPTH * P + k] = 0;
-            const bool start = in_image && s_begin < s_end && p.max_depth > 0;    // max_depth <= 0: black (src/camera_cpu.h:12-13)
-            const unsigned m = __ballot_sync(FULL, start);
-            if (start) B[L::LEND * P + n_end + __popc(m & lt)] = (unsigned char)(k | 0x80);   // 0x80: nothing to add
-            n_end += __popc(m);
-        }
-        __syncwarp();
-
+    {
         for (;;) {
             // ------------------------------------------------------------------ END stage
-            // misses add thr * sky (src/camera_cpu.h:23-25); every entry then starts its pixel's
-            // next sample (camera::render's sample loop + get_ray, src/camera.h:41-44,87-100)
+            // misses add thr * sky (src/camera_cpu.h:23-25); every entry then starts its pixel's next sample
+            // (camera::render's sample loop + get_ray, src/camera.h:41-44,87-100) in its job or in the next one
+            bool progress = false;
+            int n_idle = 0;
             for (int b = 0; b < n_end; b += 32) {
+                if (!exhausted && joined == P) {
+                    int job = 0;
+                    if (lane == 0) job = int(atomicAdd(p.job_counter, 1u));
+                    job = __shfl_sync(FULL, job, 0);
+                    if (job >= njobs) exhausted = true;
+                    else {
+                        const int slice = job % p.slices, tile = job / p.slices;
+                        const int bx = (tile % p.tiles_x) * L::tile_w, by = (tile / p.tiles_x) * L::tile_h;
+                        const int s_begin = p.sample_begin + int((long long)p.sample_count * slice / p.slices);
+                        const int s_end = p.sample_begin + int((long long)p.sample_count * (slice + 1) / p.slices);
+                        newest ^= 1; joined = 0; progress = true;
+                        if (lane == 0) ring[newest] = make_int4(bx | (by << 16), s_begin, s_end, slice);
+                    }
+                    __syncwarp();
+                }
                 const int idx = b + lane;
-                bool push = false; int pid = 0;
+                bool push = false, idle = false, join = false; int pid = 0;
                 if (idx < n_end) {
                     const int e = B[L::LEND * P + idx];
                     pid = e & 0x7f;
-                    const int i = bx + (pid & 15), j = by + (pid >> 4);
+                    const int sw = S[L::SAMPLE * P + pid];
+                    int jb = sw >> 15, sidx = sw & 0x7fff;
+                    int4 J = ring[jb];
+                    int i = (J.x & 0xffff) + (pid & 15), j = (J.x >> 16) + (pid >> 4);
                     if (!(e & 0x80)) {
                         const Vec<T> d = mk<T>(F[L::DX * P + pid], F[L::DY * P + pid], F[L::DZ * P + pid]);
                         const Vec<T> thr = mk<T>(F[L::TR * P + pid], F[L::TG * P + pid], F[L::TB * P + pid]);
                         const Vec<T> c = thr * sky<T>(d);
-                        Q* dst = acc_base + size_t(j) * size_t(W) + size_t(i);
+                        Q* dst = p.accum + size_t(J.w) * layer + size_t(j) * size_t(W) + size_t(i);
                         Q v = *dst;
                         v.x += decltype(v.x)(c.x); v.y += decltype(v.x)(c.y); v.z += decltype(v.x)(c.z);
                         *dst = v;
                     }
-                    const int s = s_begin + int(S[L::SAMPLE * P + pid]);
-                    if (s < s_end) {
+                    bool start = sidx != 0x7fff && J.y + sidx < J.z;
+                    if (!start && jb != newest) {
+                        // the same pixel position of the next job: set up its accumulator, then its first sample
+                        join = true;
+                        jb = newest; J = ring[jb]; sidx = 0;
+                        i = (J.x & 0xffff) + (pid & 15); j = (J.x >> 16) + (pid >> 4);
+                        const bool in_image = i < W && j < H;
+                        if (in_image) {
+                            Q* dst = p.accum + size_t(J.w) * layer + size_t(j) * size_t(W) + size_t(i);
+                            Q v;
+                            if (p.accumulate) { v = *dst; } else { v.x = 0; v.y = 0; v.z = 0; v.w = 0; }
+                            v.w += decltype(v.x)(J.z - J.y);
+                            *dst = v;
+                        }
+                        start = in_image && J.y < J.z && p.max_depth > 0;      // max_depth <= 0: black (src/camera_cpu.h:12-13)
+                    }
+                    if (start) {
+                        const int s = J.y + sidx;
                         Philox rng; rng.init(p.seed);
                         rng.set(uint32_t(j) * uint32_t(W) + uint32_t(i), uint32_t(s), 0u);
                         const Ray<T> ray = get_ray<T>(p.cam, i, j, rng);
                         F[L::OX * P + pid] = ray.o.x; F[L::OY * P + pid] = ray.o.y; F[L::OZ * P + pid] = ray.o.z; F[L::TM * P + pid] = ray.tm;
                         F[L::DX * P + pid] = ray.d.x; F[L::DY * P + pid] = ray.d.y; F[L::DZ * P + pid] = ray.d.z;
                         F[L::TR * P + pid] = T(1); F[L::TG * P + pid] = T(1); F[L::TB * P + pid] = T(1);
-                        S[L::SAMPLE * P + pid] = (unsigned short)(s + 1 - s_begin); S[L::DEPTH * P + pid] = (unsigned short)p.max_depth;
+                        S[L::SAMPLE * P + pid] = (unsigned short)((jb << 15) | (sidx + 1)); S[L::DEPTH * P + pid] = (unsigned short)p.max_depth;
                         push = true;
+                    } else {
+                        S[L::SAMPLE * P + pid] = (unsigned short)((jb << 15) | 0x7fff);
+                        idle = true;                                   // waits in the END list for the next job, or for the end of the frame
                     }
                 }
-                const unsigned m = __ballot_sync(FULL, push);
+                __syncwarp();                                          // the batch has read its entries: the list is refilled in place below
+                const unsigned m = __ballot_sync(FULL, push), mi = __ballot_sync(FULL, idle), mj = __ballot_sync(FULL, join);
                 if (push) B[L::QUEUE * P + n_q + __popc(m & lt)] = (unsigned char)pid;
-                n_q += __popc(m);
+                if (idle) B[L::LEND * P + n_idle + __popc(mi & lt)] = (unsigned char)(pid | 0x80);
+                n_q += __popc(m); n_idle += __popc(mi); joined += __popc(mj);
+                progress = progress || m != 0u;
             }
-            n_end = 0;
+            n_end = n_idle;
             __syncwarp();
-            if (n_q == 0) break;                                   // every pixel of the tile is done
+            if (n_q == 0) { if (progress || (!exhausted && joined == P)) continue; break; }   // nothing in flight, nothing left to start: the frame is done
 
             // ------------------------------------------------------------------ BIG stage
             // every queued ray against the spheres kept out of the tree (the r = 1000 ground), in
@@ -246,13 +283,15 @@ render_pool_kernel(const RenderParams<T> p) {
                     bool cont = false, ended = false; int pid = 0;
                     if (idx < n) {
                         pid = list[idx];
-                        const int i = bx + (pid & 15), j = by + (pid >> 4);
+                        const int sw = S[L::SAMPLE * P + pid];
+                        const int4 J = ring[sw >> 15];
+                        const int i = (J.x & 0xffff) + (pid & 15), j = (J.x >> 16) + (pid >> 4);
                         Ray<T> ray;
                         ray.o = mk<T>(F[L::OX * P + pid], F[L::OY * P + pid], F[L::OZ * P + pid]);
                         ray.d = mk<T>(F[L::DX * P + pid], F[L::DY * P + pid], F[L::DZ * P + pid]);
                         ray.tm = F[L::TM * P + pid];
                         T t = F[L::TBEST * P + pid];
-                        const int slot = I[L::BEST * P + pid], s = s_begin + int(S[L::SAMPLE * P + pid]);
+                        const int slot = I[L::BEST * P + pid], s = J.y + (sw & 0x7fff);
                         int depth = S[L::DEPTH * P + pid];
                         const Surface<T> sf = surface_at<T>(sv, st.sa, st.sb, st.sc, st.meta, ray, t, slot);
                         Philox rng; rng.init(p.seed);

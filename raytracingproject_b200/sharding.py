@@ -5,7 +5,8 @@ Every (pixel, sample) is independent once the RNG is keyed, so rank g renders sa
 exchange while tracing.  The partial buffers are combined once at the end, either
 
 * ``combine="nccl"``: ``torch.distributed.reduce(SUM)`` to rank 0 over NVLink/NVSwitch on a tensor
-  that aliases the library's device buffer (torch is plumbing only), or
+  that aliases the library's device buffer (torch is plumbing only); every rank first folds its
+  sample layers into layer 0 (``ctx.fold_slices()``) so that one layer per rank is reduced, or
 * ``combine="ipc"``: rank 0 maps every peer's buffer through CUDA IPC and its resolve kernel reads
   them over NVLink while it resolves -- one fused reduce+resolve kernel, fixed summation order.
 
@@ -37,10 +38,13 @@ class _CudaAlias:
             "data": (int(ptr), False), "version": 3, "strides": None}
 
 
-def alias_accum_tensor(ctx):
-    """torch tensor (cuda) aliasing the context's accumulation buffer [slices*H*W*4]."""
+def alias_accum_tensor(ctx, layers=None):
+    """torch tensor (cuda) aliasing the context's accumulation buffer [slices*H*W*4], or its first
+    `layers` sample layers (layers=1 after ctx.fold_slices(): the rank's whole partial sum)."""
     import torch
     ptr, n, eb = ctx.accum_buffer()
+    if layers is not None:
+        n = min(n, int(layers) * ctx.width * ctx.height * 4)
     return torch.as_tensor(_CudaAlias(ptr, n, eb), device="cuda")
 
 

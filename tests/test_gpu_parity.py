@@ -109,6 +109,35 @@ def test_sample_ranges_accumulate_and_slices_do_not_change_the_image(ctx_scene, 
     assert np.array_equal(auto["rgb8"], acc["rgb8"])
 
 
+def test_fold_slices_keeps_the_frame(ctx_scene, rt):
+    """rt_fold_slices (before a multi-GPU combine): layer 0 becomes the sum of the sample layers, the others
+    become zero; resolve gives the same frame, later accumulate passes still add up, the next render unfolds."""
+    cam = rt.camera_rtiow(200, 12, 50)
+    ctx_scene.render(cam, precision=rt.F64, seed=9, slices=3)
+    a = ctx_scene.readback(12)
+    ctx_scene.fold_slices()
+    b = ctx_scene.readback(12)
+    assert np.array_equal(a["sum"], b["sum"]) and np.array_equal(a["rgb8"], b["rgb8"])      # doubles, same order: exact
+    ctx_scene.fold_slices()                                                               # idempotent
+    assert np.array_equal(ctx_scene.readback(12)["sum"], a["sum"])
+
+    ctx_scene.render(cam, precision=rt.F32, seed=9, slices=4)
+    a = ctx_scene.readback(12)
+    ctx_scene.fold_slices()
+    b = ctx_scene.readback(12)
+    assert np.allclose(a["sum"], b["sum"], rtol=1e-6, atol=1e-7)                           # layer 0 is rounded to float once
+    assert np.abs(a["rgb8"].astype(int) - b["rgb8"].astype(int)).max() <= 1
+
+    ctx_scene.render(cam, precision=rt.F64, seed=9, sample_begin=0, sample_count=5, slices=2)
+    ctx_scene.fold_slices()
+    ctx_scene.render(cam, precision=rt.F64, seed=9, sample_begin=5, sample_count=7, accumulate=True, slices=2)
+    c = ctx_scene.readback(12)
+    ctx_scene.render(cam, precision=rt.F64, seed=9)
+    full = ctx_scene.readback(12)
+    assert np.allclose(c["sum"], full["sum"], rtol=1e-13, atol=1e-14)
+    assert np.abs(c["rgb8"].astype(int) - full["rgb8"].astype(int)).max() <= 1
+
+
 # ----------------------------------------------------------------------- closest hit --
 @pytest.mark.parametrize("backend", ["bvh", "brute"])
 def test_closest_hit_fixture(ctx_scene, rt, backend):
@@ -375,10 +404,10 @@ def test_errors_are_reported(ctx, rt):
 
 
 def test_wavefront_beyond_16_bit_sample_or_depth_counts(ctx_scene, rt, O, scene):
-    """The wavefront pool keeps a path's sample index and remaining depth in 16 bits; calls beyond that are rendered
+    """The wavefront pool keeps a path's sample index in 15 bits and its remaining depth in 16; calls beyond that are rendered
     by the warp-scheduled megakernel behind the same entry point: same image as the oracle either way."""
     s, m = scene
-    for width, spp, depth in ((6, 66000, 4), (48, 3, 70000)):
+    for width, spp, depth in ((6, 33000, 4), (48, 3, 70000)):
         cam = rt.camera_rtiow(width, spp, depth)
         ctx_scene.render(cam, precision=rt.F64, seed=12, variant=rt.WAVEFRONT)
         out = ctx_scene.readback(spp)
@@ -386,9 +415,9 @@ def test_wavefront_beyond_16_bit_sample_or_depth_counts(ctx_scene, rt, O, scene)
         assert ctx_scene.stats()["rays"] == ref["rays"]
         assert np.array_equal(out["rgb8"], ref["rgb8"])
         assert np.allclose(out["sum"], ref["sum"], rtol=1e-12, atol=1e-12)
-    # just below the limit the pool itself runs (65535 samples in one slice)
-    cam = rt.camera_rtiow(2, 65535, 2)
+    # at the limit the pool itself runs (32767 samples in one slice)
+    cam = rt.camera_rtiow(2, 32767, 2)
     ctx_scene.render(cam, precision=rt.F64, seed=1, variant=rt.WAVEFRONT)
-    out = ctx_scene.readback(65535)
-    ref = O.render(s, m, O.camera_rtiow(2, 65535, 2), rng_mode=O.RNG_PHILOX, seed=1, use_bvh=True)
+    out = ctx_scene.readback(32767)
+    ref = O.render(s, m, O.camera_rtiow(2, 32767, 2), rng_mode=O.RNG_PHILOX, seed=1, use_bvh=True)
     assert np.array_equal(out["rgb8"], ref["rgb8"]) and ctx_scene.stats()["rays"] == ref["rays"]
