@@ -474,11 +474,11 @@ extern "C" int rt_render(rt_ctx* ctx, const rt_camera* cam, const rt_render_opts
     if (cam->image_width < 1 || !(cam->aspect_ratio > 0)) return fail(ctx, RT_E_INVALID, "rt_render: bad image size");
     if (opts->precision != RT_F32 && opts->precision != RT_F64) return fail(ctx, RT_E_INVALID, "rt_render: bad precision");
     if (opts->variant != RT_MEGAKERNEL && opts->variant != RT_MEGA_LOCKSTEP && opts->variant != RT_WAVEFRONT) return fail(ctx, RT_E_INVALID, "rt_render: variant not built");
-    // the wavefront pool keeps a path's sample index in 15 bits and its remaining depth in 16: beyond that the
+    // the wavefront pool keeps a path's sample index in 14 bits and its remaining depth in 16: beyond that the
     // warp-scheduled megakernel (same arithmetic, same image) takes the call
     rt_render_opts eff = *opts;
     if (eff.variant == RT_WAVEFRONT && (cam->max_depth > 65535 ||
-        (eff.sample_count > 0 ? eff.sample_count : cam->samples_per_pixel) > 32767)) { eff.variant = RT_MEGAKERNEL; eff.sched = 0; }
+        (eff.sample_count > 0 ? eff.sample_count : cam->samples_per_pixel) > 16383)) { eff.variant = RT_MEGAKERNEL; eff.sched = 0; }
     opts = &eff;
     CK(cudaSetDevice(ctx->device));
     const int W = cam->image_width, H = image_height_of(*cam);
@@ -505,6 +505,14 @@ extern "C" int rt_render(rt_ctx* ctx, const rt_camera* cam, const rt_render_opts
     // sky blue 1.0: 0.5/8 spp -> sqrt = 0.25 -> 64.0), where one ulp decides the byte.
     int slices = opts->slices;
     if (slices <= 0 && opts->precision == RT_F64) slices = 1;
+    if (slices <= 0 && opts->variant == RT_WAVEFRONT) {
+        // the pool does not drain between jobs (two jobs open per warp), so jobs can be small: ~32 per warp for a
+        // short tail at the end of the frame, but at least 8 samples each (a slot that finishes the newer job
+        // waits for the stragglers of the older one) unless that leaves fewer than ~16 jobs per warp
+        // (measured: profiles/r1_job_overhead_ring2.txt)
+        const long long want = (32 * resident_warps + tiles - 1) / tiles, least = std::min<long long>((16 * resident_warps + tiles - 1) / tiles, sample_count);
+        slices = int(std::min<long long>(64, std::min(want, std::max<long long>(least, sample_count / 8))));
+    }
     if (slices <= 0) slices = int(std::min<long long>(64, (16 * resident_warps + tiles - 1) / tiles));
     slices = std::max(1, std::min(slices, std::max(1, sample_count)));
     const size_t elem = opts->precision == RT_F32 ? sizeof(float4) : sizeof(double4);

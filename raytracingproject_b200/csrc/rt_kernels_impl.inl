@@ -38,7 +38,7 @@ template <> cudaError_t launch_render_sched<RT_REAL>(const RenderParams<RT_REAL>
 
 template <bool STAGED, int P, int BLOCK>
 static cudaError_t launch_pool_shape(const RenderParams<RT_REAL>& p, int sm_count, cudaStream_t st) {
-    static_assert(Pool<RT_REAL, P>::bytes == int(P * (11 * sizeof(RT_REAL) + 4 + 2 * 2 + 4) + 32), "pool_warp_bytes mirrors Pool::bytes");
+    static_assert(Pool<RT_REAL, P>::bytes == int(P * (11 * sizeof(RT_REAL) + 4 + 2 * 2 + 4) + 16 * RT_RING), "pool_warp_bytes mirrors Pool::bytes");
     const size_t smem = (STAGED ? staged_bytes_aligned<RT_REAL>(p.scene.n_nodes, p.scene.n_slots) : 0) + size_t(BLOCK / 32) * Pool<RT_REAL, P>::bytes;
     cudaError_t e = cudaFuncSetAttribute(render_pool_kernel<RT_REAL, STAGED, P, BLOCK>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
     if (e != cudaSuccess) return e;

@@ -44,13 +44,16 @@ template <typename T> __host__ __device__ inline size_t staged_bytes_aligned(int
 }
 
 // SM-resident wavefront (rt_wavefront.cuh): pool of P paths per warp, one CTA of BLOCK threads per SM
+#ifndef RT_RING
+#define RT_RING 2                      // jobs a warp keeps open (rt_wavefront.cuh)
+#endif
 #define RT_POOL_SHAPES 10
 inline void pool_shape(int shape, int* paths, int* block) {
     const int P[RT_POOL_SHAPES] = { 128, 128, 128, 128, 128, 128, 96, 64, 128, 128 }, B[RT_POOL_SHAPES] = { 256, 512, 640, 768, 704, 736, 896, 1024, 896, 1024 };
     if (shape < 0 || shape >= RT_POOL_SHAPES) shape = 0;
     *paths = P[shape]; *block = B[shape];
 }
-template <typename T> inline size_t pool_warp_bytes(int paths) { return size_t(paths) * (11 * sizeof(T) + 4 + 2 * 2 + 4) + 32; }   // + the warp's two job descriptors
+template <typename T> inline size_t pool_warp_bytes(int paths) { return size_t(paths) * (11 * sizeof(T) + 4 + 2 * 2 + 4) + 16 * RT_RING; }   // + the warp's job descriptors
 #define RT_POOL_DEFAULT_SHAPE(T) (sizeof(T) == 4 ? 3 : 0)
 #define RT_POOL_UNSTAGED_SHAPE(T) (sizeof(T) == 4 ? 9 : 0)
 template <typename T> cudaError_t launch_render_pool(const RenderParams<T>& p, int shape, bool staged, int sm_count, cudaStream_t st);

@@ -11,12 +11,14 @@
 //   pool slot  = one pixel of the warp's 16 x (P/16) tile (x one sample slice): samples of a pixel
 //                are walked in order by its slot, so the per-pixel sum has the reference's order
 //                (src/camera.h:41-44) and needs no atomics
-//   jobs       a job = one tile x one sample slice.  A warp keeps TWO jobs open (a ring of two
-//                descriptors in shared memory): a slot whose pixel has no samples left in the older
-//                job moves on to the same pixel position of the newer one at once, and when every
-//                slot has joined the newer job the next job of the frame is fetched into the place
-//                of the older one.  The pool does not drain between jobs (a drain is several rounds
-//                at a fraction of the lanes)
+//   jobs       a job = one tile x one sample slice.  A warp keeps RT_RING jobs open (a ring of
+//                descriptors in shared memory): a slot whose pixel has no samples left in its job
+//                moves on to the same pixel position of the next one at once, and when every slot
+//                has left the oldest job the next job of the frame is fetched into its place.  The
+//                pool does not drain between jobs (a drain is several rounds at a fraction of the
+//                lanes).  Two open jobs measured faster than four (profiles/r1_job_ring_ab.txt):
+//                the rays of a pool that spans two tiles are more coherent than those of one that
+//                spans four
 //   TRACE      lanes PULL rays from the trace queue; node / leaf / pull sections are scheduled per
 //                warp like in render_sched_kernel, but a lane whose ray ends pulls the next ray at
 //                once (cheap: 9 LDS + 4 divisions) instead of waiting for a shade section
@@ -31,16 +33,31 @@
 
 namespace rt {
 
+#ifndef RT_RING
+#define RT_RING 2                      // jobs a warp keeps open (2 or 4)
+#endif
+
 template <typename T, int P> struct Pool {
     enum { OX, OY, OZ, TM, DX, DY, DZ, TR, TG, TB, TBEST, NF };        // T arrays [P]
     enum { BEST, NI };                                                  // int arrays [P]
-    enum { SAMPLE, DEPTH, NH };                                         // 16-bit arrays [P]: ring entry << 15 | next sample relative to the job's first (0x7fff: done with that job); bounces left
+    enum { SAMPLE, DEPTH, NH };                                         // 16-bit arrays [P]: ring entry << 14 | next sample relative to the job's first (0x3fff: done with that job); bounces left
     enum { QUEUE, LOPAQUE, LGLASS, LEND, NL };                          // byte lists [P]
-    static constexpr int ring_bytes = 32;                               // two job descriptors (int4), after the lists
+    static constexpr int ring = RT_RING, ring_bytes = 16 * ring;        // job descriptors (int4) of the warp, after the lists
     static constexpr int bytes = NF * P * int(sizeof(T)) + NI * P * 4 + NH * P * 2 + NL * P + ring_bytes;
     static constexpr int tile_w = 16, tile_h = P / 16;
     static_assert(P % 32 == 0 && P <= 128, "pool: path id is 7 bits, lists are filled 32 at a time");
 };
+
+// pixel sum += contribution of one sample.  Only this pixel's slot touches the element, one sample after the
+// other, so the order of the sum is the reference's (src/camera.h:41-44).  Fast mode sends the addition to L2 as
+// one 128-bit reduction (RED.ADD.F32x4: nothing comes back, the warp does not wait for the load); parity mode
+// keeps the plain read-modify-write.
+__device__ __forceinline__ void accum_add(float4* dst, const Vec<float>& c) { atomicAdd(dst, make_float4(c.x, c.y, c.z, 0.0f)); }
+__device__ __forceinline__ void accum_add(double4* dst, const Vec<double>& c) {
+    double4 v = *dst;
+    v.x += c.x; v.y += c.y; v.z += c.z;
+    *dst = v;
+}
 
 template <typename T, bool STAGED, int P, int BLOCK>
 __global__ void __launch_bounds__(BLOCK, 1)
@@ -76,13 +93,15 @@ render_pool_kernel(const RenderParams<T> p) {
     int stack[RT_STACK];
 
     // Ring state (warp-uniform).  Every slot goes through every job of its warp, in order: `newest` is the
-    // entry fetched last, `joined` the number of slots that have moved into it.  A slot in the other (older)
-    // entry joins the newest when its pixel there is finished; a slot that finishes the newest waits in the
-    // END list.  Once all P slots have joined the newest job nobody needs the older entry any more and the
-    // next job of the frame is fetched into it.  Start: all slots "done" with a dummy job in entry 1.
-    int newest = 1, joined = P;
+    // entry fetched last, byte e of `joined` the number of slots that have moved into entry e's job.  A slot
+    // whose pixel is finished joins the job in the next entry, or waits in the END list when it is in the
+    // newest.  Entry f can take the next job of the frame once all P slots have joined the job after it.
+    // Start: every slot "done" with a dummy job in the last entry, every entry free.
+    enum { R = L::ring, SH = R == 2 ? 15 : 14, DONE = (1 << SH) - 1 };
+    int newest = R - 1;
+    unsigned joined = unsigned(P) * 0x01010101u;
     bool exhausted = false;
-    if (lane == 0) { ring[0] = make_int4(0, 0, 0, 0); ring[1] = make_int4(0, 0, 0, 0); }
+    if (lane < R) ring[lane] = make_int4(0, 0, 0, 0);
     for (int k = lane; k < P; k += 32) {
         S[L::SAMPLE * P + k] = (unsigned short)0xffff; S[L::DEPTH * P + k] = 0;
         B[L::LEND * P + k] = (unsigned char)(k | 0x80);               // 0x80: nothing to add
@@ -98,7 +117,8 @@ render_pool_kernel(const RenderParams<T> p) {
             bool progress = false;
             int n_idle = 0;
             for (int b = 0; b < n_end; b += 32) {
-                if (!exhausted && joined == P) {
+                // fetch one job ahead of the first slot, no more: jobs a warp holds unstarted are the frame's tail
+                if (!exhausted && ((joined >> (8 * newest)) & 0xffu) != 0u && ((joined >> (8 * ((newest + 2) & (R - 1)))) & 0xffu) == unsigned(P)) {
                     int job = 0;
                     if (lane == 0) job = int(atomicAdd(p.job_counter, 1u));
                     job = __shfl_sync(FULL, job, 0);
@@ -108,18 +128,18 @@ render_pool_kernel(const RenderParams<T> p) {
                         const int bx = (tile % p.tiles_x) * L::tile_w, by = (tile / p.tiles_x) * L::tile_h;
                         const int s_begin = p.sample_begin + int((long long)p.sample_count * slice / p.slices);
                         const int s_end = p.sample_begin + int((long long)p.sample_count * (slice + 1) / p.slices);
-                        newest ^= 1; joined = 0; progress = true;
+                        newest = (newest + 1) & (R - 1); joined &= ~(0xffu << (8 * newest)); progress = true;
                         if (lane == 0) ring[newest] = make_int4(bx | (by << 16), s_begin, s_end, slice);
                     }
                     __syncwarp();
                 }
                 const int idx = b + lane;
-                bool push = false, idle = false, join = false; int pid = 0;
+                bool push = false, idle = false; int pid = 0, join = -1;
                 if (idx < n_end) {
                     const int e = B[L::LEND * P + idx];
                     pid = e & 0x7f;
                     const int sw = S[L::SAMPLE * P + pid];
-                    int jb = sw >> 15, sidx = sw & 0x7fff;
+                    int jb = sw >> SH, sidx = sw & DONE;
                     int4 J = ring[jb];
                     int i = (J.x & 0xffff) + (pid & 15), j = (J.x >> 16) + (pid >> 4);
                     if (!(e & 0x80)) {
@@ -127,15 +147,13 @@ render_pool_kernel(const RenderParams<T> p) {
                         const Vec<T> thr = mk<T>(F[L::TR * P + pid], F[L::TG * P + pid], F[L::TB * P + pid]);
                         const Vec<T> c = thr * sky<T>(d);
                         Q* dst = p.accum + size_t(J.w) * layer + size_t(j) * size_t(W) + size_t(i);
-                        Q v = *dst;
-                        v.x += decltype(v.x)(c.x); v.y += decltype(v.x)(c.y); v.z += decltype(v.x)(c.z);
-                        *dst = v;
+                        accum_add(dst, c);
                     }
-                    bool start = sidx != 0x7fff && J.y + sidx < J.z;
+                    bool start = sidx != DONE && J.y + sidx < J.z;
                     if (!start && jb != newest) {
                         // the same pixel position of the next job: set up its accumulator, then its first sample
-                        join = true;
-                        jb = newest; J = ring[jb]; sidx = 0;
+                        jb = (jb + 1) & (R - 1); J = ring[jb]; sidx = 0;
+                        join = jb;
                         i = (J.x & 0xffff) + (pid & 15); j = (J.x >> 16) + (pid >> 4);
                         const bool in_image = i < W && j < H;
                         if (in_image) {
@@ -155,23 +173,28 @@ render_pool_kernel(const RenderParams<T> p) {
                         F[L::OX * P + pid] = ray.o.x; F[L::OY * P + pid] = ray.o.y; F[L::OZ * P + pid] = ray.o.z; F[L::TM * P + pid] = ray.tm;
                         F[L::DX * P + pid] = ray.d.x; F[L::DY * P + pid] = ray.d.y; F[L::DZ * P + pid] = ray.d.z;
                         F[L::TR * P + pid] = T(1); F[L::TG * P + pid] = T(1); F[L::TB * P + pid] = T(1);
-                        S[L::SAMPLE * P + pid] = (unsigned short)((jb << 15) | (sidx + 1)); S[L::DEPTH * P + pid] = (unsigned short)p.max_depth;
+                        S[L::SAMPLE * P + pid] = (unsigned short)((jb << SH) | (sidx + 1)); S[L::DEPTH * P + pid] = (unsigned short)p.max_depth;
                         push = true;
                     } else {
-                        S[L::SAMPLE * P + pid] = (unsigned short)((jb << 15) | 0x7fff);
+                        S[L::SAMPLE * P + pid] = (unsigned short)((jb << SH) | DONE);
                         idle = true;                                   // waits in the END list for the next job, or for the end of the frame
                     }
                 }
                 __syncwarp();                                          // the batch has read its entries: the list is refilled in place below
-                const unsigned m = __ballot_sync(FULL, push), mi = __ballot_sync(FULL, idle), mj = __ballot_sync(FULL, join);
+                const unsigned m = __ballot_sync(FULL, push), mi = __ballot_sync(FULL, idle);
                 if (push) B[L::QUEUE * P + n_q + __popc(m & lt)] = (unsigned char)pid;
                 if (idle) B[L::LEND * P + n_idle + __popc(mi & lt)] = (unsigned char)(pid | 0x80);
-                n_q += __popc(m); n_idle += __popc(mi); joined += __popc(mj);
+                n_q += __popc(m); n_idle += __popc(mi);
+                if (__any_sync(FULL, join >= 0)) {
+#pragma unroll
+                    for (int e = 0; e < R; ++e) joined += unsigned(__popc(__ballot_sync(FULL, join == e))) << (8 * e);
+                    progress = true;
+                }
                 progress = progress || m != 0u;
             }
             n_end = n_idle;
             __syncwarp();
-            if (n_q == 0) { if (progress || (!exhausted && joined == P)) continue; break; }   // nothing in flight, nothing left to start: the frame is done
+            if (n_q == 0) { if (progress) continue; break; }   // nothing in flight, nothing left to start: the frame is done
 
             // ------------------------------------------------------------------ BIG stage
             // every queued ray against the spheres kept out of the tree (the r = 1000 ground), in
@@ -284,14 +307,14 @@ render_pool_kernel(const RenderParams<T> p) {
                     if (idx < n) {
                         pid = list[idx];
                         const int sw = S[L::SAMPLE * P + pid];
-                        const int4 J = ring[sw >> 15];
+                        const int4 J = ring[sw >> SH];
                         const int i = (J.x & 0xffff) + (pid & 15), j = (J.x >> 16) + (pid >> 4);
                         Ray<T> ray;
                         ray.o = mk<T>(F[L::OX * P + pid], F[L::OY * P + pid], F[L::OZ * P + pid]);
                         ray.d = mk<T>(F[L::DX * P + pid], F[L::DY * P + pid], F[L::DZ * P + pid]);
                         ray.tm = F[L::TM * P + pid];
                         T t = F[L::TBEST * P + pid];
-                        const int slot = I[L::BEST * P + pid], s = J.y + (sw & 0x7fff);
+                        const int slot = I[L::BEST * P + pid], s = J.y + (sw & DONE);
                         int depth = S[L::DEPTH * P + pid];
                         const Surface<T> sf = surface_at<T>(sv, st.sa, st.sb, st.sc, st.meta, ray, t, slot);
                         Philox rng; rng.init(p.seed);

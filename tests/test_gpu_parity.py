@@ -404,10 +404,10 @@ def test_errors_are_reported(ctx, rt):
 
 
 def test_wavefront_beyond_16_bit_sample_or_depth_counts(ctx_scene, rt, O, scene):
-    """The wavefront pool keeps a path's sample index in 15 bits and its remaining depth in 16; calls beyond that are rendered
+    """The wavefront pool keeps a path's sample index in 14 bits and its remaining depth in 16; calls beyond that are rendered
     by the warp-scheduled megakernel behind the same entry point: same image as the oracle either way."""
     s, m = scene
-    for width, spp, depth in ((6, 33000, 4), (48, 3, 70000)):
+    for width, spp, depth in ((6, 17000, 4), (48, 3, 70000)):
         cam = rt.camera_rtiow(width, spp, depth)
         ctx_scene.render(cam, precision=rt.F64, seed=12, variant=rt.WAVEFRONT)
         out = ctx_scene.readback(spp)
@@ -415,9 +415,9 @@ def test_wavefront_beyond_16_bit_sample_or_depth_counts(ctx_scene, rt, O, scene)
         assert ctx_scene.stats()["rays"] == ref["rays"]
         assert np.array_equal(out["rgb8"], ref["rgb8"])
         assert np.allclose(out["sum"], ref["sum"], rtol=1e-12, atol=1e-12)
-    # at the limit the pool itself runs (32767 samples in one slice)
-    cam = rt.camera_rtiow(2, 32767, 2)
+    # at the limit the pool itself runs (16383 samples in one slice)
+    cam = rt.camera_rtiow(2, 16383, 2)
     ctx_scene.render(cam, precision=rt.F64, seed=1, variant=rt.WAVEFRONT)
-    out = ctx_scene.readback(32767)
-    ref = O.render(s, m, O.camera_rtiow(2, 32767, 2), rng_mode=O.RNG_PHILOX, seed=1, use_bvh=True)
+    out = ctx_scene.readback(16383)
+    ref = O.render(s, m, O.camera_rtiow(2, 16383, 2), rng_mode=O.RNG_PHILOX, seed=1, use_bvh=True)
     assert np.array_equal(out["rgb8"], ref["rgb8"]) and ctx_scene.stats()["rays"] == ref["rays"]
