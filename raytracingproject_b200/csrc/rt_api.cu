@@ -69,6 +69,8 @@ struct rt_ctx {
 
     // frame
     int W = 0, H = 0, slices = 0, precision = -1;
+    int slice_begin[RT_MAX_SLICES + 1] = {};   // sample ranges of the layers of the render in flight
+    int bulk_layers = 0;                       // how many of them are full-size (the rest halve down: the tail of the frame)
     bool folded = false;                    // rt_fold_slices ran since the last render: only layer 0 (here and in the peers) holds data
     long long samples_in_buffer = 0;
     DevBuf<unsigned char> accum;            // Quad<T>[slices][H][W]
@@ -440,6 +442,8 @@ int render_impl(rt_ctx* ctx, const rt_camera& cam, const rt_render_opts& o, int 
     p.seed = o.seed;
     p.sample_begin = sample_begin; p.sample_count = sample_count; p.max_depth = cam.max_depth;
     p.slices = slices;
+    for (int k = 0; k <= slices; ++k) p.slice_begin[k] = ctx->slice_begin[k];
+    p.bulk_layers = std::min(slices, ctx->bulk_layers);
     p.tiles_x = (ctx->W + 7) / 8; p.tiles_y = (ctx->H + 3) / 4;
     p.accumulate = o.accumulate;
     size_t smem = 0;
@@ -505,16 +509,25 @@ extern "C" int rt_render(rt_ctx* ctx, const rt_camera* cam, const rt_render_opts
     // sky blue 1.0: 0.5/8 spp -> sqrt = 0.25 -> 64.0), where one ulp decides the byte.
     int slices = opts->slices;
     if (slices <= 0 && opts->precision == RT_F64) slices = 1;
-    if (slices <= 0 && opts->variant == RT_WAVEFRONT) {
-        // the pool does not drain between jobs (two jobs open per warp), so jobs can be small: ~32 per warp for a
-        // short tail at the end of the frame, but at least 8 samples each (a slot that finishes the newer job
-        // waits for the stragglers of the older one) unless that leaves fewer than ~16 jobs per warp
-        // (measured: profiles/r1_job_overhead_ring2.txt)
-        const long long want = (32 * resident_warps + tiles - 1) / tiles, least = std::min<long long>((16 * resident_warps + tiles - 1) / tiles, sample_count);
-        slices = int(std::min<long long>(64, std::min(want, std::max<long long>(least, sample_count / 8))));
+    int sizes[RT_MAX_SLICES], n_sized = -1, n_bulk = 0;
+    if (slices <= 0 && opts->variant == RT_WAVEFRONT && sample_count > 0) {
+        // The pool does not drain between jobs (two jobs open per warp), so the job size is free to vary: BULK layers
+        // of about 1/32 of a warp's share of the frame each (at least 8 samples: a slot that finishes the newer job
+        // waits for the stragglers of the older one), then layers that halve down to a few samples.  Jobs are taken
+        // layer by layer, so the frame ends on the small ones: the tail is a job or two per warp, whatever its size
+        // (measured: profiles/r1_job_overhead_ring2.txt, r1_job_sizes_geometric.txt)
+        const double tiles_per_warp = double(tiles) / double(resident_warps);
+        const int bulk = std::max(8, int(std::ceil(sample_count * tiles_per_warp / 32.0)));
+        const int small = std::max(2, bulk / 8);
+        int left = sample_count, n = 0;
+        while (left > 2 * bulk && n < RT_MAX_SLICES - 8) { sizes[n++] = bulk; left -= bulk; }
+        n_bulk = n;
+        while (left > small && n < RT_MAX_SLICES - 1) { const int h = (left + 1) / 2; sizes[n++] = h; left -= h; }
+        if (left > 0) sizes[n++] = left;
+        slices = n; n_sized = n;
     }
     if (slices <= 0) slices = int(std::min<long long>(64, (16 * resident_warps + tiles - 1) / tiles));
-    slices = std::max(1, std::min(slices, std::max(1, sample_count)));
+    slices = std::max(1, std::min(std::min(slices, RT_MAX_SLICES), std::max(1, sample_count)));
     const size_t elem = opts->precision == RT_F32 ? sizeof(float4) : sizeof(double4);
 
     // a progressive pass may use fewer slices than the buffer holds (it adds into the first ones; resolve sums all)
@@ -528,6 +541,11 @@ extern "C" int rt_render(rt_ctx* ctx, const rt_camera* cam, const rt_render_opts
     }
     if (!opts->accumulate) ctx->samples_in_buffer = 0;
     ctx->folded = false;
+    const bool sized = slices == n_sized;             // a progressive pass that got fewer layers than it wanted splits evenly
+    ctx->bulk_layers = sized ? n_bulk : slices;
+    ctx->slice_begin[0] = sample_begin;
+    for (int k = 0; k < slices; ++k)
+        ctx->slice_begin[k + 1] = sized ? ctx->slice_begin[k] + sizes[k] : sample_begin + int((long long)sample_count * (k + 1) / slices);
     int rc = opts->precision == RT_F32 ? render_impl<float>(ctx, *cam, *opts, sample_begin, sample_count, slices)
                                        : render_impl<double>(ctx, *cam, *opts, sample_begin, sample_count, slices);
     if (rc != RT_OK) return rc;

@@ -17,6 +17,8 @@ namespace rt {
 inline int sched_block(int shape) { const int b[RT_SCHED_SHAPES] = { 256, 320, 384, 512 }; return b[shape < 0 || shape >= RT_SCHED_SHAPES ? 0 : shape]; }
 #define RT_SCHED_DEFAULT_SHAPE(T) (sizeof(T) == 4 ? 2 : 0)
 
+#define RT_MAX_SLICES 64
+
 template <typename T> struct RenderParams {
     CameraFrame<T> cam;
     SceneView<T> scene;
@@ -26,6 +28,8 @@ template <typename T> struct RenderParams {
     uint64_t seed;
     int sample_begin, sample_count, max_depth;
     int slices, tiles_x, tiles_y;
+    int bulk_layers;                    // wavefront job order: tile-major over the first bulk_layers layers, then layer by layer
+    int slice_begin[RT_MAX_SLICES + 1]; // wavefront: samples [slice_begin[k], slice_begin[k+1]) of a pixel form layer k (sizes may differ)
     int accumulate;
     int th_s, th_l, th_n;               // section thresholds of the warp schedulers (render_sched_kernel, render_pool_kernel)
 };

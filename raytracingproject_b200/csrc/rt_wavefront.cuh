@@ -124,10 +124,15 @@ render_pool_kernel(const RenderParams<T> p) {
                     job = __shfl_sync(FULL, job, 0);
                     if (job >= njobs) exhausted = true;
                     else {
-                        const int slice = job % p.slices, tile = job / p.slices;
+                        // job order: the bulk layers tile by tile (the jobs a warp holds open then lie a few tile rows apart:
+                        // layer by layer -- 30 tile rows apart -- measured 4 % slower), then the short layers one after the
+                        // other, so that the frame ends on small jobs
+                        const int ntiles = p.tiles_x * p.tiles_y, nbulk = p.bulk_layers * ntiles;
+                        int slice, tile;
+                        if (job < nbulk) { tile = job / p.bulk_layers; slice = job - tile * p.bulk_layers; }
+                        else { const int r = job - nbulk; slice = r / ntiles; tile = r - slice * ntiles; slice += p.bulk_layers; }
                         const int bx = (tile % p.tiles_x) * L::tile_w, by = (tile / p.tiles_x) * L::tile_h;
-                        const int s_begin = p.sample_begin + int((long long)p.sample_count * slice / p.slices);
-                        const int s_end = p.sample_begin + int((long long)p.sample_count * (slice + 1) / p.slices);
+                        const int s_begin = p.slice_begin[slice], s_end = p.slice_begin[slice + 1];
                         newest = (newest + 1) & (R - 1); joined &= ~(0xffu << (8 * newest)); progress = true;
                         if (lane == 0) ring[newest] = make_int4(bx | (by << 16), s_begin, s_end, slice);
                     }
