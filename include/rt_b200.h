@@ -112,7 +112,7 @@ typedef struct {
     int32_t  accumulate;     /* 0: overwrite the accumulation buffer, 1: add to it (progressive) */
     uint64_t seed;           /* Philox key; stream = (pixel, sample, stage), see DESIGN.md */
     int32_t  slices;         /* sample slices per pixel rendered by different warps (0 = auto) */
-    int32_t  sched;          /* tuning: th_s | th_l << 8 | shape+1 << 16 | th_n << 20 of the warp scheduler (0 = defaults) */
+    int32_t  sched;          /* tuning: th_s | th_l << 8 | shape+1 << 16 | th_n << 20 of the warp scheduler, bulk jobs per warp << 24 (0 = defaults) */
 } rt_render_opts;
 
 typedef struct {

@@ -512,12 +512,13 @@ extern "C" int rt_render(rt_ctx* ctx, const rt_camera* cam, const rt_render_opts
     int sizes[RT_MAX_SLICES], n_sized = -1, n_bulk = 0;
     if (slices <= 0 && opts->variant == RT_WAVEFRONT && sample_count > 0) {
         // The pool does not drain between jobs (two jobs open per warp), so the job size is free to vary: BULK layers
-        // of about 1/32 of a warp's share of the frame each (at least 8 samples: a slot that finishes the newer job
+        // of about 1/20 of a warp's share of the frame each (at least 8 samples: a slot that finishes the newer job
         // waits for the stragglers of the older one), then layers that halve down to a few samples.  Jobs are taken
         // layer by layer, so the frame ends on the small ones: the tail is a job or two per warp, whatever its size
         // (measured: profiles/r1_job_overhead_ring2.txt, r1_job_sizes_geometric.txt)
         const double tiles_per_warp = double(tiles) / double(resident_warps);
-        const int bulk = std::max(8, int(std::ceil(sample_count * tiles_per_warp / 32.0)));
+        const int jobs_per_warp = ((opts->sched >> 24) & 0xff) ? ((opts->sched >> 24) & 0xff) : 20;      // tuning: bulk jobs per warp (16-24 measured best, flat: profiles/r1_job_sizes_geometric.txt)
+        const int bulk = std::max(8, int(std::ceil(sample_count * tiles_per_warp / double(jobs_per_warp))));
         const int small = std::max(2, bulk / 8);
         int left = sample_count, n = 0;
         while (left > 2 * bulk && n < RT_MAX_SLICES - 8) { sizes[n++] = bulk; left -= bulk; }
