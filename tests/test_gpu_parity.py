@@ -138,6 +138,33 @@ def test_fold_slices_keeps_the_frame(ctx_scene, rt):
     assert np.abs(c["rgb8"].astype(int) - full["rgb8"].astype(int)).max() <= 1
 
 
+def test_every_pool_shape_and_job_layout_renders_the_same_frame(ctx_scene, rt, O, scene):
+    """The wavefront kernel is compiled for several pool shapes (paths per warp x warps per SM) and cuts a frame into
+    jobs in several ways (equal layers, bulk + halving layers, 1..64 layers); every combination renders the same
+    samples: parity mode bit-identical to the oracle with one layer, ray count equal in all of them."""
+    s, m = scene
+    cam = rt.camera_rtiow(150, 11, 50)                   # 150 x 84: ragged against the 16 x 8 (and 16 x 6, 16 x 4) tiles
+    ref = O.render(s, m, O.camera_rtiow(150, 11, 50), rng_mode=O.RNG_PHILOX, seed=5, use_bvh=True)
+    for shape in range(1, 11):
+        ctx_scene.render(cam, precision=rt.F64, seed=5, variant=rt.WAVEFRONT, sched=shape << 16)
+        out = ctx_scene.readback(11)
+        assert ctx_scene.stats()["rays"] == ref["rays"], shape
+        assert np.array_equal(out["rgb8"], ref["rgb8"]), shape
+    base = None
+    for slices, jobs in ((0, 0), (0, 4), (0, 255), (1, 0), (3, 0), (11, 0), (64, 0)):
+        ctx_scene.render(cam, precision=rt.F32, seed=5, variant=rt.WAVEFRONT, slices=slices, sched=jobs << 24)
+        out = ctx_scene.readback(11)
+        st = ctx_scene.stats()
+        assert 1 <= st["slices"] <= 11
+        if base is None:
+            base, base_rays = out, st["rays"]
+        assert st["rays"] == base_rays, (slices, jobs)               # same float arithmetic per sample in every layout
+        assert abs(st["rays"] - ref["rays"]) <= 1e-3 * ref["rays"]  # float grazing decisions may differ from double ones
+        assert np.abs(out["rgb8"].astype(int) - base["rgb8"].astype(int)).max() <= 1
+        assert np.allclose(out["sum"], base["sum"], rtol=2e-6, atol=1e-6)
+        assert np.mean(np.abs(out["rgb8"].astype(int) - ref["rgb8"].astype(int)).max(-1) <= 1) > 0.999
+
+
 # ----------------------------------------------------------------------- closest hit --
 @pytest.mark.parametrize("backend", ["bvh", "brute"])
 def test_closest_hit_fixture(ctx_scene, rt, backend):
