@@ -34,7 +34,7 @@ class Camera(C.Structure):
 
 
 class BvhOpts(C.Structure):
-    _fields_ = [("abi", C.c_uint32), ("builder", C.c_int32), ("max_leaf", C.c_int32), ("pad", C.c_int32),
+    _fields_ = [("abi", C.c_uint32), ("builder", C.c_int32), ("max_leaf", C.c_int32), ("wide", C.c_int32),
                 ("big_radius", C.c_double)]
 
 

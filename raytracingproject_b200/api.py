@@ -115,11 +115,11 @@ class Context:
         if rc != 0:
             raise RtError(self._lib.rt_last_error(self._h).decode())
 
-    def upload_scene(self, spheres, materials, builder=L.BVH_SAH_HOST, max_leaf=0, big_radius=0.0):
+    def upload_scene(self, spheres, materials, builder=L.BVH_SAH_HOST, max_leaf=0, big_radius=0.0, wide=0):
         spheres = np.ascontiguousarray(spheres)
         materials = np.ascontiguousarray(materials)
         assert spheres.dtype.itemsize == 64 and materials.dtype.itemsize == 40
-        o = L.BvhOpts(L.ABI, builder, max_leaf, 0, big_radius)
+        o = L.BvhOpts(L.ABI, builder, max_leaf, wide, big_radius)
         self._ck(self._lib.rt_upload_scene(self._h, L.ptr(spheres), len(spheres), L.ptr(materials), len(materials), C.byref(o)))
 
     def render(self, cam, precision=L.F32, seed=0, variant=L.MEGAKERNEL, sample_begin=0, sample_count=0,

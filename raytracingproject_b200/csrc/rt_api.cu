@@ -62,7 +62,8 @@ struct rt_ctx {
     // scene (SoA, both precisions; see rt_device.cuh for the slot layout)
     bool has_scene = false;
     int n_spheres = 0, n_slots = 0, n_big = 0, n_nodes = 0, root_ref = RT_SENTINEL, depth = 0;
-    DevBuf<float4> nodes, sa32, sb32, sc32;
+    DevBuf<float4> nodes, nodes4, sa32, sb32, sc32;   // nodes4: 4-wide records of the same tree (null unless the tree is walked in global memory)
+    bool wide = false, wide_forced = false;
     DevBuf<double4> sa64, sb64, sc64, big_a, big_b, big_c;
     DevBuf<int> meta, big_meta;
     double build_ms = 0, upload_ms = 0;
@@ -171,6 +172,7 @@ template <> struct Sel<double> {
 template <typename T> SceneView<T> scene_view(const rt_ctx* c) {
     SceneView<T> sv;
     sv.nodes = c->nodes.p;
+    sv.nodes4 = c->wide ? c->nodes4.p : nullptr;
     sv.sa = Sel<T>::a(c); sv.sb = Sel<T>::b(c); sv.sc = Sel<T>::cc(c);
     sv.meta = c->meta.p;
     sv.big_a = c->big_a.p; sv.big_b = c->big_b.p; sv.big_c = c->big_c.p; sv.big_meta = c->big_meta.p;
@@ -232,7 +234,7 @@ int rt_destroy(rt_ctx* ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     rt_ipc_close_peers(ctx);
-    ctx->nodes.release(); ctx->sa32.release(); ctx->sb32.release(); ctx->sc32.release();
+    ctx->nodes.release(); ctx->nodes4.release(); ctx->sa32.release(); ctx->sb32.release(); ctx->sc32.release();
     ctx->sa64.release(); ctx->sb64.release(); ctx->sc64.release();
     ctx->big_a.release(); ctx->big_b.release(); ctx->big_c.release(); ctx->meta.release(); ctx->big_meta.release();
     ctx->accum.release(); ctx->reduced.release(); ctx->job_counter.release(); ctx->ray_counter.release();
@@ -388,6 +390,20 @@ extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_s
             CK(cudaStreamSynchronize(ctx->stream));
         }
     }
+    // 4-wide records (8f-4) for trees walked in global memory: opt-in (opts->wide = 1; the wavefront kernel then leaves
+    // the scene in global memory whatever its size).  Measured on C5 (10 k / 100 k / 1 M spheres): 2 % SLOWER than the
+    // binary records (profiles/r1_wide_nodes_ab.txt), so nothing turns them on by default.
+    {
+        const int want = opts ? opts->wide : 0;
+        ctx->wide_forced = want > 0;
+        ctx->wide = ctx->n_nodes > 0 && want > 0;
+        if (ctx->wide) {
+            CK(ctx->nodes4.resize(size_t(ctx->n_nodes) * 8));
+            CK(launch_widen(ctx->nodes.p, ctx->n_nodes, ctx->nodes4.p, ctx->stream));
+        } else {
+            ctx->nodes4.release();
+        }
+    }
     CK(cudaStreamSynchronize(ctx->stream));
     ctx->n_spheres = int(n_spheres); ctx->n_slots = n_tree; ctx->n_big = int(big_ids.size());
     ctx->has_scene = true;
@@ -414,8 +430,8 @@ template <typename T> int pool_shape_for(const rt_ctx* c, int sched, bool* stage
     const size_t scene = staged_bytes_aligned<T>(c->n_nodes, c->n_slots);
     const size_t budget = c->smem_optin;
     auto need = [&](int sh) { int P, B; pool_shape(sh, &P, &B); return size_t(B / 32) * pool_warp_bytes<T>(P); };
-    *staged = c->n_slots > 0 && scene + need(shape) <= budget;
-    if (!*staged && c->n_slots > 0) {                 // fewer warps, most first, until scene + pools fit
+    *staged = c->n_slots > 0 && scene + need(shape) <= budget && !c->wide_forced;
+    if (!*staged && c->n_slots > 0 && !c->wide_forced) {   // fewer warps, most first, until scene + pools fit
         const int by_warps[] = { 3, 5, 4, 2, 1, 0 };
         for (int sh : by_warps) {
             int P, B, P0, B0; pool_shape(sh, &P, &B); pool_shape(shape, &P0, &B0);

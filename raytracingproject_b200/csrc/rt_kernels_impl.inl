@@ -36,18 +36,19 @@ template <> cudaError_t launch_render_sched<RT_REAL>(const RenderParams<RT_REAL>
     }
 }
 
-template <bool STAGED, int P, int BLOCK>
+template <bool STAGED, int P, int BLOCK, bool WIDE = false>
 static cudaError_t launch_pool_shape(const RenderParams<RT_REAL>& p, int sm_count, cudaStream_t st) {
     static_assert(Pool<RT_REAL, P>::bytes == int(P * (11 * sizeof(RT_REAL) + 4 + 2 * 2 + 4) + 16 * RT_RING), "pool_warp_bytes mirrors Pool::bytes");
     const size_t smem = (STAGED ? staged_bytes_aligned<RT_REAL>(p.scene.n_nodes, p.scene.n_slots) : 0) + size_t(BLOCK / 32) * Pool<RT_REAL, P>::bytes;
-    cudaError_t e = cudaFuncSetAttribute(render_pool_kernel<RT_REAL, STAGED, P, BLOCK>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+    cudaError_t e = cudaFuncSetAttribute(render_pool_kernel<RT_REAL, STAGED, P, BLOCK, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
     if (e != cudaSuccess) return e;
-    render_pool_kernel<RT_REAL, STAGED, P, BLOCK><<<sm_count, BLOCK, smem, st>>>(p);      // persistent: one CTA per SM
+    render_pool_kernel<RT_REAL, STAGED, P, BLOCK, WIDE><<<sm_count, BLOCK, smem, st>>>(p);      // persistent: one CTA per SM
     return cudaGetLastError();
 }
 
 template <> cudaError_t launch_render_pool<RT_REAL>(const RenderParams<RT_REAL>& p, int shape, bool staged, int sm_count, cudaStream_t st) {
-#define RT_POOL_CASE(S, P, B) case S: return staged ? launch_pool_shape<true, P, B>(p, sm_count, st) : launch_pool_shape<false, P, B>(p, sm_count, st)
+    const bool wide = !staged && p.scene.nodes4 != nullptr;
+#define RT_POOL_CASE(S, P, B) case S: return staged ? launch_pool_shape<true, P, B>(p, sm_count, st) : (wide ? launch_pool_shape<false, P, B, true>(p, sm_count, st) : launch_pool_shape<false, P, B>(p, sm_count, st))
     switch (shape) {
     RT_POOL_CASE(1, 128, 512);
     RT_POOL_CASE(2, 128, 640);

@@ -51,7 +51,56 @@ __global__ void __launch_bounds__(256) scene_fill_kernel(const rt_sphere* __rest
     meta[slot] = (id << 3) | (mov ? 4 : 0) | mt.type;
 }
 
+// 4-wide record of binary node i (layout: rt_trace.cuh): an inner child is replaced by ITS two children
+// (boxes and refs read from the child's own record), a leaf child stands for itself; free places hold an
+// inverted box and RT_SENTINEL.  One thread per binary node, no dependence between threads.
+struct WideChild { float lo[3], hi[3]; int ref; };
+
+__device__ __forceinline__ void child_of(const float4& q0, const float4& q1, const float4& q2, const float4& q3, int side, WideChild& c) {
+    const float4& xy = side ? q1 : q0;
+    c.lo[0] = xy.x; c.lo[1] = xy.y; c.hi[0] = xy.z; c.hi[1] = xy.w;
+    c.lo[2] = side ? q2.y : q2.x; c.hi[2] = side ? q2.w : q2.z;
+    c.ref = __float_as_int(side ? q3.y : q3.x);
+}
+
+__global__ void widen_kernel(const float4* __restrict__ n2, int n_nodes, float4* __restrict__ n4) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_nodes) return;
+    const float4 q0 = n2[4 * i + 0], q1 = n2[4 * i + 1], q2 = n2[4 * i + 2], q3 = n2[4 * i + 3];
+    WideChild ch[4];
+    int n = 0;
+#pragma unroll
+    for (int side = 0; side < 2; ++side) {
+        WideChild c;
+        child_of(q0, q1, q2, q3, side, c);
+        if (c.ref >= 0) {
+            const float4 r0 = n2[4 * c.ref + 0], r1 = n2[4 * c.ref + 1], r2 = n2[4 * c.ref + 2], r3 = n2[4 * c.ref + 3];
+            child_of(r0, r1, r2, r3, 0, ch[n++]);
+            child_of(r0, r1, r2, r3, 1, ch[n++]);
+        } else {
+            ch[n++] = c;
+        }
+    }
+    for (; n < 4; ++n) {
+        for (int a = 0; a < 3; ++a) { ch[n].lo[a] = 1e30f; ch[n].hi[a] = -1e30f; }
+        ch[n].ref = int(0x80000000);
+    }
+    float4* o = n4 + 8 * size_t(i);
+#pragma unroll
+    for (int c = 0; c < 4; ++c) o[c] = make_float4(ch[c].lo[0], ch[c].lo[1], ch[c].hi[0], ch[c].hi[1]);
+    o[4] = make_float4(ch[0].lo[2], ch[1].lo[2], ch[0].hi[2], ch[1].hi[2]);
+    o[5] = make_float4(ch[2].lo[2], ch[3].lo[2], ch[2].hi[2], ch[3].hi[2]);
+    o[6] = make_float4(__int_as_float(ch[0].ref), __int_as_float(ch[1].ref), __int_as_float(ch[2].ref), __int_as_float(ch[3].ref));
+    o[7] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+}
+
 }  // namespace
+
+cudaError_t launch_widen(const float4* nodes2, int n_nodes, float4* nodes4, cudaStream_t st) {
+    if (n_nodes <= 0) return cudaSuccess;
+    widen_kernel<<<(n_nodes + 255) / 256, 256, 0, st>>>(nodes2, n_nodes, nodes4);
+    return cudaGetLastError();
+}
 
 cudaError_t launch_scene_boxes(const rt_sphere* spheres, const int* ids, int n, HostBox* boxes, cudaStream_t st) {
     if (n <= 0) return cudaSuccess;

@@ -18,4 +18,7 @@ cudaError_t launch_scene_fill(const rt_sphere* spheres, const rt_material* mater
                               float4* a32, float4* b32, float4* c32, double4* a64, double4* b64, double4* c64, int* meta,
                               cudaStream_t st);
 
+// 4-wide records (layout: rt_trace.cuh) of a binary tree: record i = the grandchildren of binary node i
+cudaError_t launch_widen(const float4* nodes2, int n_nodes, float4* nodes4, cudaStream_t st);
+
 }  // namespace rt

@@ -20,6 +20,7 @@ namespace rt {
 template <typename T> struct SceneView {
     typedef typename Quad<T>::type Q;
     const float4* nodes;       // global
+    const float4* nodes4;      // global, or null: the same tree as 4-wide records (scenes walked in global memory)
     const Q* sa;               // (center1, radius)
     const Q* sb;               // (center_vec, radius^2)
     const Q* sc;               // (albedo, param)
@@ -211,6 +212,76 @@ __device__ __forceinline__ void trav_node(const float4* __restrict__ nodes, cons
     tv.cur = next;
 }
 
+// ---- 4-wide records (wider nodes for trees that live in global memory) ----
+// A tree that does not fit shared memory is walked at L2 latency: the walk is a chain of dependent 64-byte
+// fetches, one per level.  The 4-wide record of binary node i holds the boxes of i's GRANDCHILDREN (a child
+// that is a leaf stands for itself), so one 128-byte fetch -- one L2 line -- advances the walk two levels:
+//   q0..q3 = child c: (min.x, min.y, max.x, max.y)       every aligned pair = one operand of the packed FMAs
+//   q4 = (min.z c0, min.z c1, max.z c0, max.z c1)   q5 = the same for c2, c3
+//   q6 = bits of the four child refs (same encoding as the binary record; RT_SENTINEL: no such child)
+// Records are indexed by the binary node they were made from (rt_scene.cu widen_kernel), so a ref means the
+// same thing in both forms; the records of the odd levels are simply never visited from the root.
+__device__ __forceinline__ void node4_boxes(const float4* q, const SlabRay<float>& s, float tmin, float tmax, float* tn, bool* hit) {
+    float nz[4], fz[4];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const f32x2 Zl = pack2(q[4 + h].x, q[4 + h].y), Zh = pack2(q[4 + h].z, q[4 + h].w);
+        unpack2(fma2(Zl, s.pzz, fma2(Zh, s.qzz, s.ozz)), nz[2 * h], nz[2 * h + 1]);
+        unpack2(fma2(Zh, s.pzz, fma2(Zl, s.qzz, s.ozz)), fz[2 * h], fz[2 * h + 1]);
+    }
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        const f32x2 Cl = pack2(q[c].x, q[c].y), Ch = pack2(q[c].z, q[c].w);
+        float nx, ny, fx, fy;
+        unpack2(fma2(Cl, s.pxy, fma2(Ch, s.qxy, s.oxy)), nx, ny);
+        unpack2(fma2(Ch, s.pxy, fma2(Cl, s.qxy, s.oxy)), fx, fy);
+        tn[c] = fmaxf(fmaxf(nx, ny), fmaxf(nz[c], tmin));
+        const float tf = fminf(fminf(fx, fy), fminf(fz[c], tmax));
+        hit[c] = tn[c] <= fmaf(tf, 1.000001f, s.delta);
+    }
+}
+__device__ __forceinline__ void node4_boxes(const float4* q, const SlabRay<double>& s, double tmin, double tmax, double* tn, bool* hit) {
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        const float4 z = q[4 + (c >> 1)];
+        const float lz = (c & 1) ? z.y : z.x, hz = (c & 1) ? z.w : z.z;
+        hit[c] = slab(q[c].x, q[c].y, lz, q[c].z, q[c].w, hz, s.o, s.inv, tmin, tmax, tn[c]);
+    }
+}
+
+// one 4-wide node: the children the ray enters, nearest next, the others pushed farthest first
+template <typename T>
+__device__ __forceinline__ void trav_node4(const float4* __restrict__ nodes4, const Ray<T>& r, T tmin, Trav<T>& tv, int* stack) {
+    const float4* rec = nodes4 + 8 * size_t(tv.cur);
+    float4 q[7];
+#pragma unroll
+    for (int k = 0; k < 7; ++k) q[k] = rec[k];
+    T tn[4];
+    bool hit[4];
+    node4_boxes(q, tv.slab, tmin, tv.tbest, tn, hit);
+    const int ref[4] = { __float_as_int(q[6].x), __float_as_int(q[6].y), __float_as_int(q[6].z), __float_as_int(q[6].w) };
+    // sort keys: entry distance (a positive float orders like its bits) with the child number in the two low bits
+    int key[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+        key[c] = (hit[c] && ref[c] != RT_SENTINEL) ? ((__float_as_int(float(tn[c])) & ~3) | c) : 0x7fffffff;
+#define RT_CSWAP(a, b) { const int lo_ = min(key[a], key[b]), hi_ = max(key[a], key[b]); key[a] = lo_; key[b] = hi_; }
+    RT_CSWAP(0, 1) RT_CSWAP(2, 3) RT_CSWAP(0, 2) RT_CSWAP(1, 3) RT_CSWAP(1, 2)
+#undef RT_CSWAP
+#define RT_REF_OF(k) ((key[k] & 2) ? ((key[k] & 1) ? ref[3] : ref[2]) : ((key[k] & 1) ? ref[1] : ref[0]))
+#pragma unroll
+    for (int k = 3; k >= 1; --k)
+        if (key[k] != 0x7fffffff && tv.sp < RT_STACK) { const int f = RT_REF_OF(k); stack[tv.sp++] = f; tv.tos = f; }
+    if (key[0] != 0x7fffffff) {
+        tv.cur = RT_REF_OF(0);
+    } else {                                // nothing entered: pop (top of the stack is in a register)
+        tv.cur = tv.tos;
+        if (tv.sp > 0) --tv.sp;
+        tv.tos = tv.sp > 0 ? stack[tv.sp - 1] : RT_SENTINEL;
+    }
+#undef RT_REF_OF
+}
+
 // one leaf: its 1..8 sphere slots
 template <typename T>
 __device__ __forceinline__ void trav_leaf(const typename Quad<T>::type* __restrict__ sa, const typename Quad<T>::type* __restrict__ sb,
@@ -242,9 +313,16 @@ __device__ __forceinline__ void trace_closest(const SceneView<T>& sv, const floa
     Trav<T> tv;
     int stack[RT_STACK];
     trav_init<T>(sv, r, tmin, tmax, tv);
-    while (tv.cur != RT_SENTINEL) {
-        if (tv.cur >= 0) trav_node<T>(nodes, r, tmin, tv, stack);
-        else trav_leaf<T>(sa, sb, meta, r, tmin, tv, stack);
+    if (sv.nodes4 && nodes == sv.nodes) {          // tree in global memory with 4-wide records
+        while (tv.cur != RT_SENTINEL) {
+            if (tv.cur >= 0) trav_node4<T>(sv.nodes4, r, tmin, tv, stack);
+            else trav_leaf<T>(sa, sb, meta, r, tmin, tv, stack);
+        }
+    } else {
+        while (tv.cur != RT_SENTINEL) {
+            if (tv.cur >= 0) trav_node<T>(nodes, r, tmin, tv, stack);
+            else trav_leaf<T>(sa, sb, meta, r, tmin, tv, stack);
+        }
     }
     t_out = tv.tbest;
     slot_out = tv.best_slot;

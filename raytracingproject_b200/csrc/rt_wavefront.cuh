@@ -59,9 +59,10 @@ __device__ __forceinline__ void accum_add(double4* dst, const Vec<double>& c) {
     *dst = v;
 }
 
-template <typename T, bool STAGED, int P, int BLOCK>
+template <typename T, bool STAGED, int P, int BLOCK, bool WIDE = false>
 __global__ void __launch_bounds__(BLOCK, 1)
 render_pool_kernel(const RenderParams<T> p) {
+    static_assert(!(WIDE && STAGED), "4-wide records are for trees walked in global memory");
     typedef Pool<T, P> L;
     typedef typename Quad<T>::type Q;
     extern __shared__ __align__(16) unsigned char smem[];
@@ -268,8 +269,12 @@ render_pool_kernel(const RenderParams<T> p) {
                         RT_STAT(12, 1); RT_STAT(13, nN); RT_STAT(14, nL); RT_STAT(15, nP);
                         do {
                             RT_STAT(16, 1); RT_STAT(17, now);
-                            if (tv.cur >= 0) trav_node<T>(st.nodes, ray, T(0.001), tv, stack);
-                            if (tv.cur >= 0) trav_node<T>(st.nodes, ray, T(0.001), tv, stack);
+                            if (WIDE) {                    // one 128-byte record = two levels of the tree
+                                if (tv.cur >= 0) trav_node4<T>(sv.nodes4, ray, T(0.001), tv, stack);
+                            } else {
+                                if (tv.cur >= 0) trav_node<T>(st.nodes, ray, T(0.001), tv, stack);
+                                if (tv.cur >= 0) trav_node<T>(st.nodes, ray, T(0.001), tv, stack);
+                            }
                             now = __popc(__ballot_sync(FULL, tv.cur >= 0));
                         } while (now > 0 && now * 8 >= nN * th_n);
                         if (isN && tv.cur == RT_SENTINEL) { F[L::TBEST * P + pid] = tv.tbest; I[L::BEST * P + pid] = tv.best_slot; }

@@ -368,6 +368,45 @@ def test_gpu_lbvh_builder_gives_the_same_hits_and_image(ctx, rt, O):
     assert h.tobytes() == g["hits"].tobytes()
 
 
+def test_four_wide_node_records_give_the_same_hits_and_image(ctx, rt, O):
+    """8f-4, wider nodes: a tree walked in global memory uses 4-wide records (one 128-byte fetch = two levels).
+    Judged like a builder: fixture rays bit-identical in parity mode, float hits identical to brute force, a
+    parity-mode image identical to the oracle in every bounce-loop variant, for both builders, with leaves of
+    several spheres, with the ground inside the tree and with two-sphere / one-sphere trees."""
+    s, m = rt.scene_rtiow()
+    g = golden("ref_closest_hit.npz")
+    for builder, max_leaf, big in ((rt.BVH_LBVH_GPU, 0, 0.0), (rt.BVH_LBVH_GPU, 3, -1.0), (rt.BVH_SAH_HOST, 0, 0.0), (rt.BVH_SAH_HOST, 1, -1.0)):
+        ctx.upload_scene(s, m, builder=builder, max_leaf=max_leaf, big_radius=big, wide=1)
+        h = ctx.trace_closest(g["rays"].view(rt.RAY), precision=rt.F64)
+        assert h.tobytes() == g["hits"].tobytes(), (builder, max_leaf, big)
+        h32 = ctx.trace_closest(g["rays"].view(rt.RAY), precision=rt.F32)
+        b32 = ctx.trace_closest(g["rays"].view(rt.RAY), precision=rt.F32, backend=rt.TRACE_BRUTE)
+        assert np.array_equal(h32["prim"], b32["prim"]) and np.array_equal(h32["t"], b32["t"])
+    cam = rt.camera_rtiow(160, 4, 50)
+    ref = O.render(s.view(O.SPHERE), m.view(O.MATERIAL), O.camera_rtiow(160, 4, 50), rng_mode=O.RNG_PHILOX, seed=7, use_bvh=True)
+    for builder in (rt.BVH_LBVH_GPU, rt.BVH_SAH_HOST):
+        ctx.upload_scene(s, m, builder=builder, wide=1)
+        for variant in VARIANTS:
+            ctx.render(cam, precision=rt.F64, seed=7, variant=variant_of(rt, variant))
+            out = ctx.readback(4)
+            assert ctx.stats()["rays"] == ref["rays"], (builder, variant)
+            assert np.array_equal(out["rgb8"], ref["rgb8"]), (builder, variant)
+            if variant == "wavefront":
+                assert not ctx.stats()["scene_in_smem"]                   # wide = 1: the tree stays in global memory
+        ctx.render(cam, precision=rt.F32, seed=7, variant=rt.WAVEFRONT)
+        o32 = ctx.readback(4)
+        assert np.mean(np.abs(o32["rgb8"].astype(int) - ref["rgb8"].astype(int)).max(-1) <= 1) > 0.999
+    # tiny trees (1 and 2 spheres besides the ground) have free places in the record
+    for n in (2, 3):
+        ctx.upload_scene(s[:n], m, builder=rt.BVH_SAH_HOST, wide=1)
+        small = O.render(s[:n].view(O.SPHERE), m.view(O.MATERIAL), O.camera_rtiow(96, 3, 8), rng_mode=O.RNG_PHILOX, seed=2, use_bvh=True)
+        ctx.render(rt.camera_rtiow(96, 3, 8), precision=rt.F64, seed=2, variant=rt.WAVEFRONT)
+        assert np.array_equal(ctx.readback(3)["rgb8"], small["rgb8"]) and ctx.stats()["rays"] == small["rays"]
+    ctx.upload_scene(s, m, builder=rt.BVH_LBVH_GPU)                                        # default: binary records, scene staged
+    ctx.render(cam, precision=rt.F64, seed=7, variant=rt.WAVEFRONT)
+    assert np.array_equal(ctx.readback(4)["rgb8"], ref["rgb8"]) and ctx.stats()["scene_in_smem"]
+
+
 # ----------------------------------------------------------------------- framebuffer --
 def test_write_color_kernel_matches_oracle(ctx, rt, O):
     rng = np.random.default_rng(1)
