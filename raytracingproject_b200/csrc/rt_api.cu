@@ -460,6 +460,7 @@ int render_impl(rt_ctx* ctx, const rt_camera& cam, const rt_render_opts& o, int 
     p.slices = slices;
     for (int k = 0; k <= slices; ++k) p.slice_begin[k] = ctx->slice_begin[k];
     p.bulk_layers = std::min(slices, ctx->bulk_layers);
+    p.job_group = 2;          // pairs: +0.3-1.5 % over single jobs; 3 and more lose to the tail (profiles/r1_job_group_sweep.txt)
     p.tiles_x = (ctx->W + 7) / 8; p.tiles_y = (ctx->H + 3) / 4;
     p.accumulate = o.accumulate;
     size_t smem = 0;

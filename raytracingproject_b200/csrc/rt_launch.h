@@ -28,6 +28,7 @@ template <typename T> struct RenderParams {
     uint64_t seed;
     int sample_begin, sample_count, max_depth;
     int slices, tiles_x, tiles_y;
+    int job_group;                      // wavefront: jobs fetched at a time = horizontally adjacent tiles of one layer
     int bulk_layers;                    // wavefront job order: tile-major over the first bulk_layers layers, then layer by layer
     int slice_begin[RT_MAX_SLICES + 1]; // wavefront: samples [slice_begin[k], slice_begin[k+1]) of a pixel form layer k (sizes may differ)
     int accumulate;

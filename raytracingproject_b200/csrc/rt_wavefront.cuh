@@ -81,7 +81,11 @@ render_pool_kernel(const RenderParams<T> p) {
     int4* const ring = reinterpret_cast<int4*>(B + L::NL * P);   // job descriptors: (bx | by << 16, s_begin, s_end, slice)
 
     const int W = p.cam.image_width, H = p.cam.image_height;
-    const int njobs = p.tiles_x * p.tiles_y * p.slices;
+    // Jobs are fetched `group` at a time: the same layer of `group` horizontally adjacent tiles, so that the jobs a warp
+    // holds open lie next to each other in the image (rays of neighbouring tiles walk the same part of the tree)
+    const int group = p.job_group, ntiles = p.tiles_x * p.tiles_y, ngroups = (ntiles + group - 1) / group;
+    const int nbulk = ngroups * group * p.bulk_layers, njobs = nbulk + (p.slices - p.bulk_layers) * ntiles;
+    int pend_next = 0, pend_left = 0;
     const size_t layer = size_t(H) * size_t(W);
     const int th_p = p.th_s, th_l = p.th_l, th_n = p.th_n;
     unsigned long long my_rays = 0;
@@ -121,19 +125,23 @@ render_pool_kernel(const RenderParams<T> p) {
                 // fetch one job ahead of the first slot, no more: jobs a warp holds unstarted are the frame's tail
                 if (!exhausted && ((joined >> (8 * newest)) & 0xffu) != 0u && ((joined >> (8 * ((newest + 2) & (R - 1)))) & 0xffu) == unsigned(P)) {
                     int job = 0;
-                    if (lane == 0) job = int(atomicAdd(p.job_counter, 1u));
-                    job = __shfl_sync(FULL, job, 0);
+                    if (pend_left > 0) { job = pend_next++; --pend_left; }
+                    else {
+                        if (lane == 0) job = int(atomicAdd(p.job_counter, unsigned(group)));
+                        job = __shfl_sync(FULL, job, 0);
+                        pend_next = job + 1; pend_left = group - 1;
+                    }
                     if (job >= njobs) exhausted = true;
                     else {
-                        // job order: the bulk layers tile by tile (the jobs a warp holds open then lie a few tile rows apart:
-                        // layer by layer -- 30 tile rows apart -- measured 4 % slower), then the short layers one after the
+                        // job order: the bulk layers group of tiles by group of tiles (layer by layer over the whole image -- the
+                        // open jobs of a warp 30 tile rows apart -- measured 4 % slower), then the short layers one after the
                         // other, so that the frame ends on small jobs
-                        const int ntiles = p.tiles_x * p.tiles_y, nbulk = p.bulk_layers * ntiles;
                         int slice, tile;
-                        if (job < nbulk) { tile = job / p.bulk_layers; slice = job - tile * p.bulk_layers; }
+                        if (job < nbulk) { const int gl = group * p.bulk_layers, g = job / gl, r = job - g * gl; slice = r / group; tile = group * g + (r - slice * group); }
                         else { const int r = job - nbulk; slice = r / ntiles; tile = r - slice * ntiles; slice += p.bulk_layers; }
-                        const int bx = (tile % p.tiles_x) * L::tile_w, by = (tile / p.tiles_x) * L::tile_h;
-                        const int s_begin = p.slice_begin[slice], s_end = p.slice_begin[slice + 1];
+                        const bool none = tile >= ntiles;                       // the last group may be short of tiles: an empty job outside the image
+                        const int bx = none ? 0x7fff : (tile % p.tiles_x) * L::tile_w, by = none ? 0 : (tile / p.tiles_x) * L::tile_h;
+                        const int s_begin = none ? 0 : p.slice_begin[slice], s_end = none ? 0 : p.slice_begin[slice + 1];
                         newest = (newest + 1) & (R - 1); joined &= ~(0xffu << (8 * newest)); progress = true;
                         if (lane == 0) ring[newest] = make_int4(bx | (by << 16), s_begin, s_end, slice);
                     }
