@@ -184,6 +184,11 @@ int rt_get_stats(rt_ctx *ctx, rt_stats *out);
  * -DRT_POOL_STATS (zeros otherwise); out[0] = rays of the last render */
 int rt_debug_counters(rt_ctx *ctx, uint64_t out[32]);
 
+/* host logic, no device needed: the sample layers rt_render cuts a wavefront frame into when rt_render_opts.slices = 0
+ * (bulk layers, then layers that halve).  sizes[] has room for 64 entries; returns how many were written
+ * (they sum to sample_count), *n_bulk = the leading bulk layers.  jobs_per_warp 0 = default. */
+int rt_plan_layers(int sample_count, long long tiles, long long resident_warps, int jobs_per_warp, int *sizes, int *n_bulk);
+
 /* ---- multi-GPU plumbing (one process per GPU) -------------------------------- */
 
 /* Device pointer / geometry of the accumulation buffer so the host framework can reduce it

@@ -72,6 +72,7 @@ SYMBOLS = {
     "rt_accum_buffer": (_I, [_VP, _VP, _VP, _VP]),
     "rt_stream": (_I, [_VP, _VP]),
     "rt_fold_slices": (_I, [_VP]),
+    "rt_plan_layers": (_I, [_I, C.c_longlong, C.c_longlong, _I, _VP, _VP]),
     "rt_ipc_export": (_I, [_VP, _VP]),
     "rt_ipc_open_peers": (_I, [_VP, _VP, _I]),
     "rt_ipc_close_peers": (_I, [_VP]),

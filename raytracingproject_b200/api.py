@@ -269,6 +269,14 @@ class Context:
         return buf.raw[:cap.value]
 
 
+def plan_layers(sample_count, tiles, resident_warps, jobs_per_warp=0):
+    """Host logic alone (no device): the sample layers of a wavefront frame in auto mode -> (sizes, n_bulk)."""
+    sizes = (C.c_int * 64)()
+    n_bulk = C.c_int()
+    n = L.lib().rt_plan_layers(int(sample_count), int(tiles), int(resident_warps), int(jobs_per_warp), sizes, C.byref(n_bulk))
+    return list(sizes[:n]), n_bulk.value
+
+
 def build_bvh_host(spheres, max_leaf=4):
     """Host SAH builder alone (no device).  -> dict(nodes (n_inner,16) f4, order, root_ref, depth)."""
     spheres = np.ascontiguousarray(spheres)

@@ -445,6 +445,26 @@ template <typename T> int pool_shape_for(const rt_ctx* c, int sched, bool* stage
     return shape;
 }
 
+// Sample layers of a wavefront frame (auto mode).  The pool does not drain between jobs (two jobs open per warp), so
+// the job size is free to vary: BULK layers of about 1/20 of a warp's share of the frame each (at least 8 samples: a
+// slot that finishes the newer job waits for the stragglers of the older one), then layers that halve down to a few
+// samples.  The short layers are taken last, so the frame ends on small jobs: the tail is a job or two per warp,
+// whatever its size (measured: profiles/r1_job_overhead_ring2.txt, r1_job_sizes_geometric.txt).
+// sizes[0..n) sum to sample_count, n <= RT_MAX_SLICES; *n_bulk = how many of them are bulk layers.
+int plan_layers(int sample_count, long long tiles, long long resident_warps, int jobs_per_warp, int* sizes, int* n_bulk) {
+    if (jobs_per_warp <= 0) jobs_per_warp = 20;                    // 16-24 measured best, flat
+    const double tiles_per_warp = double(std::max<long long>(1, tiles)) / double(std::max<long long>(1, resident_warps));
+    int bulk = std::max(8, int(std::ceil(sample_count * tiles_per_warp / double(jobs_per_warp))));
+    bulk = std::max(bulk, (sample_count + RT_MAX_SLICES - 9) / (RT_MAX_SLICES - 8));       // all of them fit the buffer's 64 layers
+    const int small = std::max(2, bulk / 8);
+    int left = sample_count, n = 0;
+    while (left > 2 * bulk && n < RT_MAX_SLICES - 8) { sizes[n++] = bulk; left -= bulk; }
+    *n_bulk = n;
+    while (left > small && n < RT_MAX_SLICES - 1) { const int h = (left + 1) / 2; sizes[n++] = h; left -= h; }
+    if (left > 0) sizes[n++] = left;
+    return n;
+}
+
 template <typename T>
 int render_impl(rt_ctx* ctx, const rt_camera& cam, const rt_render_opts& o, int sample_begin, int sample_count, int slices) {
     typedef typename Quad<T>::type Q;
@@ -528,21 +548,7 @@ extern "C" int rt_render(rt_ctx* ctx, const rt_camera* cam, const rt_render_opts
     if (slices <= 0 && opts->precision == RT_F64) slices = 1;
     int sizes[RT_MAX_SLICES], n_sized = -1, n_bulk = 0;
     if (slices <= 0 && opts->variant == RT_WAVEFRONT && sample_count > 0) {
-        // The pool does not drain between jobs (two jobs open per warp), so the job size is free to vary: BULK layers
-        // of about 1/20 of a warp's share of the frame each (at least 8 samples: a slot that finishes the newer job
-        // waits for the stragglers of the older one), then layers that halve down to a few samples.  Jobs are taken
-        // layer by layer, so the frame ends on the small ones: the tail is a job or two per warp, whatever its size
-        // (measured: profiles/r1_job_overhead_ring2.txt, r1_job_sizes_geometric.txt)
-        const double tiles_per_warp = double(tiles) / double(resident_warps);
-        const int jobs_per_warp = ((opts->sched >> 24) & 0xff) ? ((opts->sched >> 24) & 0xff) : 20;      // tuning: bulk jobs per warp (16-24 measured best, flat: profiles/r1_job_sizes_geometric.txt)
-        const int bulk = std::max(8, int(std::ceil(sample_count * tiles_per_warp / double(jobs_per_warp))));
-        const int small = std::max(2, bulk / 8);
-        int left = sample_count, n = 0;
-        while (left > 2 * bulk && n < RT_MAX_SLICES - 8) { sizes[n++] = bulk; left -= bulk; }
-        n_bulk = n;
-        while (left > small && n < RT_MAX_SLICES - 1) { const int h = (left + 1) / 2; sizes[n++] = h; left -= h; }
-        if (left > 0) sizes[n++] = left;
-        slices = n; n_sized = n;
+        slices = n_sized = plan_layers(sample_count, tiles, resident_warps, (opts->sched >> 24) & 0xff, sizes, &n_bulk);
     }
     if (slices <= 0) slices = int(std::min<long long>(64, (16 * resident_warps + tiles - 1) / tiles));
     slices = std::max(1, std::min(std::min(slices, RT_MAX_SLICES), std::max(1, sample_count)));
@@ -709,6 +715,11 @@ extern "C" int rt_accum_buffer(rt_ctx* ctx, void** dev_ptr, size_t* n_elems, int
     if (n_elems) *n_elems = size_t(ctx->slices) * ctx->W * ctx->H * 4;
     if (elem_bytes) *elem_bytes = ctx->precision == RT_F32 ? 4 : 8;
     return RT_OK;
+}
+
+extern "C" int rt_plan_layers(int sample_count, long long tiles, long long resident_warps, int jobs_per_warp, int* sizes, int* n_bulk) {
+    if (sample_count <= 0 || !sizes || !n_bulk) return 0;
+    return plan_layers(sample_count, tiles, resident_warps, jobs_per_warp, sizes, n_bulk);
 }
 
 extern "C" int rt_fold_slices(rt_ctx* ctx) {

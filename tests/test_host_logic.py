@@ -115,3 +115,25 @@ def test_sample_shards_partition_the_samples():
     assert sorted(rows.tolist()) == list(range(225))
     with pytest.raises(ValueError):
         sample_shard(10, 2, 2)
+
+
+def test_wavefront_layer_plan():
+    """rt_plan_layers (host logic of rt_render, auto mode): bulk layers of a warp's share / 20 (>= 8 samples), then
+    layers that halve; whatever the frame, the layers partition the samples, stay within the 64 layers of the
+    accumulation buffer and within the 14-bit sample index of a job."""
+    import raytracingproject_b200 as rt
+    warps_c3, tiles_1080p, tiles_4k = 148 * 24, 120 * 135, 240 * 270
+    for spp, tiles, warps in ((500, tiles_1080p, warps_c3), (62, tiles_1080p, warps_c3), (8, tiles_1080p, warps_c3), (1, tiles_1080p, warps_c3),
+                              (1000, tiles_1080p, warps_c3), (64, tiles_4k, 148 * 32), (8, tiles_4k, 148 * 32), (16383, 1, warps_c3),
+                              (16383, tiles_4k, 148 * 8), (3, 1, 1), (129, 7, 100000)):
+        sizes, n_bulk = rt.plan_layers(spp, tiles, warps)
+        assert sum(sizes) == spp and 1 <= len(sizes) <= 64 and all(1 <= x <= 16383 for x in sizes), (spp, tiles, warps, sizes)
+        assert 0 <= n_bulk <= len(sizes) and len(set(sizes[:n_bulk])) <= 1          # bulk layers are equal
+        tail = sizes[n_bulk:]
+        assert all(a >= b for a, b in zip(tail, tail[1:-1])), sizes                  # then they shrink (the last takes the rest)
+        if n_bulk:
+            assert sizes[0] >= 8 and max(tail) <= 2 * sizes[0]
+    sizes, n_bulk = rt.plan_layers(500, tiles_1080p, warps_c3)
+    assert n_bulk >= 3 and sizes[-1] <= sizes[0] // 4                                # C3: the frame ends on small jobs
+    assert rt.plan_layers(500, tiles_1080p, warps_c3, jobs_per_warp=40)[0][0] < sizes[0]
+    assert rt.plan_layers(0, 10, 10) == ([], 0)
