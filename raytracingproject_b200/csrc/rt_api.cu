@@ -518,7 +518,8 @@ extern "C" int rt_render(rt_ctx* ctx, const rt_camera* cam, const rt_render_opts
     // the wavefront pool keeps a path's sample index in 14 bits and its remaining depth in 16: beyond that the
     // warp-scheduled megakernel (same arithmetic, same image) takes the call
     rt_render_opts eff = *opts;
-    if (eff.variant == RT_WAVEFRONT && (cam->max_depth > 65535 ||
+    // (and a job's tile origin in 15 + 16 bits)
+    if (eff.variant == RT_WAVEFRONT && (cam->max_depth > 65535 || cam->image_width > 32000 || image_height_of(*cam) > 32000 ||
         (eff.sample_count > 0 ? eff.sample_count : cam->samples_per_pixel) > 16383)) { eff.variant = RT_MEGAKERNEL; eff.sched = 0; }
     opts = &eff;
     CK(cudaSetDevice(ctx->device));

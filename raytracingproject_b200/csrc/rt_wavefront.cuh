@@ -40,7 +40,7 @@ namespace rt {
 template <typename T, int P> struct Pool {
     enum { OX, OY, OZ, TM, DX, DY, DZ, TR, TG, TB, TBEST, NF };        // T arrays [P]
     enum { BEST, NI };                                                  // int arrays [P]
-    enum { SAMPLE, DEPTH, NH };                                         // 16-bit arrays [P]: ring entry << 14 | next sample relative to the job's first (0x3fff: done with that job); bounces left
+    enum { SAMPLE, DEPTH, NH };                                         // 16-bit arrays [P]: ring entry (top 1 or 2 bits) | next sample relative to the job's first (all ones: done with that job); bounces left
     enum { QUEUE, LOPAQUE, LGLASS, LEND, NL };                          // byte lists [P]
     static constexpr int ring = RT_RING, ring_bytes = 16 * ring;        // job descriptors (int4) of the warp, after the lists
     static constexpr int bytes = NF * P * int(sizeof(T)) + NI * P * 4 + NH * P * 2 + NL * P + ring_bytes;
