@@ -33,6 +33,10 @@
 
 namespace rt {
 
+#ifndef RT_NODE_VISITS
+#define RT_NODE_VISITS 3               // node visits per head-count ballot of the TRACE stage (3 measured best of 2 / 3 / 4 / 6: profiles/r1_node_visits_ab.txt)
+#endif
+
 #ifndef RT_RING
 #define RT_RING 2                      // jobs a warp keeps open (2 or 4)
 #endif
@@ -271,7 +275,7 @@ render_pool_kernel(const RenderParams<T> p) {
                             if (tv.cur == RT_SENTINEL) { F[L::TBEST * P + pid] = tv.tbest; I[L::BEST * P + pid] = tv.best_slot; }
                         }
                     } else {
-                        // node visits, two per head count, repeated while most of the lanes that started them
+                        // node visits, RT_NODE_VISITS per head count, repeated while most of the lanes that started them
                         // still have a node; a lane whose walk ends hands in its result after the loop
                         int now = nN;
                         RT_STAT(12, 1); RT_STAT(13, nN); RT_STAT(14, nL); RT_STAT(15, nP);
@@ -280,8 +284,9 @@ render_pool_kernel(const RenderParams<T> p) {
                             if (WIDE) {                    // one 128-byte record = two levels of the tree
                                 if (tv.cur >= 0) trav_node4<T>(sv.nodes4, ray, T(0.001), tv, stack);
                             } else {
-                                if (tv.cur >= 0) trav_node<T>(st.nodes, ray, T(0.001), tv, stack);
-                                if (tv.cur >= 0) trav_node<T>(st.nodes, ray, T(0.001), tv, stack);
+#pragma unroll
+                                for (int v = 0; v < RT_NODE_VISITS; ++v)
+                                    if (tv.cur >= 0) trav_node<T>(st.nodes, ray, T(0.001), tv, stack);
                             }
                             now = __popc(__ballot_sync(FULL, tv.cur >= 0));
                         } while (now > 0 && now * 8 >= nN * th_n);
