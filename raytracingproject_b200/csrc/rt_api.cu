@@ -496,7 +496,7 @@ int render_impl(rt_ctx* ctx, const rt_camera& cam, const rt_render_opts& o, int 
     CK(cudaMemsetAsync(ctx->ray_counter.p, 0, 32 * sizeof(unsigned long long), ctx->stream));
     CK(cudaEventRecord(ctx->ev[0], ctx->stream));
     // section thresholds: o.sched = th_s | th_l << 8 (0 = defaults, tuned on B200: see DESIGN.md)
-    p.th_s = (o.sched & 0xff) ? (o.sched & 0xff) : (o.variant == RT_WAVEFRONT ? 24 : 28);
+    p.th_s = (o.sched & 0xff) ? (o.sched & 0xff) : (o.variant == RT_WAVEFRONT ? 22 : 28);       // wavefront: idle lanes before a pull (profiles/r1_sched_tune_final.txt)
     p.th_l = ((o.sched >> 8) & 0xff) ? ((o.sched >> 8) & 0xff) : 33;
     p.th_n = ((o.sched >> 20) & 0xf) ? ((o.sched >> 20) & 0xf) : 4;      // node loop runs while >= th_n/8 of its lanes remain
     if (o.variant == RT_WAVEFRONT) CK(launch_render_pool<T>(p, pshape, staged, ctx->sm_count, ctx->stream));
