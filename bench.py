@@ -90,9 +90,10 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def cpu_reference_run(spp_sample, threads, steps=1, warmup=0):
+def cpu_reference_run(spp_sample, threads, steps=1, warmup=0, use_bvh=False):
     """The reference's CPU path on a bounded sample of the C3 frame: full 1920x1080 resolution,
-    `spp_sample` of the 500 samples per pixel, linear hittable_list exactly as shipped."""
+    `spp_sample` of the 500 samples per pixel; linear hittable_list exactly as shipped, or (use_bvh) the
+    reference's bvh_node::hit (src/bvh.h:16-24, made to compile and given a builder by the harness)."""
     from oracle import oracle as O
     s, m = O.scene_rtiow()
     cam = O.camera_rtiow(WIDTH, spp_sample, DEPTH)
@@ -101,16 +102,34 @@ def cpu_reference_run(spp_sample, threads, steps=1, warmup=0):
     times, rays = [], 0
     for it in range(warmup + steps):
         t0 = time.perf_counter()
-        r = O.render(s, m, cam, rng_mode=O.RNG_PHILOX, seed=0, nthreads=threads, impl=impl, use_bvh=False)
+        r = O.render(s, m, cam, rng_mode=O.RNG_PHILOX, seed=0, nthreads=threads, impl=impl, use_bvh=use_bvh)
         dt = time.perf_counter() - t0
         if it >= warmup:
             times.append(dt); rays = r["rays"]
     dt = sum(times) / len(times)
     samples = WIDTH * r["height"] * spp_sample
+    world = ("bvh_node::hit over the harness-built tree (src/bvh.h:16-24; the reference ships no builder)" if use_bvh else
+             "linear hittable_list (no BVH, as src/main.cpp:12,70)")
     return {"value": samples / dt / 1e6, "unit": "Msamples/s", "cores": threads, "kind": kind,
             "mrays_per_s": rays / dt / 1e6, "seconds_per_step": dt,
-            "sample": f"{WIDTH}x{r['height']} at {spp_sample} of {SPP} spp, depth {DEPTH}, linear hittable_list (no BVH, as "
-                      f"src/main.cpp:12,70), keyed Philox stream, {threads} host threads over rows"}
+            "sample": f"{WIDTH}x{r['height']} at {spp_sample} of {SPP} spp, depth {DEPTH}, {world}, keyed Philox stream, "
+                      f"{threads} host threads over rows"}
+
+
+def cpu_as_shipped_run():
+    """The reference exactly as shipped: src/main.cpp unmodified (400x225, 30 spp, depth 50, global mt19937,
+    ONE thread, linear hittable_list), stdout captured by the harness.  ~25-40 s.  None without the reference build."""
+    from oracle import oracle as O
+    if not (O.have_ref() and os.path.exists(O.LIB_REF)):
+        return None
+    t0 = time.perf_counter()
+    ppm = O.ref_main_ppm()
+    dt = time.perf_counter() - t0
+    samples = 400 * 225 * 30
+    return {"value": samples / dt / 1e6, "unit": "Msamples/s", "cores": 1, "kind": "reference", "seconds": dt,
+            "mrays_per_s": 6968725 / dt / 1e6,
+            "sample": f"src/main.cpp as shipped: 400x225, 30 spp, depth 50, mt19937, 1 thread, linear list; {len(ppm)} bytes of P3 "
+                      "(6 968 725 rays, SURVEY.md 8c); the C3 frame is 384x this many samples"}
 
 
 def run_reference(args):
@@ -131,6 +150,73 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def run_c2(args):
+    """BASELINE config 2: closest-hit microbenchmark, 2^26 synthetic rays generated in-kernel against the final-scene
+    BVH (isolates traversal).  One GPU (rank 0; the path has no multi-GPU form).  `value` = device time of the
+    trace kernel alone, rays generated in-kernel, results left on the device; `e2e` = the rt_bench_closest call with the
+    per-ray results (prim id + t, 8 B per ray) copied to host arrays.  Untimed: exact primitive-id check of 2^20 of the
+    rays against the oracle's linear list (hittable_list::hit, reference src/hittable_list.h:25-39)."""
+    import numpy as np
+    import torch
+    import raytracingproject_b200 as rt
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the B200 path has no CPU fallback")
+    n = 1 << 26
+    prec = rt.F32 if args.precision == "f32" else rt.F64
+    ctx = rt.Context(int(os.environ.get("LOCAL_RANK", "0")))
+    s, m = rt.scene_rtiow()
+    ctx.upload_scene(s, m)
+    cam = rt.camera_rtiow(400, 10, DEPTH)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    sampler = ClockSampler(int(os.environ.get("LOCAL_RANK", "0")))
+    for _ in range(max(3, args.warmup)):
+        ctx.bench_closest(cam, n, seed=1, precision=prec)
+    sampler.start()
+    times = []
+    for _ in range(args.steps):
+        flush.fill_(1); torch.cuda.synchronize()
+        times.append(ctx.bench_closest(cam, n, seed=1, precision=prec)["ms"])         # CUDA events on the ctx stream, inside the call
+    clocks = sampler.stop()
+    e2e = []
+    for _ in range(2):
+        t0 = time.perf_counter()
+        r = ctx.bench_closest(cam, n, seed=1, precision=prec, want_results=True)
+        e2e.append((time.perf_counter() - t0) * 1e3)
+    hit_frac = float((r["prim"] >= 0).mean())
+    check = None
+    if not args.no_check:
+        from oracle import oracle as O
+        nb = 1 << 20
+        d = ctx.bench_closest(cam, nb, seed=1, precision=prec, want_results=True, dump_rays=nb)
+        want = O.closest_hit(O.scene_rtiow()[0], d["rays"].view(O.RAY))
+        check = {"rays_checked": nb, "oracle": "linear hittable_list::hit on the dumped rays", "prim_id_mismatches": int((d["prim"] != want["prim"]).sum())}
+    ms = sum(times) / len(times)
+    levels = int(np.ceil(np.log2(len(s))))
+    f_ray = 48.0 * levels + 29.0 + 22.0          # SURVEY.md 8d without the scatter / sky term: box tests + one sphere test + hit completion
+    pk = peaks()
+    sm_mhz = clocks.get("sm_mhz") or pk.get("sm_max_mhz", 1965.0)
+    fp32_peak = 148 * 128 * 2 * sm_mhz * 1e6 / 1e12
+    achieved = n * f_ray / (ms * 1e-3) / 1e12
+    line = {"metric": "Mrays/s", "value": n / ms / 1e3, "unit": "Mrays/s", "n_gpus": 1, "steps": args.steps, "warmup": max(3, args.warmup),
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
+            "config": {"workload": "C2: closest-hit microbenchmark, 2^26 synthetic rays (even: get_ray of a virtual 8192x8192 image, odd: incoherent) "
+                                   "vs the final-scene BVH (485 spheres, host SAH, scene staged in shared memory)",
+                       "l2": "256 MB buffer written between timed iterations; the kernel reads no input from HBM (rays from counters)",
+                       "hit_fraction": hit_frac},
+            "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak, "traffic": None,
+                         "kernel": "bench_closest_kernel", "kernel_ms": ms,
+                         "note": f"algorithmic {f_ray:.0f} flop/ray (48 x {levels} levels + 29 sphere test + 22 hit completion) x 2^26 rays; "
+                                 f"output 8 B/ray = {8 * n / (ms * 1e-3) / 1e9:.0f} GB/s written"},
+            "e2e": {"value": n / (sum(e2e) / len(e2e)) / 1e3, "unit": "Mrays/s", "ms_per_step": sum(e2e) / len(e2e),
+                    "h2d_bytes_per_step": 104, "d2h_bytes_per_step": 8 * n, "api": "rt_bench_closest with prim/t copied to host arrays"},
+            "gpu_launches": args.steps, "clocks": clocks}
+    if check:
+        line["id_check"] = check
+    print(json.dumps(line), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -140,14 +226,17 @@ def main():
     ap.add_argument("--precision", default="f32", choices=["f32", "f64"])
     ap.add_argument("--combine", default="nccl", choices=["nccl", "ipc"])
     ap.add_argument("--variant", default="wavefront", choices=["wavefront", "megakernel", "lockstep"])
-    ap.add_argument("--config", default="c3", choices=sorted(CONFIGS), help="BASELINE.json config (default c3 = the headline one)")
+    ap.add_argument("--config", default="c3", choices=sorted(CONFIGS) + ["c2"], help="BASELINE.json config (default c3 = the headline one)")
     ap.add_argument("--spp", type=int, default=0, help="override spp (a non-default value is NOT the named config)")
     ap.add_argument("--ref-spp", type=int, default=1, help="spp of the CPU sample per step for --impl reference / cpu_baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-cpu-as-shipped", action="store_true", help="skip the ~30 s single-thread run of src/main.cpp as shipped")
     ap.add_argument("--no-check", action="store_true", help="skip the untimed f32-vs-f64 image check")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
+    if args.config == "c2":
+        return run_c2(args)
     args.warmup = max(args.warmup, 3)
 
     import numpy as np
@@ -255,6 +344,24 @@ def main():
     e2e_times, _, _, _, e2e_out = timed(True, max(2, min(args.steps, 3)), 1)
     launches = ctx.stats()["kernel_launches"]
 
+    # untimed, N > 1: the COMBINED frame of the last end-to-end step (folded, reduced over NVLink, resolved on rank 0)
+    # against the same frame rendered by rank 0 alone.  The float partial sums re-associate, nothing else may differ.
+    multi_check = None
+    if world > 1 and not args.no_check:
+        combined = pin_rgb8.reshape(H, W, 3).copy() if rank == 0 else None
+        if args.combine == "ipc" and rank == 0:
+            ctx.ipc_close_peers()
+        barrier()
+        if rank == 0:
+            ctx.render(cam, precision=prec, seed=0, variant=variant)
+            solo = ctx.readback(args.spp, want_sum=False)["rgb8"]
+            d = np.abs(combined.astype(int) - solo.astype(int)).max(-1)
+            mse = float(np.mean((combined.astype(float) - solo.astype(float)) ** 2))
+            multi_check = {"combined_vs_single_gpu_max_byte_diff": int(d.max()),
+                           "combined_vs_single_gpu_psnr_db": 99.0 if mse == 0 else float(10 * np.log10(255.0 ** 2 / mse)),
+                           "frac_pixels_identical": float((d == 0).mean()), "ranks": world, "combine": args.combine}
+        barrier()
+
     # untimed: the fast mode against parity mode on this very frame (north_star image tolerance)
     check = None
     if rank == 0 and world == 1 and not args.no_check and args.precision == "f32" and headline:
@@ -309,9 +416,20 @@ def main():
         }
         if check:
             line["image_check"] = check
+        if multi_check:
+            line["image_check"] = multi_check
         if not args.no_cpu_baseline and world == 1 and headline:
+            keys = ("value", "unit", "cores", "kind", "sample", "mrays_per_s")
             cb = cpu_reference_run(max(1, args.ref_spp), os.cpu_count() or 1)
-            line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+            line["cpu_baseline"] = {k: cb[k] for k in keys}
+            # how much of the ratio is the BVH, and the reference as it ships
+            cbb = cpu_reference_run(4 * max(1, args.ref_spp), os.cpu_count() or 1, use_bvh=True)
+            line["cpu_baseline_bvh"] = {k: cbb[k] for k in keys}
+            line["cpu_baseline_bvh"]["speedup_over_linear_list"] = cbb["value"] / cb["value"]
+            if not args.no_cpu_as_shipped:
+                ca = cpu_as_shipped_run()
+                if ca:
+                    line["cpu_baseline_as_shipped"] = {k: ca[k] for k in keys}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()

@@ -126,7 +126,8 @@ typedef struct {
     int32_t  n_spheres, n_big, n_nodes, bvh_depth;
     int32_t  image_width, image_height;
     int32_t  slices, kernel_launches;   /* launches of this library's kernels in the last render+resolve */
-    int32_t  scene_in_smem, pad;
+    int32_t  scene_in_smem;  /* last render: 1 = whole scene staged in shared memory, 2 = top levels of the tree only, 0 = global */
+    int32_t  big_in_tree;    /* spheres with radius >= big_radius beyond the 16 largest: they are in the tree like any sphere */
 } rt_stats;
 
 typedef struct rt_ctx rt_ctx;
@@ -202,10 +203,15 @@ int rt_accum_buffer(rt_ctx *ctx, void **dev_ptr, size_t *n_elems, int *elem_byte
  * fused resolve then reads layer 0 of each peer only).  The next rt_render ends the folded state. */
 int rt_fold_slices(rt_ctx *ctx);
 int rt_stream(rt_ctx *ctx, void **cuda_stream);
-/* CUDA IPC handle (64 bytes) of the accumulation buffer, and the fused peer reduce + resolve:
- * rank 0 reads every peer's partial buffer over NVLink inside the resolve kernel. */
-int rt_ipc_export(rt_ctx *ctx, void *handle64);
-int rt_ipc_open_peers(rt_ctx *ctx, const void *handles64, int n_peers);   /* peers other than self */
+/* The fused peer reduce + resolve: rank 0 reads every peer's partial buffer over NVLink inside the resolve
+ * kernel.  rt_ipc_export writes RT_IPC_HANDLE_BYTES: the CUDA IPC handle of the accumulation buffer + its
+ * image size and precision; rt_ipc_open_peers (n_peers blobs back to back) refuses peers whose frame differs
+ * from this context's.  Only layer 0 of a peer is read, so every rank must rt_fold_slices before rank 0
+ * resolves (rt_readback fails with RT_E_STATE otherwise).  A context whose frame changes shape drops its
+ * mappings; a rank whose buffer was reallocated (larger frame or more layers) must export again. */
+#define RT_IPC_HANDLE_BYTES 80
+int rt_ipc_export(rt_ctx *ctx, void *handle);
+int rt_ipc_open_peers(rt_ctx *ctx, const void *handles, int n_peers);   /* peers other than self */
 int rt_ipc_close_peers(rt_ctx *ctx);
 
 /* ---- parity / microbenchmark hooks (same code the render path runs) ------------------------- */

@@ -12,6 +12,7 @@
 #ifndef RTP_CAMERA_B200_H
 #define RTP_CAMERA_B200_H
 
+#include <cstring>
 #include <string>
 
 #include "camera.h"
@@ -114,10 +115,12 @@ class Camera : public camera {
   private:
     mutable rt_ctx* ctx_ = nullptr;
     mutable rt_scene_builder scene_;
-    mutable const hittable* uploaded_ = nullptr;
-    mutable size_t uploaded_count_ = 0;
+    mutable bool have_scene_ = false;
     mutable uint32_t next_sample_ = 0;
 
+    template <typename V> static bool same_pod(const V& a, const V& b) {
+        return a.size() == b.size() && (a.empty() || std::memcmp(a.data(), b.data(), a.size() * sizeof(a[0])) == 0);
+    }
     static rt_ray to_pod(const ray& r) {
         rt_ray p;
         for (int k = 0; k < 3; ++k) { p.orig[k] = r.origin()[k]; p.dir[k] = r.direction()[k]; }
@@ -134,12 +137,14 @@ class Camera : public camera {
         ensure_ctx();
         rt_scene_builder b;
         world.describe(b);
-        if (uploaded_ == &world && uploaded_count_ == b.spheres.size()) return;   // same world as last time
+        // skip the upload only when the world DESCRIBES the same as the one on the device: a world edited in place (or
+        // another list at the same address) must be rendered as it is now, as the reference does (src/camera.h:32)
+        if (have_scene_ && same_pod(b.spheres, scene_.spheres) && same_pod(b.materials, scene_.materials)) return;
         rt_bvh_opts o = {};
         o.abi = RT_ABI_VERSION; o.builder = bvh_builder;
         check(rt_upload_scene(ctx_, b.spheres.data(), b.spheres.size(), b.materials.data(), b.materials.size(), &o), "rt_upload_scene");
         scene_ = std::move(b);
-        uploaded_ = &world; uploaded_count_ = scene_.spheres.size();
+        have_scene_ = true;
     }
 };
 

@@ -19,6 +19,7 @@ LAMBERTIAN, METAL, DIELECTRIC = 0, 1, 2
 SPHERE = np.dtype([("center1", "f8", 3), ("center_vec", "f8", 3), ("radius", "f8"),
                    ("is_moving", "i4"), ("material", "i4")])
 IMG_P3, IMG_P6, IMG_PFM = 0, 1, 2
+IPC_HANDLE_BYTES = 80
 DEMO_SPHERE = np.dtype([("center", "f4", 3), ("radius", "f4"), ("color", "f4", 4)])    # rt_demo_sphere
 MATERIAL = np.dtype([("type", "i4"), ("pad", "i4"), ("albedo", "f8", 3), ("param", "f8")])
 RAY = np.dtype([("orig", "f8", 3), ("dir", "f8", 3), ("tm", "f8")])
@@ -50,7 +51,7 @@ class Stats(C.Structure):
                 ("n_spheres", C.c_int32), ("n_big", C.c_int32), ("n_nodes", C.c_int32), ("bvh_depth", C.c_int32),
                 ("image_width", C.c_int32), ("image_height", C.c_int32),
                 ("slices", C.c_int32), ("kernel_launches", C.c_int32),
-                ("scene_in_smem", C.c_int32), ("pad", C.c_int32)]
+                ("scene_in_smem", C.c_int32), ("big_in_tree", C.c_int32)]
 
 
 # every symbol include/rt_b200.h declares: name -> (restype, argtypes)

@@ -122,7 +122,7 @@ class Context:
         o = L.BvhOpts(L.ABI, builder, max_leaf, wide, big_radius)
         self._ck(self._lib.rt_upload_scene(self._h, L.ptr(spheres), len(spheres), L.ptr(materials), len(materials), C.byref(o)))
 
-    def render(self, cam, precision=L.F32, seed=0, variant=L.MEGAKERNEL, sample_begin=0, sample_count=0,
+    def render(self, cam, precision=L.F32, seed=0, variant=L.WAVEFRONT, sample_begin=0, sample_count=0,
                accumulate=False, slices=0, sched=0):
         o = L.RenderOpts(L.ABI, precision, variant, sample_begin, sample_count, int(accumulate), seed, slices, sched)
         self._ck(self._lib.rt_render(self._h, C.byref(cam), C.byref(o)))
@@ -203,7 +203,7 @@ class Context:
         return p.value or 0
 
     def ipc_export(self):
-        buf = (C.c_ubyte * 64)()
+        buf = (C.c_ubyte * L.IPC_HANDLE_BYTES)()
         self._ck(self._lib.rt_ipc_export(self._h, buf))
         return bytes(buf)
 

@@ -30,6 +30,8 @@ static_assert(sizeof(MatRec) == sizeof(rt_material), "MatRec mirrors rt_material
 
 namespace {
 
+const size_t RT_MAX_BIG = 16;          // spheres kept out of the tree (tested by every ray, in double)
+
 std::string g_create_error;
 
 template <typename T> struct DevBuf {
@@ -282,6 +284,9 @@ extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_s
     CK(cudaSetDevice(ctx->device));
     CK(cudaStreamSynchronize(ctx->stream));
     const auto t_start = std::chrono::steady_clock::now();
+    // from here on the device buffers are rewritten: until the upload has succeeded as a whole there is NO scene
+    // (an error exit must not leave the old counts and root paired with new node / slot data)
+    ctx->has_scene = false; ctx->root_ref = RT_SENTINEL; ctx->n_nodes = 0; ctx->n_slots = 0; ctx->n_big = 0;
 
     for (size_t i = 0; i < n_spheres; ++i) {
         if (spheres[i].material < 0 || size_t(spheres[i].material) >= n_materials)
@@ -291,10 +296,26 @@ extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_s
     }
 
     // split: outsized spheres stay out of the tree (tested first, in double)
+    // (every ray tests every one of them: at most RT_MAX_BIG, the LARGEST ones; further candidates go into the tree like
+    // any sphere -- same hits, float boxes around a huge sphere just prune less -- and are reported in rt_stats.big_in_tree)
     std::vector<int> tree_ids, big_ids;
-    for (size_t i = 0; i < n_spheres; ++i) {
-        if (std::fabs(spheres[i].radius) >= big_radius && big_ids.size() < 16) big_ids.push_back(int(i));
-        else tree_ids.push_back(int(i));
+    for (size_t i = 0; i < n_spheres; ++i)
+        if (std::fabs(spheres[i].radius) >= big_radius) big_ids.push_back(int(i));
+    int big_in_tree = 0;
+    if (big_ids.size() > RT_MAX_BIG) {
+        std::vector<int> by_radius = big_ids;
+        std::stable_sort(by_radius.begin(), by_radius.end(), [&](int a, int b) { return std::fabs(spheres[a].radius) > std::fabs(spheres[b].radius); });
+        by_radius.resize(RT_MAX_BIG);
+        std::sort(by_radius.begin(), by_radius.end());                     // list order again
+        big_in_tree = int(big_ids.size() - by_radius.size());
+        big_ids.swap(by_radius);
+    }
+    {
+        size_t k = 0;
+        for (size_t i = 0; i < n_spheres; ++i) {
+            if (k < big_ids.size() && big_ids[k] == int(i)) ++k;
+            else tree_ids.push_back(int(i));
+        }
     }
     const int n_tree = int(tree_ids.size());
     const size_t nt = std::max(1, n_tree), nb = std::max<size_t>(1, big_ids.size());
@@ -397,6 +418,10 @@ extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_s
         const int want = opts ? opts->wide : 0;
         ctx->wide_forced = want > 0;
         ctx->wide = ctx->n_nodes > 0 && want > 0;
+        // the 4-wide walk pushes up to 3 refs per record = per two levels of the binary tree: a tree the binary walk
+        // can hold (depth <= RT_STACK) may still overflow here
+        if (ctx->wide && 3 * ((ctx->depth + 1) / 2) > RT_STACK)
+            return fail(ctx, RT_E_INVALID, "rt_upload_scene: tree too deep for the 4-wide walk (3 * ceil(depth / 2) > traversal stack); use wide = 0");
         if (ctx->wide) {
             CK(ctx->nodes4.resize(size_t(ctx->n_nodes) * 8));
             CK(launch_widen(ctx->nodes.p, ctx->n_nodes, ctx->nodes4.p, ctx->stream));
@@ -408,7 +433,7 @@ extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_s
     ctx->n_spheres = int(n_spheres); ctx->n_slots = n_tree; ctx->n_big = int(big_ids.size());
     ctx->has_scene = true;
     ctx->upload_ms = ms_since(t_start);
-    ctx->stats.n_spheres = ctx->n_spheres; ctx->stats.n_big = ctx->n_big; ctx->stats.n_nodes = ctx->n_nodes;
+    ctx->stats.n_spheres = ctx->n_spheres; ctx->stats.n_big = ctx->n_big; ctx->stats.n_nodes = ctx->n_nodes; ctx->stats.big_in_tree = big_in_tree;
     ctx->stats.bvh_depth = ctx->depth; ctx->stats.build_ms = ctx->build_ms; ctx->stats.upload_ms = ctx->upload_ms;
     return RT_OK;
 }
@@ -561,6 +586,9 @@ extern "C" int rt_render(rt_ctx* ctx, const rt_camera* cam, const rt_render_opts
     const bool same = fits && (opts->accumulate || slices == ctx->slices);
     if (opts->accumulate && !fits) return fail(ctx, RT_E_STATE, "rt_render: accumulate needs the same image and precision as the buffer, and no more slices than it holds");
     if (!same) {
+        // the frame changes shape: mappings of peers that rendered the old shape are dropped (the caller exchanges
+        // handles again), and this context's own exported handle is stale if the buffer has to grow
+        if (ctx->peers.n > 0 && (ctx->W != W || ctx->H != H || ctx->precision != opts->precision)) rt_ipc_close_peers(ctx);
         CK(ctx->accum.resize(size_t(slices) * W * H * elem));
         ctx->W = W; ctx->H = H; ctx->precision = opts->precision; ctx->slices = slices;
     }
@@ -586,6 +614,7 @@ extern "C" int rt_readback(rt_ctx* ctx, int spp_total, double* sum_rgb, uint8_t*
     if (!ctx) return RT_E_INVALID;
     if (ctx->W == 0 || !ctx->accum.p) return fail(ctx, RT_E_STATE, "rt_readback: nothing rendered");
     if (ppm && !ppm_len) return fail(ctx, RT_E_INVALID, "rt_readback: ppm needs ppm_len");
+    if (ctx->peers.n > 0 && !ctx->folded) return fail(ctx, RT_E_STATE, "rt_readback: peers are mapped; every rank must call rt_fold_slices before the fused resolve");
     CK(cudaSetDevice(ctx->device));
     const size_t npix = size_t(ctx->W) * ctx->H;
     CK(ctx->rgb8.resize(npix * 3 + 16));
@@ -629,6 +658,7 @@ extern "C" int rt_readback(rt_ctx* ctx, int spp_total, double* sum_rgb, uint8_t*
 
 // ---------------------------------------------------------------- 8f-2: more output formats --
 static int resolve_views(rt_ctx* ctx, int spp_total, const FrameViews& v) {
+    if (ctx->peers.n > 0 && !ctx->folded) return fail(ctx, RT_E_STATE, "resolve: peers are mapped; every rank must call rt_fold_slices before the fused resolve");
     const size_t npix = size_t(ctx->W) * ctx->H;
     CK(ctx->rgb8.resize(npix * 3 + 16));
     const double scale = spp_total > 0 ? 1.0 / spp_total : 0.0;
@@ -734,15 +764,19 @@ extern "C" int rt_fold_slices(rt_ctx* ctx) {
     return RT_OK;
 }
 
-extern "C" int rt_ipc_export(rt_ctx* ctx, void* handle64) {
-    if (!ctx || !handle64) return RT_E_INVALID;
+// The blob a rank hands to the root: the CUDA IPC handle of its accumulation buffer + what the buffer is
+// (image size, precision), so that the root can refuse a peer that rendered something else.
+struct IpcBlob { cudaIpcMemHandle_t h; int32_t W, H, precision, magic; };
+static_assert(sizeof(cudaIpcMemHandle_t) == 64 && sizeof(IpcBlob) == RT_IPC_HANDLE_BYTES, "ipc blob size");
+
+extern "C" int rt_ipc_export(rt_ctx* ctx, void* handle) {
+    if (!ctx || !handle) return RT_E_INVALID;
     if (!ctx->accum.p) return fail(ctx, RT_E_STATE, "rt_ipc_export: nothing rendered");
-    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "ipc handle size");
     CK(cudaSetDevice(ctx->device));
-    cudaIpcMemHandle_t h;
-    CK(cudaIpcGetMemHandle(&h, ctx->accum.p));
-    // the slice count rides in a trailer the caller exchanges together with the handle
-    std::memcpy(handle64, &h, 64);
+    IpcBlob b;
+    CK(cudaIpcGetMemHandle(&b.h, ctx->accum.p));
+    b.W = ctx->W; b.H = ctx->H; b.precision = ctx->precision; b.magic = 0x52544950;
+    std::memcpy(handle, &b, sizeof b);
     return RT_OK;
 }
 
@@ -754,21 +788,29 @@ extern "C" int rt_ipc_close_peers(rt_ctx* ctx) {
     return RT_OK;
 }
 
-extern "C" int rt_ipc_open_peers(rt_ctx* ctx, const void* handles64, int n_peers) {
-    if (!ctx || (n_peers && !handles64)) return RT_E_INVALID;
+extern "C" int rt_ipc_open_peers(rt_ctx* ctx, const void* handles, int n_peers) {
+    if (!ctx || (n_peers && !handles)) return RT_E_INVALID;
     if (n_peers > RT_MAX_PEERS) return fail(ctx, RT_E_INVALID, "rt_ipc_open_peers: too many peers");
+    if (n_peers && !ctx->accum.p) return fail(ctx, RT_E_STATE, "rt_ipc_open_peers: render once first (the peers must match this context's frame)");
     CK(cudaSetDevice(ctx->device));
     rt_ipc_close_peers(ctx);
     for (int i = 0; i < n_peers; ++i) {
-        cudaIpcMemHandle_t h;
-        std::memcpy(&h, static_cast<const char*>(handles64) + 64 * i, 64);
+        IpcBlob b;
+        std::memcpy(&b, static_cast<const char*>(handles) + sizeof(IpcBlob) * i, sizeof b);
+        if (b.magic != 0x52544950 || b.W != ctx->W || b.H != ctx->H || b.precision != ctx->precision) {
+            rt_ipc_close_peers(ctx);
+            return fail(ctx, RT_E_INVALID, "rt_ipc_open_peers: a peer's buffer is not this context's image size / precision");
+        }
         void* p = nullptr;
-        CK(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        cudaError_t e = cudaIpcOpenMemHandle(&p, b.h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) { rt_ipc_close_peers(ctx); return cuda_fail(ctx, e, "cudaIpcOpenMemHandle"); }
         ctx->peer_mapped[i] = p;
         ctx->peers.ptr[i] = p;
-        ctx->peers.slices[i] = ctx->slices;      // peers render the same image with the same slice count
+        // only layer 0 of a peer is ever read: the resolve refuses to run with peers unless every rank has folded
+        // (rt_fold_slices), so the peers' layer plans do not matter
+        ctx->peers.slices[i] = 1;
+        ctx->peers.n = i + 1;
     }
-    ctx->peers.n = n_peers;
     return RT_OK;
 }
 

@@ -27,7 +27,7 @@ template <typename T> __host__ __device__ __forceinline__ Vec<T> operator*(T t, 
 template <typename T> __host__ __device__ __forceinline__ T dot(Vec<T> a, Vec<T> b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 template <typename T> __host__ __device__ __forceinline__ T len2(Vec<T> a) { return a.x * a.x + a.y * a.y + a.z * a.z; }
 
-__device__ __forceinline__ float  rt_sqrt(float x)  { return sqrtf(x); }   // IEEE: TU built with -prec-sqrt=true
+__device__ __forceinline__ float  rt_sqrt(float x)  { return sqrtf(x); }   // fast mode: the f32 TU is built with -prec-sqrt=false (MUFU + one step, 2 ulp)
 __device__ __forceinline__ double rt_sqrt(double x) { return sqrt(x); }
 __device__ __forceinline__ float  rt_fmin(float a, float b)   { return fminf(a, b); }
 __device__ __forceinline__ double rt_fmin(double a, double b) { return fmin(a, b); }

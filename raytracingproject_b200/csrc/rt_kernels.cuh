@@ -86,7 +86,7 @@ render_mega_kernel(const RenderParams<T> p) {
                 thr = mk<T>(1, 1, 1);
                 depth = p.max_depth;
                 ++s;
-                if (depth <= 0) continue;    // src/camera_cpu.h:12-13
+                if (depth <= 0) { depth = 0; continue; }    // src/camera_cpu.h:12-13: black, also for a negative max_depth
             }
             // one ray_color entry (depth > 0)
             ++my_rays;
@@ -319,17 +319,19 @@ __global__ void gen_rays_kernel(const CameraFrame<T> cam, const int* __restrict_
     store_ray<T>(rays_out, idx, r.o, r.d, r.tm);
 }
 
-// BASELINE config 2 ray generator: even index = get_ray of a virtual 8192x8192
-// image (pixel = idx/2); odd index = incoherent: origin uniform in [-12,12]x[0.05,3]x[-12,12],
-// direction = uniform unit vector, time uniform.  Stream (pixel = idx, sample = 0, stage = 0).
+// BASELINE config 2 ray generator: even index = get_ray of a virtual 8192x8192 image,
+// pixel = idx / 2, its own camera stream (pixel, sample 0, stage 0) -- the ray camera::get_ray would make;
+// odd index = incoherent: origin uniform in [-12,12]x[0.05,3]x[-12,12], direction = uniform unit vector
+// (ball rejection + normalise), time uniform, drawn in that order from the stream (idx / 2, sample 0, stage 1).
 template <typename T>
 __device__ __forceinline__ Ray<T> bench_ray(const CameraFrame<T>& cam, size_t idx, uint64_t seed) {
     Philox rng; rng.init(seed);
-    rng.set(uint32_t(idx), 0u, 0u);
+    const uint32_t pix = uint32_t(idx >> 1);
     if ((idx & 1) == 0) {
-        const uint32_t pix = uint32_t(idx >> 1);
+        rng.set(pix, 0u, 0u);
         return get_ray<T>(cam, int(pix % 8192u), int(pix / 8192u), rng);
     }
+    rng.set(pix, 0u, 1u);
     Ray<T> r;
     const T ux = u01<T>(rng.next24()), uy = u01<T>(rng.next24()), uz = u01<T>(rng.next24());
     r.o = mk<T>(T(-12) + T(24) * ux, T(0.05) + T(2.95) * uy, T(-12) + T(24) * uz);

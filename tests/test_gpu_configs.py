@@ -1,0 +1,267 @@
+"""GPU parity tests for the BASELINE.json configs other than C1 ("claimed but untested"):
+
+  C5  scenes that do NOT fit shared memory (10 k / 101 k / 1 M spheres): the tree is walked in global memory
+      (top levels staged per CTA), GPU LBVH and host SAH builders, wavefront and megakernel -- images, ray
+      counts and closest hits against the CPU oracle with its own BVH (or its linear list where that is cheap)
+  C2  the closest-hit microbenchmark: the in-kernel ray generator pinned against the oracle's get_ray / Philox,
+      primitive ids of >= 2^20 rays against hittable_list::hit (reference src/hittable_list.h:25-39)
+  C3  one FULL-WIDTH parity-mode frame (1920x1080, ~16 k jobs) against the oracle
+  C4  the 80 % glass/metal scene at an spp where north_star's image tolerance applies
+
+Tolerances: BASELINE.json north_star (see test_gpu_parity.py).  Parity mode (RT_F64) is bit-identical.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import psnr8
+
+pytestmark = pytest.mark.gpu
+
+T_REL = 1e-5
+PSNR_MIN = 45.0
+FRAC_MIN = 0.999
+
+
+def frac_within_1(a, b):
+    return float((np.abs(a.astype(int) - b.astype(int)).max(-1) <= 1).mean())
+
+
+def ocam_scaled(O, width, spp, depth, scale):
+    """the oracle's camera of rt_camera_rtiow(scale): src/main.cpp:57-68 moved back by g / 11"""
+    c = O.camera_rtiow(width, spp, depth)
+    c["lookfrom"]["x"], c["lookfrom"]["y"], c["lookfrom"]["z"] = 13 * scale, 2 * scale, 3 * scale
+    c["focus_dist"] = 10.0 * scale
+    return c
+
+
+def incoherent_rays(rt, n, half, seed):
+    rng = np.random.default_rng(seed)
+    rays = np.zeros(n, rt.RAY)
+    rays["orig"] = rng.uniform([-half, 0.05, -half], [half, 3, half], (n, 3))
+    d = rng.normal(size=(n, 3))
+    d[: n // 2, 1] *= 0.05                                  # half of them nearly horizontal: long walks through the grid
+    rays["dir"] = d / np.linalg.norm(d, axis=1, keepdims=True) * rng.uniform(0.1, 10, (n, 1))
+    rays["tm"] = rng.uniform(0, 1, n)
+    return rays
+
+
+_scenes = {}
+
+
+def big_scene(rt, g):
+    if g not in _scenes:
+        _scenes[g] = rt.scene_rtiow(g)
+    return _scenes[g]
+
+
+# ------------------------------------------------------------------------------------ C5 --
+@pytest.mark.parametrize("g,builder", [(50, "lbvh"), (50, "sah"), (159, "lbvh"), (159, "sah")])
+def test_c5_scene_in_global_memory_image_matches_oracle(ctx, rt, O, g, builder):
+    """10 001 / 101 124 spheres: render_pool_kernel<STAGED = false> and the megakernels on a tree that lives in
+    global memory.  Parity mode: image and ray count bit-identical to the oracle (which walks its own BVH);
+    fast mode within north_star's image tolerance of it."""
+    s, m = big_scene(rt, g)
+    assert len(s) in (10001, 101124)
+    ctx.upload_scene(s, m, builder=rt.BVH_LBVH_GPU if builder == "lbvh" else rt.BVH_SAH_HOST)
+    scale = g / 11.0
+    cam = rt.camera_rtiow(96, 2, 50, scale=scale)
+    ref = O.render(s.view(O.SPHERE), m.view(O.MATERIAL), ocam_scaled(O, 96, 2, 50, scale), rng_mode=O.RNG_PHILOX, seed=3, use_bvh=True)
+    for variant in (rt.WAVEFRONT, rt.MEGAKERNEL, rt.MEGA_LOCKSTEP):
+        ctx.render(cam, precision=rt.F64, seed=3, variant=variant)
+        out = ctx.readback(2)
+        st = ctx.stats()
+        assert st["scene_in_smem"] != 1, "a scene of this size cannot be staged whole"
+        assert st["rays"] == ref["rays"], (variant, st["rays"], ref["rays"])
+        assert np.array_equal(out["rgb8"], ref["rgb8"]), variant
+        assert np.allclose(out["sum"], ref["sum"], rtol=1e-13, atol=1e-14)
+    # fast mode at an spp where the tolerance is meaningful (a flipped path at 2 spp is a visible pixel)
+    cam32 = rt.camera_rtiow(128, 24, 50, scale=scale)
+    ref32 = O.render(s.view(O.SPHERE), m.view(O.MATERIAL), ocam_scaled(O, 128, 24, 50, scale), rng_mode=O.RNG_PHILOX, seed=3, use_bvh=True)
+    for variant in (rt.WAVEFRONT, rt.MEGAKERNEL):
+        ctx.render(cam32, precision=rt.F32, seed=3, variant=variant)
+        o32 = ctx.readback(24)
+        assert ctx.stats()["scene_in_smem"] != 1
+        assert abs(ctx.stats()["rays"] - ref32["rays"]) / ref32["rays"] < 5e-3
+        assert psnr8(o32["rgb8"], ref32["rgb8"]) >= PSNR_MIN, (variant, psnr8(o32["rgb8"], ref32["rgb8"]))
+        assert frac_within_1(o32["rgb8"], ref32["rgb8"]) >= 0.995, (variant, frac_within_1(o32["rgb8"], ref32["rgb8"]))
+
+
+@pytest.mark.parametrize("g,builder,oracle_bvh", [(50, "lbvh", False), (50, "sah", False), (159, "lbvh", True), (159, "sah", True), (500, "lbvh", True)])
+def test_c5_closest_hit_matches_oracle(ctx, rt, O, g, builder, oracle_bvh):
+    """>= 30 k incoherent rays against 10 k / 101 k / 1 M spheres: parity-mode hit records byte-equal to the oracle's
+    (linear list at 10 k = reference src/hittable_list.h:25-39; the oracle's BVH above that), float ids / t within
+    north_star's tolerance."""
+    s, m = big_scene(rt, g)
+    ctx.upload_scene(s, m, builder=rt.BVH_LBVH_GPU if builder == "lbvh" else rt.BVH_SAH_HOST)
+    st = ctx.stats()
+    assert st["n_spheres"] == len(s) and st["bvh_depth"] <= 64
+    rays = incoherent_rays(rt, 30000, float(g), seed=g)
+    want = O.closest_hit(s.view(O.SPHERE), rays.view(O.RAY), use_bvh=oracle_bvh)
+    assert (want["prim"] >= 0).mean() > 0.5
+    h64 = ctx.trace_closest(rays, precision=rt.F64)
+    assert h64.tobytes() == want.tobytes()
+    h32 = ctx.trace_closest(rays, precision=rt.F32)
+    assert (h32["prim"] != want["prim"]).mean() < 2e-3
+    same = (h32["prim"] == want["prim"]) & (want["prim"] >= 0)
+    o_mag = np.linalg.norm(rays["orig"], axis=1)[same]
+    d_mag = np.linalg.norm(rays["dir"], axis=1)[same]
+    floor = 4 * 2.0 ** -24 * (o_mag + 1.0) / d_mag            # what narrowing the ray origin to float costs by itself
+    assert np.all(np.abs(h32["t"][same] - want["t"][same]) <= T_REL * want["t"][same] + floor)
+
+
+# ------------------------------------------------------------------------------------ C2 --
+def _philox_stream(O, seed, pixel, sample, stage):
+    """24-bit draws k = 0, 1, 2, ... of the keyed stream, from the oracle's Philox"""
+    key = np.array([seed & 0xffffffff, seed >> 32], "u4")
+    block = 0
+    while True:
+        w = O.philox(np.array([pixel, sample, stage, block], "u4"), key)
+        for x in w:
+            yield int(x) >> 8
+        block += 1
+
+
+def _odd_ray(O, seed, pix):
+    """bench_ray's incoherent ray restated with python floats (IEEE double, same operation order)"""
+    g = _philox_stream(O, seed, pix, 0, 1)
+    u = lambda: next(g) / 16777216.0
+    ux, uy, uz = u(), u(), u()
+    o = (-12 + 24 * ux, 0.05 + 2.95 * uy, -12 + 24 * uz)
+    while True:                                                        # src/vec3.h:129-135, draw order z, y, x
+        az, ay, ax = next(g) - (1 << 23), next(g) - (1 << 23), next(g) - (1 << 23)
+        if ax * ax + ay * ay + az * az < (1 << 46):
+            break
+    v = (ax / 8388608.0, ay / 8388608.0, az / 8388608.0)
+    inv = 1.0 / np.sqrt(np.float64(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]))      # unit_vector: (1 / length) * v, src/vec3.h:117-119
+    return o, (inv * v[0], inv * v[1], inv * v[2]), u()
+
+
+def test_c2_generator_and_primitive_ids_match_the_oracle(ctx_scene, rt, O, scene):
+    """BASELINE config 2: 2^20 of the synthetic rays bench_closest_kernel generates in-kernel are
+    dumped and (a) compared with what the oracle generates for the same streams -- camera::get_ray of a virtual
+    8192x8192 image for even indices, the restated incoherent generator for odd ones --, (b) re-traced by
+    hittable_list::hit (the linear list, reference src/hittable_list.h:25-39): primitive ids bit-exact in parity
+    mode, fast mode within north_star (ids equal but for grazing rays, t within 1e-5)."""
+    s, _ = scene
+    n = 1 << 20
+    cam = rt.camera_rtiow(400, 10, 50)
+    r64 = ctx_scene.bench_closest(cam, n, seed=1, precision=rt.F64, want_results=True, dump_rays=n)
+    rays = r64["rays"]
+    # (a) the generator
+    ocam = O.camera_rtiow(8192, 1, 50)
+    ocam["aspect_ratio"] = 1.0
+    idx = np.concatenate([np.arange(0, 4096, 2), np.arange(n - 4096, n, 2), np.arange(0, n, 2)[:: 257]])
+    pix = idx >> 1
+    want_even, _ = O.get_rays(ocam, pix % 8192, pix // 8192, np.zeros(len(pix), "u4"), seed=1)
+    assert rays[idx].tobytes() == want_even.tobytes()
+    for i in list(range(1, 400, 2)) + [n - 1, n - 3, 777777]:
+        o, d, tm = _odd_ray(O, 1, i >> 1)
+        assert tuple(rays["orig"][i]) == o and tuple(rays["dir"][i]) == d and rays["tm"][i] == tm, i
+    # (b) the ids
+    want = O.closest_hit(s, rays.view(O.RAY))
+    assert np.array_equal(r64["prim"], want["prim"])
+    assert np.array_equal(r64["t"][want["prim"] >= 0], want["t"][want["prim"] >= 0].astype("f4"))
+    assert 0.3 < (want["prim"] >= 0).mean() < 0.99
+    brute = ctx_scene.bench_closest(cam, n, seed=1, precision=rt.F64, backend=rt.TRACE_BRUTE, want_results=True)
+    assert np.array_equal(brute["prim"], want["prim"])
+    r32 = ctx_scene.bench_closest(cam, n, seed=1, precision=rt.F32, want_results=True)
+    assert (r32["prim"] != want["prim"]).mean() < 1e-4, int((r32["prim"] != want["prim"]).sum())
+    same = (r32["prim"] == want["prim"]) & (want["prim"] >= 0)
+    floor = 4 * 2.0 ** -24 * (np.linalg.norm(rays["orig"], axis=1)[same] + 1.0) / np.linalg.norm(rays["dir"], axis=1)[same]
+    assert np.all(np.abs(r32["t"][same] - want["t"][same]) <= T_REL * want["t"][same] + floor + 1e-7 * want["t"][same])
+
+
+# ------------------------------------------------------------------------------------ C3 --
+def test_c3_full_width_parity_frame_is_the_oracles(ctx_scene, rt, O, scene):
+    """One full-width frame of BASELINE config 3 (1920x1080: 120 x 135 tiles, the job ring, every layer path of the
+    default kernel) in parity mode at 2 spp against the oracle -- not against the GPU's other precision."""
+    s, m = scene
+    cam = rt.camera_rtiow(1920, 2, 50)
+    ref = O.render(s, m, O.camera_rtiow(1920, 2, 50), rng_mode=O.RNG_PHILOX, seed=0, use_bvh=True, nthreads=os.cpu_count())
+    for variant, slices in ((rt.WAVEFRONT, 0), (rt.WAVEFRONT, 2), (rt.MEGAKERNEL, 0)):
+        ctx_scene.render(cam, precision=rt.F64, seed=0, variant=variant, slices=slices)
+        out = ctx_scene.readback(2, want_ppm=True)
+        assert ctx_scene.stats()["rays"] == ref["rays"]
+        if slices <= 1:
+            assert np.array_equal(out["rgb8"], ref["rgb8"])
+            assert out["ppm"] == O.ppm_p3(ref["rgb8"])
+        else:                                    # two layers re-associate the per-pixel sum: the last bit may move a byte boundary
+            d = np.abs(out["rgb8"].astype(int) - ref["rgb8"].astype(int))
+            assert d.max() <= 1 and (d > 0).mean() < 1e-4
+
+
+# ------------------------------------------------------------------------------------ C4 --
+def test_c4_glass_metal_scene_within_north_star_tolerance(ctx, rt, O):
+    """BASELINE config 4's scene (80 % glass / metal) at 64 spp on a small image: the fast mode is within north_star's
+    image tolerance (PSNR >= 45 dB, >= 99.9 % of pixels within 1/255) of the oracle; parity mode is the oracle's image."""
+    s, m = rt.scene_rtiow(11, 0.2, 0.6, 5489)
+    assert (m["type"] != rt.LAMBERTIAN).mean() > 0.7
+    ctx.upload_scene(s, m)
+    cam = rt.camera_rtiow(160, 64, 50)
+    ref = O.render(s.view(O.SPHERE), m.view(O.MATERIAL), O.camera_rtiow(160, 64, 50), rng_mode=O.RNG_PHILOX, seed=4, use_bvh=True)
+    assert ref["rays"] / (160 * 90 * 64) > 2.7            # more bounces than the final scene (2.58)
+    for variant in (rt.WAVEFRONT, rt.MEGAKERNEL):
+        ctx.render(cam, precision=rt.F64, seed=4, variant=variant)
+        out = ctx.readback(64)
+        assert ctx.stats()["rays"] == ref["rays"] and np.array_equal(out["rgb8"], ref["rgb8"])
+        ctx.render(cam, precision=rt.F32, seed=4, variant=variant)
+        o32 = ctx.readback(64)
+        assert psnr8(o32["rgb8"], ref["rgb8"]) >= PSNR_MIN, psnr8(o32["rgb8"], ref["rgb8"])
+        assert frac_within_1(o32["rgb8"], ref["rgb8"]) >= FRAC_MIN, frac_within_1(o32["rgb8"], ref["rgb8"])
+
+
+# ------------------------------------------------------------------------- hardened paths --
+def test_more_big_spheres_than_the_out_of_tree_list_holds(ctx, rt, O):
+    """more than 16 spheres of radius >= big_radius: the 16 largest stay out of the tree, the others go into it
+    (reported in rt_stats.big_in_tree); hits and image are the oracle's either way"""
+    s, m = rt.scene_rtiow()
+    n = 24
+    sb = np.zeros(n, rt.SPHERE); mb = np.zeros(n, rt.MATERIAL)
+    rng = np.random.default_rng(11)
+    sb["center1"] = rng.uniform([-30, -160, -30], [30, -140, 30], (n, 3))
+    sb["radius"] = 100.0 + np.arange(n)
+    sb["material"] = len(m) + np.arange(n)
+    mb["type"] = rt.LAMBERTIAN; mb["albedo"] = rng.uniform(0.2, 0.9, (n, 3))
+    s2 = np.concatenate([s, sb]); m2 = np.concatenate([m, mb])
+    ctx.upload_scene(s2, m2)
+    st = ctx.stats()
+    assert st["n_big"] == 16 and st["big_in_tree"] == n + 1 - 16
+    cam = rt.camera_rtiow(96, 3, 20)
+    ref = O.render(s2.view(O.SPHERE), m2.view(O.MATERIAL), O.camera_rtiow(96, 3, 20), rng_mode=O.RNG_PHILOX, seed=2, use_bvh=True)
+    for variant in (rt.WAVEFRONT, rt.MEGAKERNEL):
+        ctx.render(cam, precision=rt.F64, seed=2, variant=variant)
+        assert np.array_equal(ctx.readback(3)["rgb8"], ref["rgb8"]) and ctx.stats()["rays"] == ref["rays"]
+    rays = incoherent_rays(rt, 5000, 12.0, seed=3)
+    assert ctx.trace_closest(rays, precision=rt.F64).tobytes() == O.closest_hit(s2.view(O.SPHERE), rays.view(O.RAY)).tobytes()
+    ctx.render(cam, precision=rt.F32, seed=2)
+    assert frac_within_1(ctx.readback(3)["rgb8"], ref["rgb8"]) > 0.99
+
+
+@pytest.mark.parametrize("depth", [0, -1, -50])
+def test_non_positive_max_depth_is_black_in_every_variant(ctx_scene, rt, O, scene, depth):
+    """ray_color returns black for depth <= 0 (reference src/camera_cpu.h:12-13): no ray is traced"""
+    s, m = scene
+    cam = rt.camera_rtiow(48, 2, depth)
+    ref = O.render(s, m, O.camera_rtiow(48, 2, depth), rng_mode=O.RNG_PHILOX, seed=3)
+    assert ref["rays"] == 0 and not ref["rgb8"].any()
+    for variant in (rt.WAVEFRONT, rt.MEGAKERNEL, rt.MEGA_LOCKSTEP):
+        for prec in (rt.F64, rt.F32):
+            ctx_scene.render(cam, precision=prec, seed=3, variant=variant)
+            out = ctx_scene.readback(2)
+            assert ctx_scene.stats()["rays"] == 0 and not out["rgb8"].any(), (variant, prec)
+
+
+def test_failed_upload_leaves_no_scene(ctx, rt):
+    """an upload that fails must not leave the previous scene's counts paired with new buffers"""
+    s, m = rt.scene_rtiow()
+    ctx.upload_scene(s, m)
+    bad = s.copy(); bad["material"][7] = len(m) + 5
+    with pytest.raises(rt.RtError):
+        ctx.upload_scene(bad, m)
+    with pytest.raises(rt.RtError, match="no scene"):
+        ctx.render(rt.camera_rtiow(32, 1, 5))
+    ctx.upload_scene(s, m)
+    ctx.render(rt.camera_rtiow(32, 1, 5))
+    ctx.synchronize()
