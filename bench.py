@@ -224,7 +224,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--precision", default="f32", choices=["f32", "f64"])
-    ap.add_argument("--combine", default="nccl", choices=["nccl", "ipc"])
+    ap.add_argument("--combine", default="nccl", choices=["nccl", "ipc"], help="--shard samples: how the partial buffers are combined")
+    ap.add_argument("--shard", default="tiles", choices=["tiles", "samples"],
+                    help="N > 1: tile-interleaved shards (every rank writes its tiles' bytes into rank 0's image over NVLink) or "
+                         "sample-range shards (fold + reduce of float partial buffers)")
     ap.add_argument("--variant", default="wavefront", choices=["wavefront", "megakernel", "lockstep"])
     ap.add_argument("--config", default="c3", choices=sorted(CONFIGS) + ["c2"], help="BASELINE.json config (default c3 = the headline one)")
     ap.add_argument("--spp", type=int, default=0, help="override spp (a non-default value is NOT the named config)")
@@ -279,10 +282,16 @@ def main():
         torch.cuda.synchronize()
 
     # warm-up render so buffers exist, then set up the combine
-    sharding.render_sharded(ctx, cam, rank, world, prec, variant=variant)
+    tiles = world > 1 and args.shard == "tiles" and args.variant == "wavefront"
+    if tiles:
+        ctx.render(cam, precision=prec, seed=0, tile_rank=rank, tile_world=world)
+        ctx.synchronize()
+        sharding.setup_tile_frame(ctx, rank, world)
+    else:
+        sharding.render_sharded(ctx, cam, rank, world, prec, variant=variant)
     ctx.synchronize()
-    acc = sharding.alias_accum_tensor(ctx, layers=1) if world > 1 else None      # layer 0: the rank's partial sum after fold_slices
-    if world > 1 and args.combine == "ipc":
+    acc = sharding.alias_accum_tensor(ctx, layers=1) if world > 1 and not tiles else None      # layer 0: the rank's partial sum after fold_slices
+    if world > 1 and not tiles and args.combine == "ipc":
         handles = sharding.exchange_ipc_handles(ctx.ipc_export())
         if rank == 0:
             ctx.ipc_open_peers([h for r, h in enumerate(handles) if r != 0])
@@ -295,8 +304,13 @@ def main():
         """one frame; returns nothing, everything is enqueued on ctx's stream"""
         if e2e:
             ctx.upload_scene(s, m, builder=builder_id)               # H2D: the world, every step (BVH build included)
-        sharding.render_sharded(ctx, cam, rank, world, prec, variant=variant)
-        if world > 1:
+        if tiles:
+            # every rank renders all samples of its tiles; ranks != 0 resolve them into rank 0's image over NVLink and signal;
+            # rank 0's readback below waits for the signals on its stream.  No host synchronisation inside the step.
+            sharding.render_tiles(ctx, cam, rank, world, prec)
+        else:
+            sharding.render_sharded(ctx, cam, rank, world, prec, variant=variant)
+        if world > 1 and not tiles:
             ctx.fold_slices()                                        # one [H][W] layer per rank crosses NVLink, not `slices` of them
             if args.combine == "nccl":
                 with torch.cuda.stream(stream):
@@ -349,7 +363,7 @@ def main():
     multi_check = None
     if world > 1 and not args.no_check:
         combined = pin_rgb8.reshape(H, W, 3).copy() if rank == 0 else None
-        if args.combine == "ipc" and rank == 0:
+        if args.combine == "ipc" and rank == 0 and not tiles:
             ctx.ipc_close_peers()
         barrier()
         if rank == 0:
@@ -359,7 +373,8 @@ def main():
             mse = float(np.mean((combined.astype(float) - solo.astype(float)) ** 2))
             multi_check = {"combined_vs_single_gpu_max_byte_diff": int(d.max()),
                            "combined_vs_single_gpu_psnr_db": 99.0 if mse == 0 else float(10 * np.log10(255.0 ** 2 / mse)),
-                           "frac_pixels_identical": float((d == 0).mean()), "ranks": world, "combine": args.combine}
+                           "frac_pixels_identical": float((d == 0).mean()), "ranks": world,
+                           "combine": "tiles over NVLink" if tiles else args.combine}
         barrier()
 
     # untimed: the fast mode against parity mode on this very frame (north_star image tolerance)
@@ -395,7 +410,9 @@ def main():
                        "bvh": ("host SAH" if builder == "sah" else "GPU Morton LBVH") + f", depth {st_scene['bvh_depth']}, " +
                               ("whole scene staged in shared memory" if st_scene["scene_in_smem"] else "nodes and spheres in global memory (L2 / HBM)"),
                        "seed": 0,
-                       "parallelism": f"sample-range sharding x{world}, combine={args.combine if world > 1 else 'none'}",
+                       "parallelism": (f"tile-interleaved sharding x{world} (pairs of 16x8 tiles), every rank's resolve kernel writes its tiles' "
+                                       f"bytes into rank 0's image over NVLink" if tiles else
+                                       f"sample-range sharding x{world}, combine={args.combine if world > 1 else 'none'}"),
                        "l2": f"256 MB buffer written between timed iterations (L2 flushed); scene inputs are {(s.nbytes + m.nbytes) / 1e3:.0f} KB"},
             "mrays_per_s": rays / ms / 1e3, "rays_per_sample": rays / samples,
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak,

@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define RT_ABI_VERSION 1u
+#define RT_ABI_VERSION 2u
 
 enum {
     RT_OK = 0,
@@ -114,6 +114,10 @@ typedef struct {
     uint64_t seed;           /* Philox key; stream = (pixel, sample, stage), see DESIGN.md */
     int32_t  slices;         /* sample slices per pixel rendered by different warps (0 = auto) */
     int32_t  sched;          /* tuning: th_s | th_l << 8 | shape+1 << 16 | th_n << 20 of the warp scheduler, bulk jobs per warp << 24 (0 = defaults) */
+    int32_t  tile_rank;      /* tile-interleaved sharding: with tile_world > 1 this call renders ALL its samples, but only of the */
+    int32_t  tile_world;     /* tile pairs whose index is tile_rank modulo tile_world (RT_WAVEFRONT only; 0 or 1 = the whole image) */
+    int32_t  top_cap;        /* tuning: cap on the tree nodes staged in shared memory for a scene in global memory (0 = all that fits, -1 = none) */
+    int32_t  pad;
 } rt_render_opts;
 
 typedef struct {
@@ -128,6 +132,8 @@ typedef struct {
     int32_t  slices, kernel_launches;   /* launches of this library's kernels in the last render+resolve */
     int32_t  scene_in_smem;  /* last render: 1 = whole scene staged in shared memory, 2 = top levels of the tree only, 0 = global */
     int32_t  big_in_tree;    /* spheres with radius >= big_radius beyond the 16 largest: they are in the tree like any sphere */
+    int32_t  top_nodes_in_smem;   /* last render, scene_in_smem == 2: how many nodes of the tree's first levels were staged */
+    int32_t  pad;
 } rt_stats;
 
 typedef struct rt_ctx rt_ctx;
@@ -213,6 +219,20 @@ int rt_stream(rt_ctx *ctx, void **cuda_stream);
 int rt_ipc_export(rt_ctx *ctx, void *handle);
 int rt_ipc_open_peers(rt_ctx *ctx, const void *handles, int n_peers);   /* peers other than self */
 int rt_ipc_close_peers(rt_ctx *ctx);
+
+/* Tile-interleaved sharding (rt_render_opts.tile_rank / tile_world): every rank renders ALL samples of its share of
+ * the tiles, so the combine has no arithmetic -- each rank's resolve kernel writes the write_color bytes of its tiles
+ * straight into the ROOT's image over NVLink (CUDA IPC mapping) and bumps a counter there; the root's rt_readback
+ * resolves its own tiles, waits on its stream for the counter (every peer delivered), then encodes / copies.
+ *   root:  rt_render(tile_rank = r0, tile_world = N) once, rt_frame_export -> blob to every peer; per frame
+ *          rt_render(...), rt_readback(...)
+ *   peer:  rt_frame_open(blob); per frame rt_render(tile_rank = r, tile_world = N), rt_resolve_tiles(spp_total)
+ * A peer must not start frame k + 1 before the root's rt_readback of frame k has returned (one barrier per frame).
+ * The per-pixel sums (sum_rgb, PFM) of the root cover its own tiles only. */
+int rt_frame_export(rt_ctx *ctx, void *handle);            /* RT_IPC_HANDLE_BYTES; re-export after the image size changes */
+int rt_frame_open(rt_ctx *ctx, const void *handle);
+int rt_frame_close(rt_ctx *ctx);
+int rt_resolve_tiles(rt_ctx *ctx, int spp_total);          /* asynchronous on the context's stream */
 
 /* ---- parity / microbenchmark hooks (same code the render path runs) ------------------------- */
 

@@ -8,7 +8,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(HERE, "librt_b200.so")   # RT_B200_LIB: an A/B or STATS build of the same library
 
-ABI = 1
+ABI = 2
 F32, F64 = 0, 1
 MEGAKERNEL, WAVEFRONT, MEGA_LOCKSTEP = 0, 1, 2
 TRACE_BVH, TRACE_BRUTE = 0, 1
@@ -42,7 +42,8 @@ class BvhOpts(C.Structure):
 class RenderOpts(C.Structure):
     _fields_ = [("abi", C.c_uint32), ("precision", C.c_int32), ("variant", C.c_int32),
                 ("sample_begin", C.c_int32), ("sample_count", C.c_int32), ("accumulate", C.c_int32),
-                ("seed", C.c_uint64), ("slices", C.c_int32), ("sched", C.c_int32)]
+                ("seed", C.c_uint64), ("slices", C.c_int32), ("sched", C.c_int32),
+                ("tile_rank", C.c_int32), ("tile_world", C.c_int32), ("top_cap", C.c_int32), ("pad", C.c_int32)]
 
 
 class Stats(C.Structure):
@@ -51,7 +52,8 @@ class Stats(C.Structure):
                 ("n_spheres", C.c_int32), ("n_big", C.c_int32), ("n_nodes", C.c_int32), ("bvh_depth", C.c_int32),
                 ("image_width", C.c_int32), ("image_height", C.c_int32),
                 ("slices", C.c_int32), ("kernel_launches", C.c_int32),
-                ("scene_in_smem", C.c_int32), ("big_in_tree", C.c_int32)]
+                ("scene_in_smem", C.c_int32), ("big_in_tree", C.c_int32),
+                ("top_nodes_in_smem", C.c_int32), ("pad", C.c_int32)]
 
 
 # every symbol include/rt_b200.h declares: name -> (restype, argtypes)
@@ -77,6 +79,10 @@ SYMBOLS = {
     "rt_ipc_export": (_I, [_VP, _VP]),
     "rt_ipc_open_peers": (_I, [_VP, _VP, _I]),
     "rt_ipc_close_peers": (_I, [_VP]),
+    "rt_frame_export": (_I, [_VP, _VP]),
+    "rt_frame_open": (_I, [_VP, _VP]),
+    "rt_frame_close": (_I, [_VP]),
+    "rt_resolve_tiles": (_I, [_VP, _I]),
     "rt_trace_closest": (_I, [_VP, _VP, _SZ, _D, _D, _I, _I, _VP]),
     "rt_scatter": (_I, [_VP, _VP, _VP, _VP, _SZ, _U64, _I, _VP, _VP, _VP]),
     "rt_gen_rays": (_I, [_VP, _VP, _VP, _VP, _VP, _SZ, _U64, _I, _VP]),

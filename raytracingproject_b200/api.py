@@ -123,8 +123,9 @@ class Context:
         self._ck(self._lib.rt_upload_scene(self._h, L.ptr(spheres), len(spheres), L.ptr(materials), len(materials), C.byref(o)))
 
     def render(self, cam, precision=L.F32, seed=0, variant=L.WAVEFRONT, sample_begin=0, sample_count=0,
-               accumulate=False, slices=0, sched=0):
-        o = L.RenderOpts(L.ABI, precision, variant, sample_begin, sample_count, int(accumulate), seed, slices, sched)
+               accumulate=False, slices=0, sched=0, tile_rank=0, tile_world=0, top_cap=0):
+        o = L.RenderOpts(L.ABI, precision, variant, sample_begin, sample_count, int(accumulate), seed, slices, sched,
+                         tile_rank, tile_world, top_cap, 0)
         self._ck(self._lib.rt_render(self._h, C.byref(cam), C.byref(o)))
         w, h = C.c_int(), C.c_int()
         self._lib.rt_image_size(C.byref(cam), C.byref(w), C.byref(h))
@@ -213,6 +214,21 @@ class Context:
 
     def ipc_close_peers(self):
         self._ck(self._lib.rt_ipc_close_peers(self._h))
+
+    # ---- tile-sharded frames: bytes written into the root's image over NVLink (rt_b200.h) ----
+    def frame_export(self):
+        buf = (C.c_ubyte * L.IPC_HANDLE_BYTES)()
+        self._ck(self._lib.rt_frame_export(self._h, buf))
+        return bytes(buf)
+
+    def frame_open(self, handle):
+        self._ck(self._lib.rt_frame_open(self._h, handle))
+
+    def frame_close(self):
+        self._ck(self._lib.rt_frame_close(self._h))
+
+    def resolve_tiles(self, spp_total=0):
+        self._ck(self._lib.rt_resolve_tiles(self._h, spp_total))
 
     # ---- parity hooks ----
     def trace_closest(self, rays, tmin=0.001, tmax=np.inf, precision=L.F64, backend=L.TRACE_BVH):

@@ -66,6 +66,7 @@ struct rt_ctx {
     int n_spheres = 0, n_slots = 0, n_big = 0, n_nodes = 0, root_ref = RT_SENTINEL, depth = 0;
     DevBuf<float4> nodes, nodes4, sa32, sb32, sc32;   // nodes4: 4-wide records of the same tree (null unless the tree is walked in global memory)
     bool wide = false, wide_forced = false;
+    int top_ordered = 0;                          // nodes [0, top_ordered) are the first levels of the tree in breadth-first order (rt_scene.cu)
     DevBuf<double4> sa64, sb64, sc64, big_a, big_b, big_c;
     DevBuf<int> meta, big_meta;
     double build_ms = 0, upload_ms = 0;
@@ -93,6 +94,14 @@ struct rt_ctx {
     PeerList peers = {};
     void* peer_mapped[RT_MAX_PEERS] = {};
 
+    // tile-interleaved sharding: the last render's share of the tiles, and the image hand-over
+    TileOwner tiles = { 0, 0, 0, 0, 0, 0, 0 };
+    bool frame_exported = false, tiles_pending = false;   // root: its image is mapped by peers; a tile-sharded render awaits their bytes
+    unsigned frame_target = 0;                            // root: counter value once every peer has delivered the frame in flight
+    void* frame_remote = nullptr;                         // peer: the root's image (rgb8 + counter), mapped through CUDA IPC
+    int frame_remote_W = 0, frame_remote_H = 0;
+    DevBuf<int> frame_timeout;                            // root: set by the wait kernel when the peers' tiles did not arrive
+
     rt_stats stats = {};
 };
 
@@ -104,6 +113,9 @@ int cuda_fail(rt_ctx* c, cudaError_t e, const char* what) {
 }
 // layers the resolve pass has to read: all of them, or layer 0 alone after rt_fold_slices (every rank folds)
 int live_slices(const rt_ctx* c) { return c->folded ? 1 : c->slices; }
+// the image buffer: rgb8 [npix * 3, padded for the encoder's 32-bit loads], then the hand-over counter of tile-sharded frames
+size_t frame_counter_offset(size_t npix) { return (npix * 3 + 16 + 127) & ~size_t(127); }
+cudaError_t ensure_rgb8(rt_ctx* c, size_t npix) { return c->rgb8.resize(frame_counter_offset(npix) + 128); }
 PeerList live_peers(const rt_ctx* c) {
     PeerList p = c->peers;
     if (c->folded) for (int i = 0; i < p.n; ++i) p.slices[i] = 1;
@@ -179,6 +191,7 @@ template <typename T> SceneView<T> scene_view(const rt_ctx* c) {
     sv.meta = c->meta.p;
     sv.big_a = c->big_a.p; sv.big_b = c->big_b.p; sv.big_c = c->big_c.p; sv.big_meta = c->big_meta.p;
     sv.n_slots = c->n_slots; sv.n_nodes = c->n_nodes; sv.n_big = c->n_big; sv.root_ref = c->root_ref;
+    sv.n_top = 0;
     const int q = int(sizeof(typename Quad<T>::type));
     sv.off_sa = c->n_nodes * 64; sv.off_sb = sv.off_sa + c->n_slots * q; sv.off_sc = sv.off_sb + c->n_slots * q;
     sv.off_meta = sv.off_sc + c->n_slots * q;
@@ -226,6 +239,8 @@ int rt_create(rt_ctx** out, int device) {
     ctx->smem_per_sm = prop.sharedMemPerMultiprocessor;
     for (auto& ev : ctx->ev) cudaEventCreate(&ev);
     ctx->job_counter.resize(1);
+    ctx->frame_timeout.resize(1);
+    cudaMemset(ctx->frame_timeout.p, 0, sizeof(int));
     ctx->ray_counter.resize(32);      // [0] rays; [1..] scheduler counters of a -DRT_POOL_STATS build
     *out = ctx;
     return RT_OK;
@@ -236,6 +251,7 @@ int rt_destroy(rt_ctx* ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     rt_ipc_close_peers(ctx);
+    rt_frame_close(ctx);
     ctx->nodes.release(); ctx->nodes4.release(); ctx->sa32.release(); ctx->sb32.release(); ctx->sc32.release();
     ctx->sa64.release(); ctx->sb64.release(); ctx->sc64.release();
     ctx->big_a.release(); ctx->big_b.release(); ctx->big_c.release(); ctx->meta.release(); ctx->big_meta.release();
@@ -411,6 +427,18 @@ extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_s
             CK(cudaStreamSynchronize(ctx->stream));
         }
     }
+    // top of the tree first: nodes 0 .. k-1 = the first levels in breadth-first order, so that a render whose scene stays in
+    // global memory can keep them in shared memory (north_star item 2).  Parity is defined on hits, not on node numbers.
+    ctx->top_ordered = 0;
+    if (ctx->n_nodes > 1 && ctx->root_ref >= 0) {
+        DevBuf<int> newpos, top_ids; DevBuf<float4> permuted;
+        CK(newpos.resize(ctx->n_nodes)); CK(top_ids.resize(RT_TOP_MAX)); CK(permuted.resize(size_t(ctx->n_nodes) * 4));
+        CK(launch_top_first(ctx->nodes.p, ctx->n_nodes, ctx->root_ref, RT_TOP_MAX, newpos.p, top_ids.p, permuted.p, ctx->stream));
+        CK(cudaMemcpyAsync(ctx->nodes.p, permuted.p, size_t(ctx->n_nodes) * 64, cudaMemcpyDeviceToDevice, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        ctx->root_ref = 0;
+        ctx->top_ordered = std::min(ctx->n_nodes, RT_TOP_MAX);
+    }
     // 4-wide records (8f-4) for trees walked in global memory: opt-in (opts->wide = 1; the wavefront kernel then leaves
     // the scene in global memory whatever its size).  Measured on C5 (10 k / 100 k / 1 M spheres): 2 % SLOWER than the
     // binary records (profiles/r1_wide_nodes_ab.txt), so nothing turns them on by default.
@@ -508,6 +536,7 @@ int render_impl(rt_ctx* ctx, const rt_camera& cam, const rt_render_opts& o, int 
     p.job_group = 2;          // pairs: +0.3-1.5 % over single jobs; 3 and more lose to the tail (profiles/r1_job_group_sweep.txt)
     p.tiles_x = (ctx->W + 7) / 8; p.tiles_y = (ctx->H + 3) / 4;
     p.accumulate = o.accumulate;
+    p.tile_rank = 0; p.tile_world = 1;
     size_t smem = 0;
     bool staged = can_stage<T>(ctx, &smem);
     int pshape = 0;
@@ -515,8 +544,23 @@ int render_impl(rt_ctx* ctx, const rt_camera& cam, const rt_render_opts& o, int 
         pshape = pool_shape_for<T>(ctx, o.sched, &staged);
         int P, B; pool_shape(pshape, &P, &B);
         p.tiles_x = (ctx->W + 15) / 16; p.tiles_y = (ctx->H + P / 16 - 1) / (P / 16);
+        if (o.tile_world > 1) { p.tile_rank = o.tile_rank; p.tile_world = o.tile_world; }
+        ctx->tiles = TileOwner{ p.tile_world, p.tile_rank, p.tiles_x, 16, P / 16, p.job_group, ctx->W };
+        ctx->tiles_pending = p.tile_world > 1;
+    } else {
+        ctx->tiles = TileOwner{ 0, 0, 0, 0, 0, 0, 0 };
     }
-    ctx->stats.scene_in_smem = staged;
+    if (o.variant == RT_WAVEFRONT && !staged && !ctx->wide && ctx->top_ordered > 0) {
+        // the shared memory the pools leave free holds the top of the tree (rt_render_opts.top_cap: tuning knob)
+        int P, B; pool_shape(pshape, &P, &B);
+        const size_t pools = size_t(B / 32) * pool_warp_bytes<T>(P);
+        const size_t spare = ctx->smem_optin > pools ? ctx->smem_optin - pools : 0;
+        int n_top = int(std::min<size_t>(size_t(ctx->top_ordered), spare / 64));
+        if (o.top_cap < 0) n_top = 0; else if (o.top_cap > 0) n_top = std::min(n_top, o.top_cap);
+        p.scene.n_top = n_top;
+    }
+    ctx->stats.scene_in_smem = staged ? 1 : (p.scene.n_top > 0 ? 2 : 0);
+    ctx->stats.top_nodes_in_smem = p.scene.n_top;
     CK(cudaMemsetAsync(ctx->job_counter.p, 0, sizeof(unsigned int), ctx->stream));
     CK(cudaMemsetAsync(ctx->ray_counter.p, 0, 32 * sizeof(unsigned long long), ctx->stream));
     CK(cudaEventRecord(ctx->ev[0], ctx->stream));
@@ -540,12 +584,14 @@ extern "C" int rt_render(rt_ctx* ctx, const rt_camera* cam, const rt_render_opts
     if (cam->image_width < 1 || !(cam->aspect_ratio > 0)) return fail(ctx, RT_E_INVALID, "rt_render: bad image size");
     if (opts->precision != RT_F32 && opts->precision != RT_F64) return fail(ctx, RT_E_INVALID, "rt_render: bad precision");
     if (opts->variant != RT_MEGAKERNEL && opts->variant != RT_MEGA_LOCKSTEP && opts->variant != RT_WAVEFRONT) return fail(ctx, RT_E_INVALID, "rt_render: variant not built");
+    if (opts->tile_world > 1 && (opts->tile_rank < 0 || opts->tile_rank >= opts->tile_world)) return fail(ctx, RT_E_INVALID, "rt_render: tile_rank out of range");
     // the wavefront pool keeps a path's sample index in 14 bits and its remaining depth in 16: beyond that the
     // warp-scheduled megakernel (same arithmetic, same image) takes the call
     rt_render_opts eff = *opts;
     // (and a job's tile origin in 15 + 16 bits)
     if (eff.variant == RT_WAVEFRONT && (cam->max_depth > 65535 || cam->image_width > 32000 || image_height_of(*cam) > 32000 ||
         (eff.sample_count > 0 ? eff.sample_count : cam->samples_per_pixel) > 16383)) { eff.variant = RT_MEGAKERNEL; eff.sched = 0; }
+    if (eff.tile_world > 1 && eff.variant != RT_WAVEFRONT) return fail(ctx, RT_E_INVALID, "rt_render: tile-interleaved sharding needs the wavefront variant (and its 16-bit sample / depth limits)");
     opts = &eff;
     CK(cudaSetDevice(ctx->device));
     const int W = cam->image_width, H = image_height_of(*cam);
@@ -574,7 +620,8 @@ extern "C" int rt_render(rt_ctx* ctx, const rt_camera* cam, const rt_render_opts
     if (slices <= 0 && opts->precision == RT_F64) slices = 1;
     int sizes[RT_MAX_SLICES], n_sized = -1, n_bulk = 0;
     if (slices <= 0 && opts->variant == RT_WAVEFRONT && sample_count > 0) {
-        slices = n_sized = plan_layers(sample_count, tiles, resident_warps, (opts->sched >> 24) & 0xff, sizes, &n_bulk);
+        const long long my_tiles = opts->tile_world > 1 ? (tiles + opts->tile_world - 1) / opts->tile_world : tiles;
+        slices = n_sized = plan_layers(sample_count, my_tiles, resident_warps, (opts->sched >> 24) & 0xff, sizes, &n_bulk);
     }
     if (slices <= 0) slices = int(std::min<long long>(64, (16 * resident_warps + tiles - 1) / tiles));
     slices = std::max(1, std::min(std::min(slices, RT_MAX_SLICES), std::max(1, sample_count)));
@@ -617,17 +664,27 @@ extern "C" int rt_readback(rt_ctx* ctx, int spp_total, double* sum_rgb, uint8_t*
     if (ctx->peers.n > 0 && !ctx->folded) return fail(ctx, RT_E_STATE, "rt_readback: peers are mapped; every rank must call rt_fold_slices before the fused resolve");
     CK(cudaSetDevice(ctx->device));
     const size_t npix = size_t(ctx->W) * ctx->H;
-    CK(ctx->rgb8.resize(npix * 3 + 16));
+    CK(ensure_rgb8(ctx, npix));
     if (sum_rgb) CK(ctx->sum.resize(npix * 3));
     const double scale = spp_total > 0 ? 1.0 / spp_total : 0.0;                 // src/color.h:20
     CK(cudaEventRecord(ctx->ev[2], ctx->stream));
     int launches = 1;
+    const FrameViews no_views{nullptr, nullptr, 0, 0};
     if (ctx->precision == RT_F32)
         CK(launch_resolve<float4>(reinterpret_cast<const float4*>(ctx->accum.p), live_slices(ctx), live_peers(ctx), npix, scale,
-                                  sum_rgb ? ctx->sum.p : nullptr, ctx->rgb8.p, nullptr, ctx->stream));
+                                  sum_rgb ? ctx->sum.p : nullptr, ctx->rgb8.p, nullptr, ctx->stream, no_views, ctx->tiles));
     else
         CK(launch_resolve<double4>(reinterpret_cast<const double4*>(ctx->accum.p), live_slices(ctx), live_peers(ctx), npix, scale,
-                                   sum_rgb ? ctx->sum.p : nullptr, ctx->rgb8.p, nullptr, ctx->stream));
+                                   sum_rgb ? ctx->sum.p : nullptr, ctx->rgb8.p, nullptr, ctx->stream, no_views, ctx->tiles));
+    // tile-sharded frame on the root: the other ranks' resolve kernels store their tiles' bytes straight into this image over
+    // NVLink and bump its counter; the stream waits for all of them here, before the image is encoded or copied
+    bool waited = false;
+    if (ctx->tiles.world > 1 && ctx->frame_exported && ctx->tiles_pending) {
+        ctx->frame_target += unsigned(ctx->tiles.world - 1);
+        CK(launch_frame_wait(reinterpret_cast<const unsigned*>(ctx->rgb8.p + frame_counter_offset(npix)), ctx->frame_target, 10000,
+                             ctx->frame_timeout.p, ctx->stream));
+        ctx->tiles_pending = false; waited = true; ++launches;
+    }
     unsigned long long text_len = 0;
     if (ppm || (ppm_len && !ppm)) {
         EncodeHeader hdr;
@@ -643,6 +700,14 @@ extern "C" int rt_readback(rt_ctx* ctx, int spp_total, double* sum_rgb, uint8_t*
     if (sum_rgb) CK(cudaMemcpyAsync(sum_rgb, ctx->sum.p, npix * 3 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     if (rgb8) CK(cudaMemcpyAsync(rgb8, ctx->rgb8.p, npix * 3, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    if (waited) {
+        int timed_out = 0;
+        CK(cudaMemcpy(&timed_out, ctx->frame_timeout.p, sizeof timed_out, cudaMemcpyDeviceToHost));
+        if (timed_out) {
+            CK(cudaMemset(ctx->frame_timeout.p, 0, sizeof(int)));
+            return fail(ctx, RT_E_STATE, "rt_readback: the other ranks' tiles did not arrive within 10 s (did every rank call rt_resolve_tiles for this frame?)");
+        }
+    }
     if (ppm_len) {
         if (ppm) {
             if (*ppm_len < text_len) { *ppm_len = size_t(text_len); return fail(ctx, RT_E_INVALID, "rt_readback: ppm buffer too small"); }
@@ -660,14 +725,14 @@ extern "C" int rt_readback(rt_ctx* ctx, int spp_total, double* sum_rgb, uint8_t*
 static int resolve_views(rt_ctx* ctx, int spp_total, const FrameViews& v) {
     if (ctx->peers.n > 0 && !ctx->folded) return fail(ctx, RT_E_STATE, "resolve: peers are mapped; every rank must call rt_fold_slices before the fused resolve");
     const size_t npix = size_t(ctx->W) * ctx->H;
-    CK(ctx->rgb8.resize(npix * 3 + 16));
+    CK(ensure_rgb8(ctx, npix));
     const double scale = spp_total > 0 ? 1.0 / spp_total : 0.0;
     if (ctx->precision == RT_F32)
         CK(launch_resolve<float4>(reinterpret_cast<const float4*>(ctx->accum.p), live_slices(ctx), live_peers(ctx), npix, scale,
-                                  nullptr, ctx->rgb8.p, nullptr, ctx->stream, v));
+                                  nullptr, ctx->rgb8.p, nullptr, ctx->stream, v, ctx->tiles));
     else
         CK(launch_resolve<double4>(reinterpret_cast<const double4*>(ctx->accum.p), live_slices(ctx), live_peers(ctx), npix, scale,
-                                   nullptr, ctx->rgb8.p, nullptr, ctx->stream, v));
+                                   nullptr, ctx->rgb8.p, nullptr, ctx->stream, v, ctx->tiles));
     return RT_OK;
 }
 
@@ -811,6 +876,68 @@ extern "C" int rt_ipc_open_peers(rt_ctx* ctx, const void* handles, int n_peers) 
         ctx->peers.slices[i] = 1;
         ctx->peers.n = i + 1;
     }
+    return RT_OK;
+}
+
+// ---- tile-sharded frames: the image hand-over (rt_b200.h) ----
+struct FrameBlob { cudaIpcMemHandle_t h; int32_t W, H, magic, pad; };
+static_assert(sizeof(FrameBlob) == RT_IPC_HANDLE_BYTES, "frame blob size");
+
+extern "C" int rt_frame_export(rt_ctx* ctx, void* handle) {
+    if (!ctx || !handle) return RT_E_INVALID;
+    if (ctx->W == 0) return fail(ctx, RT_E_STATE, "rt_frame_export: render once first (the image size must be known)");
+    CK(cudaSetDevice(ctx->device));
+    const size_t npix = size_t(ctx->W) * ctx->H;
+    CK(ensure_rgb8(ctx, npix));
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemset(ctx->rgb8.p + frame_counter_offset(npix), 0, 128));
+    FrameBlob b;
+    CK(cudaIpcGetMemHandle(&b.h, ctx->rgb8.p));
+    b.W = ctx->W; b.H = ctx->H; b.magic = 0x52544652; b.pad = 0;
+    std::memcpy(handle, &b, sizeof b);
+    ctx->frame_exported = true; ctx->frame_target = 0;
+    return RT_OK;
+}
+
+extern "C" int rt_frame_close(rt_ctx* ctx) {
+    if (!ctx) return RT_E_INVALID;
+    if (ctx->frame_remote) { cudaIpcCloseMemHandle(ctx->frame_remote); ctx->frame_remote = nullptr; }
+    ctx->frame_exported = false; ctx->frame_target = 0;
+    return RT_OK;
+}
+
+extern "C" int rt_frame_open(rt_ctx* ctx, const void* handle) {
+    if (!ctx || !handle) return RT_E_INVALID;
+    CK(cudaSetDevice(ctx->device));
+    FrameBlob b;
+    std::memcpy(&b, handle, sizeof b);
+    if (b.magic != 0x52544652) return fail(ctx, RT_E_INVALID, "rt_frame_open: not a frame handle");
+    if (ctx->frame_remote) { cudaIpcCloseMemHandle(ctx->frame_remote); ctx->frame_remote = nullptr; }
+    void* p = nullptr;
+    CK(cudaIpcOpenMemHandle(&p, b.h, cudaIpcMemLazyEnablePeerAccess));
+    ctx->frame_remote = p; ctx->frame_remote_W = b.W; ctx->frame_remote_H = b.H;
+    return RT_OK;
+}
+
+extern "C" int rt_resolve_tiles(rt_ctx* ctx, int spp_total) {
+    if (!ctx) return RT_E_INVALID;
+    if (ctx->W == 0 || !ctx->accum.p) return fail(ctx, RT_E_STATE, "rt_resolve_tiles: nothing rendered");
+    if (ctx->tiles.world <= 1) return fail(ctx, RT_E_STATE, "rt_resolve_tiles: the last render was not tile-sharded");
+    if (!ctx->frame_remote) return fail(ctx, RT_E_STATE, "rt_resolve_tiles: no root image mapped (rt_frame_open)");
+    if (ctx->frame_remote_W != ctx->W || ctx->frame_remote_H != ctx->H) return fail(ctx, RT_E_STATE, "rt_resolve_tiles: the root's image has another size");
+    CK(cudaSetDevice(ctx->device));
+    const size_t npix = size_t(ctx->W) * ctx->H;
+    const double scale = spp_total > 0 ? 1.0 / spp_total : 0.0;
+    unsigned char* image = static_cast<unsigned char*>(ctx->frame_remote);
+    const FrameViews no_views{nullptr, nullptr, 0, 0};
+    PeerList none = {};
+    if (ctx->precision == RT_F32)
+        CK(launch_resolve<float4>(reinterpret_cast<const float4*>(ctx->accum.p), live_slices(ctx), none, npix, scale, nullptr, image, nullptr, ctx->stream, no_views, ctx->tiles));
+    else
+        CK(launch_resolve<double4>(reinterpret_cast<const double4*>(ctx->accum.p), live_slices(ctx), none, npix, scale, nullptr, image, nullptr, ctx->stream, no_views, ctx->tiles));
+    CK(launch_frame_signal(reinterpret_cast<unsigned*>(image + frame_counter_offset(npix)), ctx->stream));
+    ctx->tiles_pending = false;
+    ctx->stats.kernel_launches = (ctx->render_timed ? 1 : 0) + 2;
     return RT_OK;
 }
 

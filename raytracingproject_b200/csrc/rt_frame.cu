@@ -19,11 +19,27 @@ __device__ __forceinline__ unsigned char write_color_byte(double sum, double sca
 // 3 x 32-bit stores of packed rgb.  Slices and peers are summed in a fixed order, so the image is
 // reproducible.  peers[] are device pointers of other ranks' buffers opened through CUDA IPC: the
 // loads cross NVLink inside this kernel (fused reduce + resolve).
+__device__ __forceinline__ bool owns_pixel(const TileOwner& o, size_t pixel) {
+    const int y = int(pixel / size_t(o.width)), x = int(pixel - size_t(y) * size_t(o.width));
+    const int tile = (y / o.tile_h) * o.tiles_x + x / o.tile_w;
+    return (tile / o.group) % o.world == o.rank;
+}
+
 template <typename Q>
 __global__ void resolve_kernel(const Q* __restrict__ accum, int slices, PeerList peers, size_t n_pixels, double scale,
-                               double* __restrict__ sum_out, unsigned char* __restrict__ rgb8, Q* __restrict__ reduced_out, FrameViews views) {
+                               double* __restrict__ sum_out, unsigned char* __restrict__ rgb8, Q* __restrict__ reduced_out, FrameViews views,
+                               TileOwner owner) {
     const size_t g = (size_t(blockIdx.x) * blockDim.x + threadIdx.x) * 4;
     if (g >= n_pixels) return;
+    // tile-sharded frame: only the pixels this rank rendered (the image the bytes go to may be another GPU's, over NVLink)
+    bool mine[4] = { true, true, true, true };
+    bool all_mine = true;
+    if (owner.world > 1) {
+        bool any = false;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { mine[k] = g + k < n_pixels && owns_pixel(owner, g + k); any = any || mine[k]; all_mine = all_mine && mine[k]; }
+        if (!any) return;
+    }
     double s[4][4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) s[k][0] = s[k][1] = s[k][2] = s[k][3] = 0.0;
@@ -44,7 +60,7 @@ __global__ void resolve_kernel(const Q* __restrict__ accum, int slices, PeerList
     unsigned char b[12];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-        if (k < np) {
+        if (k < np && mine[k]) {
             const double sc = scale > 0.0 ? scale : 1.0 / s[k][3];       // spp_total = 0: samples actually accumulated
             b[3 * k + 0] = write_color_byte(s[k][0], sc);
             b[3 * k + 1] = write_color_byte(s[k][1], sc);
@@ -61,9 +77,11 @@ __global__ void resolve_kernel(const Q* __restrict__ accum, int slices, PeerList
         }
     }
     if (views.rgba8)
-        for (int k = 0; k < np; ++k) views.rgba8[g + k] = make_uchar4(b[3 * k], b[3 * k + 1], b[3 * k + 2], 255);
+        for (int k = 0; k < np; ++k) if (mine[k]) views.rgba8[g + k] = make_uchar4(b[3 * k], b[3 * k + 1], b[3 * k + 2], 255);
     if (rgb8) {
-        if (np == 4) {
+        if (!all_mine) {                        // a 4-pixel group that straddles two owners (image width not a multiple of 4)
+            for (int k = 0; k < np; ++k) if (mine[k]) { rgb8[3 * (g + k)] = b[3 * k]; rgb8[3 * (g + k) + 1] = b[3 * k + 1]; rgb8[3 * (g + k) + 2] = b[3 * k + 2]; }
+        } else if (np == 4) {
             unsigned int* dst = reinterpret_cast<unsigned int*>(rgb8 + 3 * g);      // g % 4 == 0 -> 12-byte groups, 4-aligned
             dst[0] = b[0] | (b[1] << 8) | (b[2] << 16) | (unsigned(b[3]) << 24);
             dst[1] = b[4] | (b[5] << 8) | (b[6] << 16) | (unsigned(b[7]) << 24);
@@ -76,14 +94,42 @@ __global__ void resolve_kernel(const Q* __restrict__ accum, int slices, PeerList
 
 template <typename Q>
 cudaError_t launch_resolve(const Q* accum, int slices, const PeerList& peers, size_t n_pixels, double scale,
-                           double* sum_out, unsigned char* rgb8, Q* reduced_out, cudaStream_t st, const FrameViews& views) {
+                           double* sum_out, unsigned char* rgb8, Q* reduced_out, cudaStream_t st, const FrameViews& views, const TileOwner& owner) {
     if (n_pixels == 0) return cudaSuccess;
     const size_t threads = (n_pixels + 3) / 4;
-    resolve_kernel<Q><<<unsigned((threads + 255) / 256), 256, 0, st>>>(accum, slices, peers, n_pixels, scale, sum_out, rgb8, reduced_out, views);
+    resolve_kernel<Q><<<unsigned((threads + 255) / 256), 256, 0, st>>>(accum, slices, peers, n_pixels, scale, sum_out, rgb8, reduced_out, views, owner);
     return cudaGetLastError();
 }
-template cudaError_t launch_resolve<float4>(const float4*, int, const PeerList&, size_t, double, double*, unsigned char*, float4*, cudaStream_t, const FrameViews&);
-template cudaError_t launch_resolve<double4>(const double4*, int, const PeerList&, size_t, double, double*, unsigned char*, double4*, cudaStream_t, const FrameViews&);
+template cudaError_t launch_resolve<float4>(const float4*, int, const PeerList&, size_t, double, double*, unsigned char*, float4*, cudaStream_t, const FrameViews&, const TileOwner&);
+template cudaError_t launch_resolve<double4>(const double4*, int, const PeerList&, size_t, double, double*, unsigned char*, double4*, cudaStream_t, const FrameViews&, const TileOwner&);
+
+// ---------------------------------------------------------- tile-sharded frame hand-over --
+// (see rt_frame.h)  The signal runs AFTER the peer's resolve kernel on the same stream, so that kernel's stores to the
+// root's image have been performed; the fence + system-scope atomic publish them to the root GPU.
+__global__ void frame_signal_kernel(unsigned* remote_counter) {
+    __threadfence_system();
+    atomicAdd_system(remote_counter, 1u);
+}
+__global__ void frame_wait_kernel(const unsigned* counter, unsigned target, long long timeout_ns, int* timed_out) {
+    unsigned long long t0, t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (;;) {
+        const unsigned v = *reinterpret_cast<const volatile unsigned*>(counter);
+        if (int(v - target) >= 0) break;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        if ((long long)(t - t0) > timeout_ns) { *timed_out = 1; break; }
+        __nanosleep(200);
+    }
+    __threadfence_system();
+}
+cudaError_t launch_frame_signal(unsigned* remote_counter, cudaStream_t st) {
+    frame_signal_kernel<<<1, 1, 0, st>>>(remote_counter);
+    return cudaGetLastError();
+}
+cudaError_t launch_frame_wait(const unsigned* counter, unsigned target, int timeout_ms, int* timed_out, cudaStream_t st) {
+    frame_wait_kernel<<<1, 1, 0, st>>>(counter, target, (long long)timeout_ms * 1000000ll, timed_out);
+    return cudaGetLastError();
+}
 
 // -------------------------------------------------------------------------- slice fold --
 // The wavefront kernel renders a pixel's samples in `slices` groups, each into its own [H][W] layer

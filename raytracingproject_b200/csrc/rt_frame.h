@@ -22,10 +22,23 @@ struct EncodeHeader { int len; char text[48]; };     // "P3\n<W> <H>\n255\n" (sr
 //   rgba8  the write_color bytes + alpha 255, 4 bytes per pixel: the headless stand-in for a presentable image
 struct FrameViews { float* pfm; uchar4* rgba8; int width, height; };
 
+// tile-interleaved sharding: the resolve pass of a rank touches only the pixels of the tile groups it
+// rendered -- (tile / group) % world == rank, tiles of tile_w x tile_h pixels, tiles_x per row of an image `width` wide.
+// world <= 1: every pixel.
+struct TileOwner { int world, rank, tiles_x, tile_w, tile_h, group, width; };
+
 template <typename Q>
 cudaError_t launch_resolve(const Q* accum, int slices, const PeerList& peers, size_t n_pixels, double scale,
                            double* sum_out, unsigned char* rgb8, Q* reduced_out, cudaStream_t st,
-                           const FrameViews& views = FrameViews{nullptr, nullptr, 0, 0});
+                           const FrameViews& views = FrameViews{nullptr, nullptr, 0, 0},
+                           const TileOwner& owner = TileOwner{0, 0, 0, 0, 0, 0, 0});
+
+// Stream-ordered hand-over of tile-sharded frames between GPUs: a peer that has written its tiles' bytes into the root's
+// image (stores over NVLink inside its resolve kernel) bumps a counter in the root's memory (launch_frame_signal, after
+// the resolve on the same stream); the root's stream waits until the counter reaches `target` (launch_frame_wait) before
+// it encodes / copies the image.  *timed_out (device int, root) is set when the wait gives up after ~timeout_ms.
+cudaError_t launch_frame_signal(unsigned* remote_counter, cudaStream_t st);
+cudaError_t launch_frame_wait(const unsigned* counter, unsigned target, int timeout_ms, int* timed_out, cudaStream_t st);
 
 // sums the sample layers of the accumulation buffer into layer 0 and zeroes the others (before a multi-GPU combine)
 template <typename Q> cudaError_t launch_fold(Q* accum, int slices, size_t n_pixels, cudaStream_t st);

@@ -32,6 +32,7 @@ template <typename T> struct RenderParams {
     int bulk_layers;                    // wavefront job order: tile-major over the first bulk_layers layers, then layer by layer
     int slice_begin[RT_MAX_SLICES + 1]; // wavefront: samples [slice_begin[k], slice_begin[k+1]) of a pixel form layer k (sizes may differ)
     int accumulate;
+    int tile_rank, tile_world;          // wavefront: tile-interleaved sharding -- this launch renders the tile groups g with g % tile_world == tile_rank
     int th_s, th_l, th_n;               // section thresholds of the warp schedulers (render_sched_kernel, render_pool_kernel)
 };
 

@@ -94,7 +94,102 @@ __global__ void widen_kernel(const float4* __restrict__ n2, int n_nodes, float4*
     o[7] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
 }
 
+// ---- top of the tree first (north_star item 2: "staged in shared memory for the top levels") ----
+// A tree too large for shared memory is walked in global memory, but its first levels are fetched by EVERY ray.
+// This pass renumbers the inner nodes so that the first k of them in breadth-first order from the root are node
+// indices 0 .. k-1 (any prefix of a breadth-first order is closed under "parent of"), which lets a render kernel
+// copy nodes [0, n_top) next to its path pools and walk `cur < n_top` from shared memory, the rest from L2 / HBM.
+//   top_select_kernel   one block: level-synchronous BFS over at most k inner nodes -> newpos[] (old index -> new index):
+//                       top node j goes to j, the nodes that sat in 0 .. k-1 before move to the places the top nodes left
+//   top_permute_kernel  every record moves to newpos[i] with its two child refs renamed
+__global__ void iota_kernel(int* __restrict__ a, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) a[i] = i;
+}
+
+#define RT_TOP_BLOCK 1024
+__global__ void __launch_bounds__(RT_TOP_BLOCK) top_select_kernel(const float4* __restrict__ nodes, int n_nodes, int root, int k,
+                                                                  int* __restrict__ newpos, int* __restrict__ top_ids) {
+    __shared__ int frontier[2][2 * RT_TOP_BLOCK];
+    __shared__ int cnt[RT_TOP_BLOCK + 1];
+    __shared__ int n_front, n_top;
+    const int t = threadIdx.x;
+    if (t == 0) { frontier[0][0] = root; n_front = 1; n_top = 0; }
+    __syncthreads();
+    int cur = 0;
+    while (true) {
+        const int nf = n_front, base = n_top;
+        if (nf == 0 || base >= k) break;
+        const int take = min(nf, k - base);                       // this level's nodes that still fit, in frontier order
+        int cl = -1, cr = -1;
+        if (t < take) {
+            const int node = frontier[cur][t];
+            top_ids[base + t] = node;
+            const float4 q3 = nodes[4 * size_t(node) + 3];
+            cl = __float_as_int(q3.x); cr = __float_as_int(q3.y);
+        }
+        cnt[t] = (cl >= 0) + (cr >= 0);
+        __syncthreads();
+        if (t == 0) {                                              // exclusive prefix over <= 1024 counts
+            int acc = 0;
+            for (int i = 0; i < take; ++i) { const int c = cnt[i]; cnt[i] = acc; acc += c; }
+            n_front = min(acc, 2 * RT_TOP_BLOCK); n_top = base + take;
+        }
+        __syncthreads();
+        if (t < take) {
+            int o = cnt[t];
+            if (cl >= 0 && o < 2 * RT_TOP_BLOCK) frontier[cur ^ 1][o++] = cl;
+            if (cr >= 0 && o < 2 * RT_TOP_BLOCK) frontier[cur ^ 1][o++] = cr;
+        }
+        cur ^= 1;
+        __syncthreads();
+        if (n_front > RT_TOP_BLOCK) { if (t == 0) n_front = RT_TOP_BLOCK; __syncthreads(); }   // k <= RT_TOP_BLOCK: the rest never fits anyway
+    }
+    __syncthreads();
+    const int kk = n_top;                                          // top nodes found (<= k)
+    // old indices 0 .. kk-1 that are not top nodes trade places with the top nodes that sat at >= kk
+    int* mark = frontier[0];                                       // mark[i] = 1: old index i (< kk) is a top node
+    for (int i = t; i < kk; i += RT_TOP_BLOCK) mark[i] = 0;
+    __syncthreads();
+    for (int j = t; j < kk; j += RT_TOP_BLOCK) { const int o = top_ids[j]; if (o < kk) mark[o] = 1; }
+    __syncthreads();
+    if (t == 0) {
+        int a = 0;                                                 // next displaced old index
+        for (int j = 0; j < kk; ++j) {
+            const int o = top_ids[j];
+            newpos[o] = j;
+            if (o >= kk) {
+                while (mark[a]) ++a;
+                newpos[a++] = o;
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) top_permute_kernel(const float4* __restrict__ src, const int* __restrict__ newpos, int n_nodes,
+                                                          float4* __restrict__ dst) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_nodes) return;
+    const float4 q0 = src[4 * size_t(i) + 0], q1 = src[4 * size_t(i) + 1], q2 = src[4 * size_t(i) + 2];
+    float4 q3 = src[4 * size_t(i) + 3];
+    const int cl = __float_as_int(q3.x), cr = __float_as_int(q3.y);
+    if (cl >= 0) q3.x = __int_as_float(newpos[cl]);
+    if (cr >= 0) q3.y = __int_as_float(newpos[cr]);
+    float4* o = dst + 4 * size_t(newpos[i]);
+    o[0] = q0; o[1] = q1; o[2] = q2; o[3] = q3;
+}
+
 }  // namespace
+
+cudaError_t launch_top_first(const float4* nodes, int n_nodes, int root_ref, int k, int* newpos, int* top_ids, float4* nodes_out, cudaStream_t st) {
+    if (n_nodes <= 0 || root_ref < 0) return cudaSuccess;
+    k = k < n_nodes ? k : n_nodes;
+    if (k > RT_TOP_BLOCK) k = RT_TOP_BLOCK;
+    iota_kernel<<<(n_nodes + 255) / 256, 256, 0, st>>>(newpos, n_nodes);
+    top_select_kernel<<<1, RT_TOP_BLOCK, 0, st>>>(nodes, n_nodes, root_ref, k, newpos, top_ids);
+    top_permute_kernel<<<(n_nodes + 255) / 256, 256, 0, st>>>(nodes, newpos, n_nodes, nodes_out);
+    return cudaGetLastError();
+}
 
 cudaError_t launch_widen(const float4* nodes2, int n_nodes, float4* nodes4, cudaStream_t st) {
     if (n_nodes <= 0) return cudaSuccess;

@@ -18,6 +18,12 @@ cudaError_t launch_scene_fill(const rt_sphere* spheres, const rt_material* mater
                               float4* a32, float4* b32, float4* c32, double4* a64, double4* b64, double4* c64, int* meta,
                               cudaStream_t st);
 
+// Renumbers the inner nodes so that the first min(k, n_nodes, RT_TOP_MAX) of them in breadth-first order from the
+// root become indices 0, 1, 2, ... (the root becomes node 0): nodes_out = the permuted records with renamed child refs.
+// newpos (n_nodes ints) and top_ids (RT_TOP_MAX ints) are scratch.  Nothing is done when the root is a leaf.
+#define RT_TOP_MAX 1024
+cudaError_t launch_top_first(const float4* nodes, int n_nodes, int root_ref, int k, int* newpos, int* top_ids, float4* nodes_out, cudaStream_t st);
+
 // 4-wide records (layout: rt_trace.cuh) of a binary tree: record i = the grandchildren of binary node i
 cudaError_t launch_widen(const float4* nodes2, int n_nodes, float4* nodes4, cudaStream_t st);
 

@@ -31,6 +31,7 @@ template <typename T> struct SceneView {
     const double4* big_c;
     const int* big_meta;
     int n_slots, n_nodes, n_big, root_ref;
+    int n_top;                 // wavefront, scene in global memory: nodes [0, n_top) are also kept in shared memory (the tree's first levels)
     int off_sa, off_sb, off_sc, off_meta;   // byte offsets of the staged copies in shared memory (nodes at 0)
 };
 
@@ -205,6 +206,31 @@ __device__ __forceinline__ void trav_node(const float4* __restrict__ nodes, cons
     if (hl && hr && tv.sp < RT_STACK) { stack[tv.sp++] = far; tv.tos = far; }
     int next = near;
     if (!(hl || hr)) {                      // pop: the top of the stack is in a register (RT_SENTINEL when the stack is empty)
+        next = tv.tos;
+        if (tv.sp > 0) --tv.sp;
+        tv.tos = tv.sp > 0 ? stack[tv.sp - 1] : RT_SENTINEL;
+    }
+    tv.cur = next;
+}
+
+// The same visit for a tree in global memory whose first n_top nodes (breadth-first from the root, rt_scene.cu
+// launch_top_first) are ALSO resident in shared memory: the upper levels, which every ray fetches, come from `top`
+// (LDS latency), the rest from L2 / HBM.  One generic-address load path for both, no divergence.
+template <typename T>
+__device__ __forceinline__ void trav_node_top(const float4* __restrict__ nodes, const float4* top, int n_top, const Ray<T>& r, T tmin,
+                                              Trav<T>& tv, int* stack) {
+    const int cur = tv.cur;
+    const float4* rec = (cur < n_top ? top : nodes) + 4 * size_t(cur);
+    const float4 q0 = rec[0], q1 = rec[1], q2 = rec[2], q3 = rec[3];
+    T tl, tr;
+    bool hl, hr;
+    node_boxes(q0, q1, q2, tv.slab, tmin, tv.tbest, hl, hr, tl, tr);
+    const int cl = __float_as_int(q3.x), cr = __float_as_int(q3.y);
+    const bool left_first = !hr || (hl && tl <= tr);
+    const int near = left_first ? cl : cr, far = left_first ? cr : cl;
+    if (hl && hr && tv.sp < RT_STACK) { stack[tv.sp++] = far; tv.tos = far; }
+    int next = near;
+    if (!(hl || hr)) {
         next = tv.tos;
         if (tv.sp > 0) --tv.sp;
         tv.tos = tv.sp > 0 ? stack[tv.sp - 1] : RT_SENTINEL;

@@ -75,8 +75,17 @@ render_pool_kernel(const RenderParams<T> p) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned lt = (1u << lane) - 1u;
+    // a scene that stays in global memory: the first levels of its tree (nodes [0, n_top), breadth-first from the root) are
+    // copied in front of the pools and walked from shared memory; the rest of the tree is fetched from L2 / HBM
+    const int n_top = (STAGED || WIDE) ? 0 : sv.n_top;
+    const float4* const top = reinterpret_cast<const float4*>(smem);
+    if (!STAGED && !WIDE && n_top > 0) {
+        float4* t = reinterpret_cast<float4*>(smem);
+        for (int i = threadIdx.x; i < 4 * n_top; i += BLOCK) t[i] = sv.nodes[i];
+        __syncthreads();
+    }
 
-    unsigned char* wb = smem + (STAGED ? staged_bytes_aligned<T>(sv.n_nodes, sv.n_slots) : 0) + size_t(warp) * L::bytes;
+    unsigned char* wb = smem + (STAGED ? staged_bytes_aligned<T>(sv.n_nodes, sv.n_slots) : size_t(n_top) * 64) + size_t(warp) * L::bytes;
     T* const F = reinterpret_cast<T*>(wb);
     int* const I = reinterpret_cast<int*>(F + L::NF * P);
     unsigned short* const S = reinterpret_cast<unsigned short*>(I + L::NI * P);
@@ -87,8 +96,12 @@ render_pool_kernel(const RenderParams<T> p) {
     const int W = p.cam.image_width, H = p.cam.image_height;
     // Jobs are fetched `group` at a time: the same layer of `group` horizontally adjacent tiles, so that the jobs a warp
     // holds open lie next to each other in the image (rays of neighbouring tiles walk the same part of the tree)
-    const int group = p.job_group, ntiles = p.tiles_x * p.tiles_y, ngroups = (ntiles + group - 1) / group;
-    const int nbulk = ngroups * group * p.bulk_layers, njobs = nbulk + (p.slices - p.bulk_layers) * ntiles;
+    // Tile-interleaved sharding over GPUs: of the frame's tile groups this launch owns those whose index is
+    // tile_rank modulo tile_world (every one with tile_world = 1); local group gl stands for group gl * tile_world + tile_rank
+    const int group = p.job_group, ntiles = p.tiles_x * p.tiles_y;
+    const int tw = p.tile_world > 1 ? p.tile_world : 1, tr = p.tile_world > 1 ? p.tile_rank : 0;
+    const int ngroups = ((ntiles + group - 1) / group - tr + tw - 1) / tw, ntiles_l = ngroups * group;
+    const int nbulk = ntiles_l * p.bulk_layers, njobs = nbulk + (p.slices - p.bulk_layers) * ntiles_l;
     int pend_next = 0, pend_left = 0;
     const size_t layer = size_t(H) * size_t(W);
     const int th_p = p.th_s, th_l = p.th_l, th_n = p.th_n;
@@ -141,8 +154,8 @@ render_pool_kernel(const RenderParams<T> p) {
                         // open jobs of a warp 30 tile rows apart -- measured 4 % slower), then the short layers one after the
                         // other, so that the frame ends on small jobs
                         int slice, tile;
-                        if (job < nbulk) { const int gl = group * p.bulk_layers, g = job / gl, r = job - g * gl; slice = r / group; tile = group * g + (r - slice * group); }
-                        else { const int r = job - nbulk; slice = r / ntiles; tile = r - slice * ntiles; slice += p.bulk_layers; }
+                        if (job < nbulk) { const int gl = group * p.bulk_layers, g = job / gl, r = job - g * gl; slice = r / group; tile = group * (g * tw + tr) + (r - slice * group); }
+                        else { const int r = job - nbulk; slice = r / ntiles_l; const int tl = r - slice * ntiles_l, g = tl / group; tile = group * (g * tw + tr) + (tl - g * group); slice += p.bulk_layers; }
                         const bool none = tile >= ntiles;                       // the last group may be short of tiles: an empty job outside the image
                         const int bx = none ? 0x7fff : (tile % p.tiles_x) * L::tile_w, by = none ? 0 : (tile / p.tiles_x) * L::tile_h;
                         const int s_begin = none ? 0 : p.slice_begin[slice], s_end = none ? 0 : p.slice_begin[slice + 1];
@@ -285,8 +298,10 @@ render_pool_kernel(const RenderParams<T> p) {
                                 if (tv.cur >= 0) trav_node4<T>(sv.nodes4, ray, T(0.001), tv, stack);
                             } else {
 #pragma unroll
-                                for (int v = 0; v < RT_NODE_VISITS; ++v)
-                                    if (tv.cur >= 0) trav_node<T>(st.nodes, ray, T(0.001), tv, stack);
+                                for (int v = 0; v < RT_NODE_VISITS; ++v) {
+                                    if (STAGED) { if (tv.cur >= 0) trav_node<T>(st.nodes, ray, T(0.001), tv, stack); }
+                                    else { if (tv.cur >= 0) trav_node_top<T>(st.nodes, top, n_top, ray, T(0.001), tv, stack); }
+                                }
                             }
                             now = __popc(__ballot_sync(FULL, tv.cur >= 0));
                         } while (now > 0 && now * 8 >= nN * th_n);

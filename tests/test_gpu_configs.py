@@ -265,3 +265,38 @@ def test_failed_upload_leaves_no_scene(ctx, rt):
     ctx.upload_scene(s, m)
     ctx.render(rt.camera_rtiow(32, 1, 5))
     ctx.synchronize()
+
+
+# ------------------------------------------------------------ tile-interleaved sharding, one GPU --
+@pytest.mark.parametrize("width,spp,world", [(400, 6, 2), (97, 3, 3), (160, 4, 8), (33, 2, 5)])
+def test_tile_shards_rendered_one_after_the_other_compose_the_frame(ctx_scene, rt, O, scene, width, spp, world):
+    """SURVEY.md 8e tile sharding without a second GPU: the tile shares of `world` ranks are rendered one after the other by the
+    same context; every readback resolves only the share just rendered into the image, so after the last one the image (and
+    its P3 text) is the oracle's full frame, bit for bit in parity mode (no sum crosses a shard: the combine has no arithmetic).
+    Widths that are not a multiple of 4 exercise the resolve groups that straddle two owners; the 2-GPU version with the
+    bytes crossing NVLink is tests/test_gpu_multi.py."""
+    s, m = scene
+    cam = rt.camera_rtiow(width, spp, 50)
+    ref = O.render(s, m, O.camera_rtiow(width, spp, 50), rng_mode=O.RNG_PHILOX, seed=9, use_bvh=True)
+    # poison the image first: a full frame of another seed
+    ctx_scene.render(cam, precision=rt.F64, seed=10)
+    ctx_scene.readback(spp)
+    rays = 0
+    for rank in range(world):
+        ctx_scene.render(cam, precision=rt.F64, seed=9, tile_rank=rank, tile_world=world)
+        out = ctx_scene.readback(spp, want_ppm=True)
+        rays += ctx_scene.stats()["rays"]
+        if rank < world - 1 and world <= width // 32:
+            assert not np.array_equal(out["rgb8"], ref["rgb8"])            # still holds other tiles of the poison frame
+    assert rays == ref["rays"]
+    assert np.array_equal(out["rgb8"], ref["rgb8"])
+    assert out["ppm"] == O.ppm_p3(ref["rgb8"])
+    # fast mode: same composition, north_star tolerance against the oracle
+    for rank in range(world):
+        ctx_scene.render(cam, precision=rt.F32, seed=9, tile_rank=rank, tile_world=world)
+        o32 = ctx_scene.readback(spp)
+    assert frac_within_1(o32["rgb8"], ref["rgb8"]) >= 0.99
+    with pytest.raises(rt.RtError):
+        ctx_scene.render(cam, precision=rt.F32, seed=9, tile_rank=2, tile_world=2)
+    with pytest.raises(rt.RtError):
+        ctx_scene.render(cam, precision=rt.F32, seed=9, tile_rank=0, tile_world=2, variant=rt.MEGAKERNEL)
