@@ -7,6 +7,7 @@
 #include <chrono>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <random>
 #include <string>
@@ -430,7 +431,7 @@ extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_s
     // top of the tree first: nodes 0 .. k-1 = the first levels in breadth-first order, so that a render whose scene stays in
     // global memory can keep them in shared memory (north_star item 2).  Parity is defined on hits, not on node numbers.
     ctx->top_ordered = 0;
-    if (ctx->n_nodes > 1 && ctx->root_ref >= 0) {
+    if (ctx->n_nodes > 1 && ctx->root_ref >= 0 && !std::getenv("RT_NO_TOP_FIRST")) {       // (the env knob is for A/B measurements)
         DevBuf<int> newpos, top_ids; DevBuf<float4> permuted;
         CK(newpos.resize(ctx->n_nodes)); CK(top_ids.resize(RT_TOP_MAX)); CK(permuted.resize(size_t(ctx->n_nodes) * 4));
         CK(launch_top_first(ctx->nodes.p, ctx->n_nodes, ctx->root_ref, RT_TOP_MAX, newpos.p, top_ids.p, permuted.p, ctx->stream));
@@ -529,6 +530,7 @@ int render_impl(rt_ctx* ctx, const rt_camera& cam, const rt_render_opts& o, int 
     p.job_counter = ctx->job_counter.p;
     p.ray_counter = ctx->ray_counter.p;
     p.seed = o.seed;
+    philox_round_keys(o.seed, p.keys);
     p.sample_begin = sample_begin; p.sample_count = sample_count; p.max_depth = cam.max_depth;
     p.slices = slices;
     for (int k = 0; k <= slices; ++k) p.slice_begin[k] = ctx->slice_begin[k];
@@ -670,31 +672,49 @@ extern "C" int rt_readback(rt_ctx* ctx, int spp_total, double* sum_rgb, uint8_t*
     CK(cudaEventRecord(ctx->ev[2], ctx->stream));
     int launches = 1;
     const FrameViews no_views{nullptr, nullptr, 0, 0};
-    if (ctx->precision == RT_F32)
-        CK(launch_resolve<float4>(reinterpret_cast<const float4*>(ctx->accum.p), live_slices(ctx), live_peers(ctx), npix, scale,
-                                  sum_rgb ? ctx->sum.p : nullptr, ctx->rgb8.p, nullptr, ctx->stream, no_views, ctx->tiles));
-    else
-        CK(launch_resolve<double4>(reinterpret_cast<const double4*>(ctx->accum.p), live_slices(ctx), live_peers(ctx), npix, scale,
-                                   sum_rgb ? ctx->sum.p : nullptr, ctx->rgb8.p, nullptr, ctx->stream, no_views, ctx->tiles));
-    // tile-sharded frame on the root: the other ranks' resolve kernels store their tiles' bytes straight into this image over
-    // NVLink and bump its counter; the stream waits for all of them here, before the image is encoded or copied
-    bool waited = false;
-    if (ctx->tiles.world > 1 && ctx->frame_exported && ctx->tiles_pending) {
-        ctx->frame_target += unsigned(ctx->tiles.world - 1);
-        CK(launch_frame_wait(reinterpret_cast<const unsigned*>(ctx->rgb8.p + frame_counter_offset(npix)), ctx->frame_target, 10000,
-                             ctx->frame_timeout.p, ctx->stream));
-        ctx->tiles_pending = false; waited = true; ++launches;
-    }
+    const bool want_text = ppm || (ppm_len && !ppm);
+    // whole frame on this GPU, text wanted, no per-pixel sums: ONE kernel from the accumulation layers to rgb8 + P3 text
+    const bool fused = want_text && !sum_rgb && ctx->tiles.world <= 1 && !std::getenv("RT_NO_FUSED_ENCODE");
     unsigned long long text_len = 0;
-    if (ppm || (ppm_len && !ppm)) {
+    bool waited = false;
+    if (fused) {
         EncodeHeader hdr;
         hdr.len = std::snprintf(hdr.text, sizeof hdr.text, "P3\n%d %d\n255\n", ctx->W, ctx->H);   // src/camera.h:35
         const int nb = encode_blocks(npix);
-        CK(ctx->enc_sums.resize(nb + 1)); CK(ctx->enc_offsets.resize(nb + 2));
+        CK(ctx->enc_offsets.resize(nb + 3));
         CK(ctx->text.resize(npix * 12 + 64));
-        CK(launch_encode_p3(ctx->rgb8.p, npix, hdr, ctx->enc_sums.p, ctx->enc_offsets.p, ctx->enc_offsets.p + nb + 1, ctx->text.p, ctx->stream));
-        launches += 3;
-        CK(cudaMemcpyAsync(&text_len, ctx->enc_offsets.p + nb + 1, sizeof text_len, cudaMemcpyDeviceToHost, ctx->stream));
+        if (ctx->precision == RT_F32)
+            CK(launch_resolve_encode<float4>(reinterpret_cast<const float4*>(ctx->accum.p), live_slices(ctx), live_peers(ctx), npix, scale,
+                                             ctx->rgb8.p, ctx->text.p, hdr, ctx->enc_offsets.p, ctx->enc_offsets.p + nb + 2, ctx->stream));
+        else
+            CK(launch_resolve_encode<double4>(reinterpret_cast<const double4*>(ctx->accum.p), live_slices(ctx), live_peers(ctx), npix, scale,
+                                              ctx->rgb8.p, ctx->text.p, hdr, ctx->enc_offsets.p, ctx->enc_offsets.p + nb + 2, ctx->stream));
+        CK(cudaMemcpyAsync(&text_len, ctx->enc_offsets.p + nb + 2, sizeof text_len, cudaMemcpyDeviceToHost, ctx->stream));
+    } else {
+        if (ctx->precision == RT_F32)
+            CK(launch_resolve<float4>(reinterpret_cast<const float4*>(ctx->accum.p), live_slices(ctx), live_peers(ctx), npix, scale,
+                                      sum_rgb ? ctx->sum.p : nullptr, ctx->rgb8.p, nullptr, ctx->stream, no_views, ctx->tiles));
+        else
+            CK(launch_resolve<double4>(reinterpret_cast<const double4*>(ctx->accum.p), live_slices(ctx), live_peers(ctx), npix, scale,
+                                       sum_rgb ? ctx->sum.p : nullptr, ctx->rgb8.p, nullptr, ctx->stream, no_views, ctx->tiles));
+        // tile-sharded frame on the root: the other ranks' resolve kernels store their tiles' bytes straight into this image over
+        // NVLink and bump its counter; the stream waits for all of them here, before the image is encoded or copied
+        if (ctx->tiles.world > 1 && ctx->frame_exported && ctx->tiles_pending) {
+            ctx->frame_target += unsigned(ctx->tiles.world - 1);
+            CK(launch_frame_wait(reinterpret_cast<const unsigned*>(ctx->rgb8.p + frame_counter_offset(npix)), ctx->frame_target, 10000,
+                                 ctx->frame_timeout.p, ctx->stream));
+            ctx->tiles_pending = false; waited = true; ++launches;
+        }
+        if (want_text) {
+            EncodeHeader hdr;
+            hdr.len = std::snprintf(hdr.text, sizeof hdr.text, "P3\n%d %d\n255\n", ctx->W, ctx->H);   // src/camera.h:35
+            const int nb = encode_blocks(npix);
+            CK(ctx->enc_sums.resize(nb + 1)); CK(ctx->enc_offsets.resize(nb + 3));
+            CK(ctx->text.resize(npix * 12 + 64));
+            CK(launch_encode_p3(ctx->rgb8.p, npix, hdr, ctx->enc_sums.p, ctx->enc_offsets.p, ctx->enc_offsets.p + nb + 1, ctx->text.p, ctx->stream));
+            launches += 3;
+            CK(cudaMemcpyAsync(&text_len, ctx->enc_offsets.p + nb + 1, sizeof text_len, cudaMemcpyDeviceToHost, ctx->stream));
+        }
     }
     CK(cudaEventRecord(ctx->ev[3], ctx->stream));
     if (sum_rgb) CK(cudaMemcpyAsync(sum_rgb, ctx->sum.p, npix * 3 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));

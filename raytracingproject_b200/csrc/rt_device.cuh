@@ -49,12 +49,23 @@ template <typename T> __device__ __forceinline__ Vec<T> refract(Vec<T> uv, Vec<T
 // Replaces the global mt19937 of src/rtweekend.h:25-29 (keyed-stream contract):
 // Philox4x32-10, key = seed, counter = (pixel, sample, stage, k >> 2), draw k uses word k & 3,
 // u = (word >> 8) * 2^-24 -- exactly representable in float and double.
-struct Philox {
+// TABLE = true: the ten round keys (key + r * Weyl constant, the same for every block of a launch) come precomputed
+// from the kernel's parameter block -- a constant-bank operand of the XOR, no instruction -- instead of two additions
+// per round: 4 instead of 6 issue slots per round in the render kernels, whose hottest lines these are.
+struct PhiloxKeys { uint32_t k[20]; };     // k[2r], k[2r + 1] = round keys of round r
+inline void philox_round_keys(uint64_t seed, PhiloxKeys& out) {
+    uint32_t k0 = uint32_t(seed), k1 = uint32_t(seed >> 32);
+    for (int r = 0; r < 10; ++r) { out.k[2 * r] = k0; out.k[2 * r + 1] = k1; k0 += 0x9E3779B9u; k1 += 0xBB67AE85u; }
+}
+
+template <bool TABLE> struct PhiloxT {
     uint32_t key0, key1;
+    const uint32_t* rk;
     uint32_t pixel, sample, stage, k;
     uint32_t w0, w1, w2, w3;
 
-    __device__ __forceinline__ void init(uint64_t seed) { key0 = uint32_t(seed); key1 = uint32_t(seed >> 32); k = 0; pixel = sample = stage = 0; }
+    __device__ __forceinline__ void init(uint64_t seed) { key0 = uint32_t(seed); key1 = uint32_t(seed >> 32); rk = nullptr; k = 0; pixel = sample = stage = 0; }
+    __device__ __forceinline__ void init(const PhiloxKeys& keys) { key0 = key1 = 0; rk = keys.k; k = 0; pixel = sample = stage = 0; }
     __device__ __forceinline__ void set(uint32_t px, uint32_t s, uint32_t st) { pixel = px; sample = s; stage = st; k = 0; }
 
     __device__ __forceinline__ void generate(uint32_t block) {
@@ -64,8 +75,8 @@ struct Philox {
         for (int r = 0; r < 10; ++r) {
             const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
             const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
-            c0 = hi1 ^ c1 ^ k0; c1 = lo1; c2 = hi0 ^ c3 ^ k1; c3 = lo0;
-            k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+            if (TABLE) { c0 = hi1 ^ c1 ^ rk[2 * r]; c1 = lo1; c2 = hi0 ^ c3 ^ rk[2 * r + 1]; c3 = lo0; }
+            else { c0 = hi1 ^ c1 ^ k0; c1 = lo1; c2 = hi0 ^ c3 ^ k1; c3 = lo0; k0 += 0x9E3779B9u; k1 += 0xBB67AE85u; }
         }
         w0 = c0; w1 = c1; w2 = c2; w3 = c3;
     }
@@ -79,6 +90,7 @@ struct Philox {
         return w >> 8;
     }
 };
+typedef PhiloxT<false> Philox;
 
 template <typename T> __device__ __forceinline__ T u01(uint32_t m) { return T(m) * T(1.0 / 16777216.0); }   // random_double()
 
@@ -97,7 +109,7 @@ template <typename T> __device__ __forceinline__ bool ball_accept(uint32_t mz, u
     out = mk<T>(T(ax) * T(1.0 / 8388608.0), T(ay) * T(1.0 / 8388608.0), T(az) * T(1.0 / 8388608.0));
     return true;
 }
-template <typename T> __device__ __forceinline__ Vec<T> random_in_unit_sphere(Philox& rng) {
+template <typename T, typename R> __device__ __forceinline__ Vec<T> random_in_unit_sphere(R& rng) {
     for (;;) {
         const uint32_t mz = rng.next24(), my = rng.next24(), mx = rng.next24();
         Vec<T> v;
@@ -110,7 +122,7 @@ template <typename T> __device__ __forceinline__ Vec<T> random_in_unit_sphere(Ph
 // draw site -- the triplets (z, y, x) of iteration i are draws 3i..3i+2, so block b completes one
 // triplet (b % 3 == 0, 1) or two (b % 3 == 2).  Smaller code (the kernels are I-cache bound) and
 // the lanes of a warp stay converged on the expensive part.
-template <typename T> __device__ __forceinline__ Vec<T> random_in_unit_sphere_from0(Philox& rng) {
+template <typename T, typename R> __device__ __forceinline__ Vec<T> random_in_unit_sphere_from0(R& rng) {
     uint32_t c0 = 0, c1 = 0;
     int nc = 0;
     Vec<T> v = mk<T>(T(0), T(0), T(0));
@@ -145,7 +157,7 @@ template <typename T> struct Ray { Vec<T> o, d; T tm; };
 
 // src/camera.h:87-113.  Draw order: px, py (:104-105); disk iterations, first draw -> y,
 // second -> x (src/vec3.h:123 under g++); time (:97).  Stream stage 0.
-template <typename T> __device__ __forceinline__ Ray<T> get_ray(const CameraFrame<T>& c, int i, int j, Philox& rng) {
+template <typename T, typename R> __device__ __forceinline__ Ray<T> get_ray(const CameraFrame<T>& c, int i, int j, R& rng) {
     const Vec<T> pixel_center = (c.pixel00_loc + T(i) * c.pixel_delta_u) + T(j) * c.pixel_delta_v;
     rng.generate(0u);                                   // draws 0..3: px, py, first disk pair (or time)
     const T px = T(-0.5) + u01<T>(rng.w0 >> 8);
@@ -283,12 +295,12 @@ template <typename T> __device__ __forceinline__ T reflectance(T cosine, T ref_i
     return r0 + (T(1) - r0) * ((x2 * x2) * x);
 }
 
-template <typename T> __device__ __forceinline__ bool scatter(int type, Vec<T> albedo, T param, const Vec<T>& d_in, const Vec<T>& n,
-                                                              bool front_face, Philox& rng, Vec<T>& attenuation, Vec<T>& d_out) {
+template <typename T, typename R> __device__ __forceinline__ bool scatter(int type, Vec<T> albedo, T param, const Vec<T>& d_in, const Vec<T>& n,
+                                                                          bool front_face, R& rng, Vec<T>& attenuation, Vec<T>& d_out) {
     if (type < 2) {
         // both opaque materials draw one point in the unit ball first (3k draws, metal even when
         // fuzz == 0, :38); the sampler is instantiated once for the two of them
-        const Vec<T> ball = random_in_unit_sphere_from0<T>(rng);
+        const Vec<T> ball = random_in_unit_sphere_from0<T, R>(rng);
         attenuation = albedo;
         if (type == 0) {                               // lambertian, no near_zero guard (:21)
             d_out = n + unit_vector(ball);

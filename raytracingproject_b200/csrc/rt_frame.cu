@@ -290,6 +290,155 @@ __global__ void __launch_bounds__(ENC_BLOCK) encode_write_kernel(const unsigned 
 
 int encode_blocks(size_t n_pixels) { return int((n_pixels + ENC_TILE - 1) / ENC_TILE); }
 
+// ----------------------------------------------------------- fused resolve + P3 encode --
+// ONE pass from the accumulation buffer to the image AND its P3 text: a block resolves a tile of ENC_TILE pixels
+// (write_color, as resolve_kernel), keeps the bytes in registers, counts the characters of its lines, finds where its
+// text starts with a single-pass prefix sum over the tiles (decoupled look-back: a tile publishes its own total at once
+// and adds up its predecessors' totals until it meets one whose inclusive prefix is known), and writes the lines.
+// Traffic = the accumulation layers read once + 3 B of rgb8 + <= 12 B of text written per pixel; the three-kernel
+// encoder (count / scan / write) read the bytes twice more and paid three launches on a 30 us job.
+// Tiles are numbered by a ticket in the order the blocks START, so a tile only ever waits for tiles that are already running.
+#define LB_AGG 1ull
+#define LB_INC 2ull
+template <typename Q>
+__global__ void __launch_bounds__(ENC_BLOCK) resolve_encode_kernel(const Q* __restrict__ accum, int slices, PeerList peers, size_t n_pixels, double scale,
+                                                                   unsigned char* __restrict__ rgb8, char* __restrict__ text, EncodeHeader hdr,
+                                                                   unsigned* __restrict__ ticket, unsigned long long* __restrict__ tile_state,
+                                                                   unsigned long long* __restrict__ total_len, int n_tiles) {
+    __shared__ unsigned warp_sums[ENC_BLOCK / 32];
+    __shared__ __align__(16) char stage[ENC_TILE * 12 + 16];
+    __shared__ unsigned s_tile;
+    __shared__ unsigned long long s_base;
+    if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
+    __syncthreads();
+    const unsigned tile = s_tile;
+    const size_t p0 = size_t(tile) * ENC_TILE + size_t(threadIdx.x) * ENC_PPT;
+    unsigned char px[12];
+    unsigned len = 0;
+    if (p0 < n_pixels) {
+        const int np = int(min(size_t(4), n_pixels - p0));
+        double s[4][4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) s[k][0] = s[k][1] = s[k][2] = s[k][3] = 0.0;
+        for (int sl = 0; sl < slices; ++sl) {
+            const Q* src = accum + size_t(sl) * n_pixels + p0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) if (k < np) { const Q v = src[k]; s[k][0] += double(v.x); s[k][1] += double(v.y); s[k][2] += double(v.z); s[k][3] += double(v.w); }
+        }
+        for (int p = 0; p < peers.n; ++p) {
+            const Q* base = reinterpret_cast<const Q*>(peers.ptr[p]);
+            for (int sl = 0; sl < peers.slices[p]; ++sl) {
+                const Q* src = base + size_t(sl) * n_pixels + p0;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) if (k < np) { const Q v = src[k]; s[k][0] += double(v.x); s[k][1] += double(v.y); s[k][2] += double(v.z); s[k][3] += double(v.w); }
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if (k < np) {
+                const double sc = scale > 0.0 ? scale : 1.0 / s[k][3];
+                px[3 * k + 0] = write_color_byte(s[k][0], sc);
+                px[3 * k + 1] = write_color_byte(s[k][1], sc);
+                px[3 * k + 2] = write_color_byte(s[k][2], sc);
+                len += line_len(px + 3 * k);
+            } else {
+                px[3 * k] = px[3 * k + 1] = px[3 * k + 2] = 0;
+            }
+        }
+        if (rgb8) {
+            if (np == 4) {
+                unsigned int* dst = reinterpret_cast<unsigned int*>(rgb8 + 3 * p0);
+                dst[0] = px[0] | (px[1] << 8) | (px[2] << 16) | (unsigned(px[3]) << 24);
+                dst[1] = px[4] | (px[5] << 8) | (px[6] << 16) | (unsigned(px[7]) << 24);
+                dst[2] = px[8] | (px[9] << 8) | (px[10] << 16) | (unsigned(px[11]) << 24);
+            } else {
+                for (int k = 0; k < 3 * np; ++k) rgb8[3 * p0 + k] = px[k];
+            }
+        }
+    }
+    unsigned total;
+    const unsigned local = block_exclusive_scan(len, warp_sums, total);
+    // ---- where does this tile's text start: header + the totals of all tiles before it
+    if (threadIdx.x < 32) {
+        const unsigned lane = threadIdx.x;
+        volatile unsigned long long* st = tile_state;
+        if (lane == 0) {
+            if (tile == 0) st[0] = (LB_INC << 62) | (unsigned long long)(hdr.len + total);
+            else st[tile] = (LB_AGG << 62) | (unsigned long long)total;
+        }
+        unsigned long long base = 0;
+        if (tile == 0) base = (unsigned long long)hdr.len;
+        else {
+            unsigned long long run = 0;
+            int look = int(tile) - 1;                                  // the window [look - 31, look], lane 0 nearest
+            for (;;) {
+                const int idx = look - int(lane);
+                unsigned long long v = 0;
+                if (idx >= 0) { do { v = st[idx]; } while ((v >> 62) == 0ull); }
+                else v = LB_INC << 62;                                 // before tile 0: an inclusive prefix of 0
+                const unsigned inc = __ballot_sync(0xffffffffu, (v >> 62) == LB_INC);
+                const unsigned long long val = v & ((1ull << 62) - 1);
+                // add the aggregates of the lanes nearer than the first inclusive prefix, and that prefix itself
+                const int first = inc ? __ffs(inc) - 1 : 32;
+                unsigned long long mine = int(lane) <= first ? val : 0ull;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
+                run += mine;
+                if (inc) break;
+                look -= 32;
+            }
+            base = run;
+            if (lane == 0) { __threadfence(); st[tile] = (LB_INC << 62) | (base + total); }
+        }
+        if (lane == 0) {
+            s_base = base;
+            if (int(tile) == n_tiles - 1) *total_len = base + total;
+        }
+    }
+    __syncthreads();
+    char* dst = text + s_base;
+    const unsigned mis = unsigned(reinterpret_cast<unsigned long long>(dst) & 15ull);
+    unsigned off = mis + local;
+    if (p0 < n_pixels) {
+#pragma unroll
+        for (int k = 0; k < ENC_PPT; ++k) {
+            if (p0 + k >= n_pixels) break;
+            off += put_number(stage + off, px[3 * k + 0]); stage[off++] = ' ';
+            off += put_number(stage + off, px[3 * k + 1]); stage[off++] = ' ';
+            off += put_number(stage + off, px[3 * k + 2]); stage[off++] = '\n';
+        }
+    }
+    __syncthreads();
+    const unsigned begin = mis, end = mis + total;
+    const unsigned c0 = (begin + 15u) >> 4, c1 = end >> 4;
+    char* dst0 = dst - mis;
+    if (c0 < c1) {
+        for (unsigned c = c0 + threadIdx.x; c < c1; c += ENC_BLOCK)
+            reinterpret_cast<uint4*>(dst0)[c] = reinterpret_cast<const uint4*>(stage)[c];
+        for (unsigned i = begin + threadIdx.x; i < c0 * 16u; i += ENC_BLOCK) dst0[i] = stage[i];
+        for (unsigned i = c1 * 16u + threadIdx.x; i < end; i += ENC_BLOCK) dst0[i] = stage[i];
+    } else {
+        for (unsigned i = begin + threadIdx.x; i < end; i += ENC_BLOCK) dst0[i] = stage[i];
+    }
+    if (tile == 0 && threadIdx.x < hdr.len) text[threadIdx.x] = hdr.text[threadIdx.x];
+}
+
+template <typename Q>
+cudaError_t launch_resolve_encode(const Q* accum, int slices, const PeerList& peers, size_t n_pixels, double scale, unsigned char* rgb8,
+                                  char* text, const EncodeHeader& hdr, unsigned long long* tile_state, unsigned long long* total_len, cudaStream_t st) {
+    const int nb = encode_blocks(n_pixels);
+    if (nb <= 0) return cudaSuccess;
+    // tile_state: [nb] look-back words, then the ticket (one 64-bit word)
+    cudaError_t e = cudaMemsetAsync(tile_state, 0, (size_t(nb) + 1) * sizeof(unsigned long long), st);
+    if (e != cudaSuccess) return e;
+    resolve_encode_kernel<Q><<<nb, ENC_BLOCK, 0, st>>>(accum, slices, peers, n_pixels, scale, rgb8, text, hdr,
+                                                       reinterpret_cast<unsigned*>(tile_state + nb), tile_state, total_len, nb);
+    return cudaGetLastError();
+}
+template cudaError_t launch_resolve_encode<float4>(const float4*, int, const PeerList&, size_t, double, unsigned char*, char*, const EncodeHeader&, unsigned long long*, unsigned long long*, cudaStream_t);
+template cudaError_t launch_resolve_encode<double4>(const double4*, int, const PeerList&, size_t, double, unsigned char*, char*, const EncodeHeader&, unsigned long long*, unsigned long long*, cudaStream_t);
+
+
 cudaError_t launch_encode_p3(const unsigned char* rgb8, size_t n_pixels, const EncodeHeader& hdr, unsigned* block_sums,
                              unsigned long long* block_offsets, unsigned long long* total_len, char* text, cudaStream_t st) {
     const int nb = encode_blocks(n_pixels);

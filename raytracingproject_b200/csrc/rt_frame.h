@@ -44,6 +44,11 @@ cudaError_t launch_frame_wait(const unsigned* counter, unsigned target, int time
 template <typename Q> cudaError_t launch_fold(Q* accum, int slices, size_t n_pixels, cudaStream_t st);
 
 int encode_blocks(size_t n_pixels);
+// One pass: accumulation layers (+ peers) -> rgb8 (optional) + P3 text.  tile_state: encode_blocks(n) + 1 64-bit words of
+// scratch, *total_len = length of the text.  Same bytes as launch_resolve + launch_encode_p3.
+template <typename Q>
+cudaError_t launch_resolve_encode(const Q* accum, int slices, const PeerList& peers, size_t n_pixels, double scale, unsigned char* rgb8,
+                                  char* text, const EncodeHeader& hdr, unsigned long long* tile_state, unsigned long long* total_len, cudaStream_t st);
 // rgb8 must be readable up to 12 bytes past its last pixel (32-bit loads of 4-pixel groups)
 cudaError_t launch_encode_p3(const unsigned char* rgb8, size_t n_pixels, const EncodeHeader& hdr, unsigned* block_sums,
                              unsigned long long* block_offsets, unsigned long long* total_len, char* text, cudaStream_t st);

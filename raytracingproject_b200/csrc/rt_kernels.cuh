@@ -335,7 +335,7 @@ __device__ __forceinline__ Ray<T> bench_ray(const CameraFrame<T>& cam, size_t id
     Ray<T> r;
     const T ux = u01<T>(rng.next24()), uy = u01<T>(rng.next24()), uz = u01<T>(rng.next24());
     r.o = mk<T>(T(-12) + T(24) * ux, T(0.05) + T(2.95) * uy, T(-12) + T(24) * uz);
-    r.d = unit_vector(random_in_unit_sphere<T>(rng));
+    r.d = unit_vector(random_in_unit_sphere<T, Philox>(rng));
     r.tm = u01<T>(rng.next24());
     return r;
 }

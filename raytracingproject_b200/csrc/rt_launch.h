@@ -26,6 +26,7 @@ template <typename T> struct RenderParams {
     unsigned int* job_counter;
     unsigned long long* ray_counter;
     uint64_t seed;
+    PhiloxKeys keys;                    // the ten Philox round keys of `seed` (wavefront kernel: constant-bank operands)
     int sample_begin, sample_count, max_depth;
     int slices, tiles_x, tiles_y;
     int job_group;                      // wavefront: jobs fetched at a time = horizontally adjacent tiles of one layer

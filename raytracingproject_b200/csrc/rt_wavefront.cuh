@@ -41,6 +41,14 @@ namespace rt {
 #define RT_RING 2                      // jobs a warp keeps open (2 or 4)
 #endif
 
+#ifndef RT_PHILOX_TABLE
+#define RT_PHILOX_TABLE 0              // 1: Philox round keys precomputed in the parameter block (LDCU into uniform registers) instead of two uniform
+#endif                                 // additions per round -- measured 0.7 % SLOWER on C3 / C4 (profiles/r2_ab_merge_table_top.txt), so off; make TABLE=1
+
+#ifndef RT_MERGE_HITS
+#define RT_MERGE_HITS 1                // HIT stage: opaque and glass hits of a round shaded as one sequence of batches (A/B: make MERGE=0)
+#endif
+
 template <typename T, int P> struct Pool {
     enum { OX, OY, OZ, TM, DX, DY, DZ, TR, TG, TB, TBEST, NF };        // T arrays [P]
     enum { BEST, NI };                                                  // int arrays [P]
@@ -198,7 +206,7 @@ render_pool_kernel(const RenderParams<T> p) {
                     }
                     if (start) {
                         const int s = J.y + sidx;
-                        Philox rng; rng.init(p.seed);
+                        PhiloxT<RT_PHILOX_TABLE != 0> rng; if (RT_PHILOX_TABLE) rng.init(p.keys); else rng.init(p.seed);
                         rng.set(uint32_t(j) * uint32_t(W) + uint32_t(i), uint32_t(s), 0u);
                         const Ray<T> ray = get_ray<T>(p.cam, i, j, rng);
                         F[L::OX * P + pid] = ray.o.x; F[L::OY * P + pid] = ray.o.y; F[L::OZ * P + pid] = ray.o.z; F[L::TM * P + pid] = ray.tm;
@@ -312,7 +320,10 @@ render_pool_kernel(const RenderParams<T> p) {
             __syncwarp();
 
             // ------------------------------------------------------------- CLASSIFY stage
-            // regroup the traced rays by what they hit: opaque | glass | nothing (warp ballot + prefix popcount)
+            // regroup the traced rays by what they hit (warp ballot + prefix popcount): misses go to the END list; hits go to
+            // ONE shading list, opaque ones (lambertian + metal: they share the ball sampler) filled from its front, glass from
+            // its back.  With RT_MERGE_HITS the HIT stage walks that list as one sequence, so the last few opaque hits and the
+            // few glass hits of a round share a batch (and its surface / ray load-store code) instead of taking one batch each.
             for (int b = 0; b < n_q; b += 32) {
                 const int idx = b + lane;
                 int key = -1, pid = 0;
@@ -327,7 +338,7 @@ render_pool_kernel(const RenderParams<T> p) {
                 }
                 const unsigned m0 = __ballot_sync(FULL, key == 0), m1 = __ballot_sync(FULL, key == 1), m2 = __ballot_sync(FULL, key == 2);
                 if (key == 0) B[L::LOPAQUE * P + n_opq + __popc(m0 & lt)] = (unsigned char)pid;
-                if (key == 1) B[L::LGLASS * P + n_gls + __popc(m1 & lt)] = (unsigned char)pid;
+                if (key == 1) B[L::LOPAQUE * P + (P - 1) - n_gls - __popc(m1 & lt)] = (unsigned char)pid;
                 if (key == 2) B[L::LEND * P + n_end + __popc(m2 & lt)] = (unsigned char)pid;     // miss: sky is added in END
                 n_opq += __popc(m0); n_gls += __popc(m1); n_end += __popc(m2);
             }
@@ -336,14 +347,24 @@ render_pool_kernel(const RenderParams<T> p) {
 
             // ------------------------------------------------------------------ HIT stage
             // rec.mat->scatter (src/camera_cpu.h:18-20), opaque hits first, then glass
+#if RT_MERGE_HITS
+            for (int l = 0; l < 1; ++l) {
+                const unsigned char* list = B + L::LOPAQUE * P;
+                const int n = n_opq + n_gls;
+#else
             for (int l = 0; l < 2; ++l) {
-                const unsigned char* list = B + (l ? L::LGLASS : L::LOPAQUE) * P;
+                const unsigned char* list = B + L::LOPAQUE * P;
                 const int n = l ? n_gls : n_opq;
+#endif
                 for (int b = 0; b < n; b += 32) {
                     const int idx = b + lane;
                     bool cont = false, ended = false; int pid = 0;
                     if (idx < n) {
-                        pid = list[idx];
+#if RT_MERGE_HITS
+                        pid = list[idx < n_opq ? idx : (P - 1) - (idx - n_opq)];
+#else
+                        pid = list[l ? (P - 1) - idx : idx];
+#endif
                         const int sw = S[L::SAMPLE * P + pid];
                         const int4 J = ring[sw >> SH];
                         const int i = (J.x & 0xffff) + (pid & 15), j = (J.x >> 16) + (pid >> 4);
@@ -355,7 +376,7 @@ render_pool_kernel(const RenderParams<T> p) {
                         const int slot = I[L::BEST * P + pid], s = J.y + (sw & DONE);
                         int depth = S[L::DEPTH * P + pid];
                         const Surface<T> sf = surface_at<T>(sv, st.sa, st.sb, st.sc, st.meta, ray, t, slot);
-                        Philox rng; rng.init(p.seed);
+                        PhiloxT<RT_PHILOX_TABLE != 0> rng; if (RT_PHILOX_TABLE) rng.init(p.keys); else rng.init(p.seed);
                         rng.set(uint32_t(j) * uint32_t(W) + uint32_t(i), uint32_t(s - 1), uint32_t(p.max_depth - depth + 1));   // b-th hit: stage b
                         Vec<T> att, dnew;
                         if (!scatter<T>(sf.type, sf.albedo, sf.param, ray.d, sf.normal, sf.front_face, rng, att, dnew)) {
