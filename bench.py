@@ -430,6 +430,10 @@ def main():
                     "d2h_bytes_per_step": int(W * H * 3 + (e2e_out["ppm_len"] if e2e_out else 0)),
                     "api": "rt_upload_scene + rt_render + rt_readback(rgb8 + P3 text) per step; scene from host arrays, results into pinned host buffers"},
             "gpu_launches": int(launches) * args.steps, "clocks": clocks,
+            # where a step's time goes (device-resident leg): rank 0's render kernel (CUDA events inside the library) and what
+            # follows it until the frame is resolved on rank 0 -- tiles: wait for the peers' bytes + resolve of rank 0's tiles;
+            # samples: fold + reduce + resolve; N = 1: resolve alone.  (NVTX ranges of the same names: rt_api.cu)
+            "phases_ms": {"render_kernel_rank0": kms, "after_render_until_frame_resolved": ms - kms},
         }
         if check:
             line["image_check"] = check

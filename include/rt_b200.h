@@ -152,6 +152,13 @@ uint32_t    rt_abi_version(void);
 int rt_upload_scene(rt_ctx *ctx, const rt_sphere *spheres, size_t n_spheres,
                     const rt_material *materials, size_t n_materials, const rt_bvh_opts *opts);
 
+/* Next row 8f-4, dynamic scenes: the world of the last rt_upload_scene with its spheres moved -- same count, same order,
+ * other centres / motion vectors (src/sphere.h:19-28) / radii / materials.  The tree keeps its topology and is REFITTED on the
+ * device (every box recomputed bottom-up); no rebuild.  Hits stay exact; the tree's quality ages with the distance moved.
+ * RT_E_STATE when the count changed or a sphere crossed big_radius (the split into tree / outsized spheres is fixed at upload). */
+int rt_update_spheres(rt_ctx *ctx, const rt_sphere *spheres, size_t n_spheres,
+                      const rt_material *materials, size_t n_materials);
+
 /* camera::initialize + the pixel/sample/bounce loops (src/camera.h:37-47, src/camera_cpu.h:8-26).
  * Asynchronous: enqueues on the context's stream. */
 int rt_render(rt_ctx *ctx, const rt_camera *cam, const rt_render_opts *opts);

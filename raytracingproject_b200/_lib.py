@@ -64,6 +64,7 @@ SYMBOLS = {
     "rt_last_error": (C.c_char_p, [_VP]),
     "rt_abi_version": (C.c_uint32, []),
     "rt_upload_scene": (_I, [_VP, _VP, _SZ, _VP, _SZ, _VP]),
+    "rt_update_spheres": (_I, [_VP, _VP, _SZ, _VP, _SZ]),
     "rt_render": (_I, [_VP, _VP, _VP]),
     "rt_readback": (_I, [_VP, _I, _VP, _VP, _VP, _VP]),
     "rt_readback_image": (_I, [_VP, _I, _I, _VP, _VP]),

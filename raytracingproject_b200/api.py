@@ -122,6 +122,13 @@ class Context:
         o = L.BvhOpts(L.ABI, builder, max_leaf, wide, big_radius)
         self._ck(self._lib.rt_upload_scene(self._h, L.ptr(spheres), len(spheres), L.ptr(materials), len(materials), C.byref(o)))
 
+    def update_spheres(self, spheres, materials):
+        """rt_update_spheres: the uploaded world with its spheres moved (same count and order); the tree is refitted on the device."""
+        spheres = np.ascontiguousarray(spheres)
+        materials = np.ascontiguousarray(materials)
+        assert spheres.dtype.itemsize == 64 and materials.dtype.itemsize == 40
+        self._ck(self._lib.rt_update_spheres(self._h, L.ptr(spheres), len(spheres), L.ptr(materials), len(materials)))
+
     def render(self, cam, precision=L.F32, seed=0, variant=L.WAVEFRONT, sample_begin=0, sample_count=0,
                accumulate=False, slices=0, sched=0, tile_rank=0, tile_world=0, top_cap=0):
         o = L.RenderOpts(L.ABI, precision, variant, sample_begin, sample_count, int(accumulate), seed, slices, sched,

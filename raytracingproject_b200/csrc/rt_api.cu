@@ -13,6 +13,8 @@
 #include <string>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>          // header-only: ranges show up in an Nsight Systems timeline, no-ops otherwise
+
 #include "rt_bvh_host.h"
 #include "rt_demo.h"
 #include "rt_frame.h"
@@ -67,6 +69,9 @@ struct rt_ctx {
     int n_spheres = 0, n_slots = 0, n_big = 0, n_nodes = 0, root_ref = RT_SENTINEL, depth = 0;
     DevBuf<float4> nodes, nodes4, sa32, sb32, sc32;   // nodes4: 4-wide records of the same tree (null unless the tree is walked in global memory)
     bool wide = false, wide_forced = false;
+    DevBuf<int> slot_sphere;                      // slot -> index of its sphere in the caller's array (for rt_update_spheres)
+    std::vector<int> big_ids;                     // the spheres kept out of the tree, in list order
+    double big_radius = 100.0;
     int top_ordered = 0;                          // nodes [0, top_ordered) are the first levels of the tree in breadth-first order (rt_scene.cu)
     DevBuf<double4> sa64, sb64, sc64, big_a, big_b, big_c;
     DevBuf<int> meta, big_meta;
@@ -107,6 +112,10 @@ struct rt_ctx {
 };
 
 namespace {
+
+// NVTX range over a scope (tracing).  Names: rt_upload_scene / rt_update_spheres / rt_render (enqueue) /
+// rt_readback (resolve + encode + copies) / rt_fold_slices / rt_resolve_tiles.
+struct NvtxRange { explicit NvtxRange(const char* name) { nvtxRangePushA(name); } ~NvtxRange() { nvtxRangePop(); } };
 
 int fail(rt_ctx* c, int code, const std::string& msg) { if (c) c->err = msg; else g_create_error = msg; return code; }
 int cuda_fail(rt_ctx* c, cudaError_t e, const char* what) {
@@ -289,6 +298,7 @@ int rt_stream(rt_ctx* ctx, void** cuda_stream) {
 // ------------------------------------------------------------------------ scene upload --
 extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_spheres,
                                const rt_material* materials, size_t n_materials, const rt_bvh_opts* opts) {
+    NvtxRange nvtx_("rt_upload_scene");
     if (!ctx) return RT_E_INVALID;
     if (n_spheres && (!spheres || !materials)) return fail(ctx, RT_E_INVALID, "rt_upload_scene: null arrays");
     if (opts && opts->abi != RT_ABI_VERSION) return fail(ctx, RT_E_INVALID, "rt_upload_scene: ABI version mismatch");
@@ -335,6 +345,8 @@ extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_s
         }
     }
     const int n_tree = int(tree_ids.size());
+    ctx->big_ids = big_ids; ctx->big_radius = big_radius;
+    CK(ctx->slot_sphere.resize(std::max(1, n_tree)));
     const size_t nt = std::max(1, n_tree), nb = std::max<size_t>(1, big_ids.size());
     CK(ctx->sa32.resize(nt)); CK(ctx->sb32.resize(nt)); CK(ctx->sc32.resize(nt));
     CK(ctx->sa64.resize(nt)); CK(ctx->sb64.resize(nt)); CK(ctx->sc64.resize(nt)); CK(ctx->meta.resize(nt));
@@ -370,7 +382,7 @@ extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_s
         int root = RT_SENTINEL, depth = 0;
         if (e == cudaSuccess) e = build_lbvh_gpu(d_boxes.p, n_tree, lbvh_leaf, ctx->nodes.p, d_order.p, &root, &depth, ctx->stream);
         if (e == cudaSuccess) e = launch_scene_fill(d_sph.p, d_mat.p, d_ids.p, d_order.p, n_tree, ctx->sa32.p, ctx->sb32.p, ctx->sc32.p,
-                                                    ctx->sa64.p, ctx->sb64.p, ctx->sc64.p, ctx->meta.p, ctx->stream);
+                                                    ctx->sa64.p, ctx->sb64.p, ctx->sc64.p, ctx->meta.p, ctx->stream, ctx->slot_sphere.p);
         if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
         d_sph.release(); d_mat.release(); d_ids.release(); d_boxes.release(); d_order.release();
         if (e != cudaSuccess) return cuda_fail(ctx, e, "rt_upload_scene: device scene build");
@@ -413,6 +425,7 @@ extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_s
             CK(cudaMemcpyAsync(ctx->sb64.p, b64.data(), sizeof(double4) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
             CK(cudaMemcpyAsync(ctx->sc64.p, c64.data(), sizeof(double4) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
             CK(cudaMemcpyAsync(ctx->meta.p, meta.data(), sizeof(int) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
+            CK(cudaMemcpyAsync(ctx->slot_sphere.p, slot_ids.data(), sizeof(int) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
             CK(cudaStreamSynchronize(ctx->stream));               // the staging vectors go out of scope
         }
     }
@@ -464,6 +477,81 @@ extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_s
     ctx->upload_ms = ms_since(t_start);
     ctx->stats.n_spheres = ctx->n_spheres; ctx->stats.n_big = ctx->n_big; ctx->stats.n_nodes = ctx->n_nodes; ctx->stats.big_in_tree = big_in_tree;
     ctx->stats.bvh_depth = ctx->depth; ctx->stats.build_ms = ctx->build_ms; ctx->stats.upload_ms = ctx->upload_ms;
+    return RT_OK;
+}
+
+// ------------------------------------------------------------------------ scene update --
+// SURVEY.md 8f-4, dynamic scenes: the world of the last rt_upload_scene with its spheres MOVED (centres, motion vectors,
+// radii, materials may all change; the count, the order and the split into tree / outsized spheres may not).  The tree keeps
+// its topology and is refitted on the device: new SoA slots, new slot boxes, every node box recomputed bottom-up
+// (rt_scene.cu tree_refit_kernel) -- no sort, no hierarchy pass, no host builder.  Hits stay exact (the boxes are
+// conservative by construction); only the tree's QUALITY ages as spheres drift from where the builder saw them.
+extern "C" int rt_update_spheres(rt_ctx* ctx, const rt_sphere* spheres, size_t n_spheres, const rt_material* materials, size_t n_materials) {
+    NvtxRange nvtx_("rt_update_spheres");
+    if (!ctx) return RT_E_INVALID;
+    if (!ctx->has_scene) return fail(ctx, RT_E_STATE, "rt_update_spheres: no scene uploaded");
+    if (n_spheres != size_t(ctx->n_spheres)) return fail(ctx, RT_E_STATE, "rt_update_spheres: the sphere count changed; use rt_upload_scene");
+    if (n_spheres && (!spheres || !materials)) return fail(ctx, RT_E_INVALID, "rt_update_spheres: null arrays");
+    CK(cudaSetDevice(ctx->device));
+    const auto t_start = std::chrono::steady_clock::now();
+    {
+        size_t k = 0;
+        for (size_t i = 0; i < n_spheres; ++i) {
+            if (spheres[i].material < 0 || size_t(spheres[i].material) >= n_materials)
+                return fail(ctx, RT_E_INVALID, "rt_update_spheres: sphere material index out of range");
+            const int ty = materials[spheres[i].material].type;
+            if (ty < RT_LAMBERTIAN || ty > RT_DIELECTRIC) return fail(ctx, RT_E_INVALID, "rt_update_spheres: unknown material type");
+            const bool was_big = k < ctx->big_ids.size() && ctx->big_ids[k] == int(i);
+            if (was_big) ++k;
+            // (with more than 16 candidates the largest 16 were chosen at upload: a candidate that was in the tree stays there)
+            if (was_big && !(std::fabs(spheres[i].radius) >= ctx->big_radius))
+                return fail(ctx, RT_E_STATE, "rt_update_spheres: an outsized sphere (kept out of the tree) shrank below big_radius; use rt_upload_scene");
+            if (!was_big && std::fabs(spheres[i].radius) >= ctx->big_radius && ctx->big_ids.size() < RT_MAX_BIG)
+                return fail(ctx, RT_E_STATE, "rt_update_spheres: a sphere grew to big_radius (outsized spheres are kept out of the tree); use rt_upload_scene");
+        }
+    }
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->has_scene = false;                                    // until the update has succeeded as a whole
+    const int n_tree = ctx->n_slots;
+    DevBuf<rt_sphere> d_sph; DevBuf<rt_material> d_mat; DevBuf<HostBox> d_boxes; DevBuf<int> d_parent, d_flags;
+    if (n_tree > 0) {
+        CK(d_sph.resize(n_spheres)); CK(d_mat.resize(n_materials)); CK(d_boxes.resize(n_tree));
+        CK(cudaMemcpyAsync(d_sph.p, spheres, sizeof(rt_sphere) * n_spheres, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(d_mat.p, materials, sizeof(rt_material) * n_materials, cudaMemcpyHostToDevice, ctx->stream));
+        CK(launch_scene_fill(d_sph.p, d_mat.p, ctx->slot_sphere.p, nullptr, n_tree, ctx->sa32.p, ctx->sb32.p, ctx->sc32.p,
+                             ctx->sa64.p, ctx->sb64.p, ctx->sc64.p, ctx->meta.p, ctx->stream));
+        if (ctx->n_nodes > 0) {
+            CK(d_parent.resize(ctx->n_nodes)); CK(d_flags.resize(ctx->n_nodes));
+            CK(launch_scene_boxes(d_sph.p, ctx->slot_sphere.p, n_tree, d_boxes.p, ctx->stream));
+            CK(launch_tree_refit(ctx->nodes.p, ctx->n_nodes, d_boxes.p, d_parent.p, d_flags.p, ctx->stream));
+            if (ctx->wide) CK(launch_widen(ctx->nodes.p, ctx->n_nodes, ctx->nodes4.p, ctx->stream));
+        }
+    }
+    if (!ctx->big_ids.empty()) {
+        std::vector<double4> ba(ctx->big_ids.size()), bb(ba.size()), bc(ba.size());
+        std::vector<int> bmeta(ba.size());
+        for (size_t k = 0; k < ba.size(); ++k) {
+            const rt_sphere& sp = spheres[ctx->big_ids[k]];
+            const rt_material& mt = materials[sp.material];
+            const bool mov = sp.is_moving != 0;
+            ba[k] = make_double4(sp.center1[0], sp.center1[1], sp.center1[2], sp.radius);
+            bb[k] = make_double4(mov ? sp.center_vec[0] : 0.0, mov ? sp.center_vec[1] : 0.0, mov ? sp.center_vec[2] : 0.0, sp.radius * sp.radius);
+            double param = mt.param;
+            if (mt.type == RT_METAL) param = param < 1 ? param : 1;             // src/material.h:33
+            bc[k] = make_double4(mt.albedo[0], mt.albedo[1], mt.albedo[2], param);
+            bmeta[k] = (ctx->big_ids[k] << 3) | (mov ? 4 : 0) | mt.type;
+        }
+        CK(cudaMemcpyAsync(ctx->big_a.p, ba.data(), sizeof(double4) * ba.size(), cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(ctx->big_b.p, bb.data(), sizeof(double4) * bb.size(), cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(ctx->big_c.p, bc.data(), sizeof(double4) * bc.size(), cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(ctx->big_meta.p, bmeta.data(), sizeof(int) * bmeta.size(), cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+    }
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->has_scene = true;
+    ctx->upload_ms = ms_since(t_start);
+    ctx->build_ms = 0.0;
+    ctx->stats.upload_ms = ctx->upload_ms; ctx->stats.build_ms = 0.0;
     return RT_OK;
 }
 
@@ -580,6 +668,7 @@ int render_impl(rt_ctx* ctx, const rt_camera& cam, const rt_render_opts& o, int 
 }  // namespace
 
 extern "C" int rt_render(rt_ctx* ctx, const rt_camera* cam, const rt_render_opts* opts) {
+    NvtxRange nvtx_("rt_render");
     if (!ctx || !cam || !opts) return RT_E_INVALID;
     if (opts->abi != RT_ABI_VERSION) return fail(ctx, RT_E_INVALID, "rt_render: ABI version mismatch");
     if (!ctx->has_scene) return fail(ctx, RT_E_STATE, "rt_render: no scene uploaded");
@@ -660,6 +749,7 @@ extern "C" int rt_render(rt_ctx* ctx, const rt_camera* cam, const rt_render_opts
 }
 
 extern "C" int rt_readback(rt_ctx* ctx, int spp_total, double* sum_rgb, uint8_t* rgb8, char* ppm, size_t* ppm_len) {
+    NvtxRange nvtx_("rt_readback");
     if (!ctx) return RT_E_INVALID;
     if (ctx->W == 0 || !ctx->accum.p) return fail(ctx, RT_E_STATE, "rt_readback: nothing rendered");
     if (ppm && !ppm_len) return fail(ctx, RT_E_INVALID, "rt_readback: ppm needs ppm_len");
@@ -839,6 +929,7 @@ extern "C" int rt_plan_layers(int sample_count, long long tiles, long long resid
 }
 
 extern "C" int rt_fold_slices(rt_ctx* ctx) {
+    NvtxRange nvtx_("rt_fold_slices");
     if (!ctx) return RT_E_INVALID;
     if (!ctx->accum.p) return fail(ctx, RT_E_STATE, "rt_fold_slices: nothing rendered");
     CK(cudaSetDevice(ctx->device));
@@ -940,6 +1031,7 @@ extern "C" int rt_frame_open(rt_ctx* ctx, const void* handle) {
 }
 
 extern "C" int rt_resolve_tiles(rt_ctx* ctx, int spp_total) {
+    NvtxRange nvtx_("rt_resolve_tiles");
     if (!ctx) return RT_E_INVALID;
     if (ctx->W == 0 || !ctx->accum.p) return fail(ctx, RT_E_STATE, "rt_resolve_tiles: nothing rendered");
     if (ctx->tiles.world <= 1) return fail(ctx, RT_E_STATE, "rt_resolve_tiles: the last render was not tile-sharded");

@@ -31,10 +31,11 @@ __global__ void __launch_bounds__(256) scene_fill_kernel(const rt_sphere* __rest
                                                          const int* __restrict__ ids, const int* __restrict__ order, int n,
                                                          float4* __restrict__ a32, float4* __restrict__ b32, float4* __restrict__ c32,
                                                          double4* __restrict__ a64, double4* __restrict__ b64, double4* __restrict__ c64,
-                                                         int* __restrict__ meta) {
+                                                         int* __restrict__ meta, int* __restrict__ slot_sphere) {
     const int slot = blockIdx.x * blockDim.x + threadIdx.x;
     if (slot >= n) return;
-    const int id = ids[order[slot]];
+    const int id = ids[order ? order[slot] : slot];
+    if (slot_sphere) slot_sphere[slot] = id;
     const rt_sphere s = spheres[id];
     const rt_material mt = materials[s.material];
     const bool mov = s.is_moving != 0;
@@ -179,6 +180,67 @@ __global__ void __launch_bounds__(256) top_permute_kernel(const float4* __restri
     o[0] = q0; o[1] = q1; o[2] = q2; o[3] = q3;
 }
 
+// ---- refit: new boxes for an unchanged tree (dynamic scenes) ----
+// The spheres of a scene move (other centres, other motion vectors, other radii) but keep their slots: the tree's TOPOLOGY
+// stays, every box is recomputed bottom-up.  Works on the final node array of either builder, whatever its numbering:
+//   tree_parents_kernel  parent[c] = 2 * node + side for every inner child c (the root keeps -1)
+//   tree_refit_kernel    one thread per node: boxes of its LEAF children from the new slot boxes; the thread that completes
+//                        a node (second arrival, atomic counter) unites its two child boxes into the parent's record and
+//                        climbs.  Boxes other threads wrote are read with ld.cg (L2): an L1 line may hold a stale copy.
+__global__ void __launch_bounds__(256) tree_parents_kernel(const float4* __restrict__ nodes, int n_nodes, int* __restrict__ parent) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_nodes) return;
+    const float4 q3 = nodes[4 * size_t(i) + 3];
+    const int cl = __float_as_int(q3.x), cr = __float_as_int(q3.y);
+    if (cl >= 0) parent[cl] = 2 * i;
+    if (cr >= 0) parent[cr] = 2 * i + 1;
+}
+
+__device__ __forceinline__ void store_child_box(float4* nodes, int node, int side, const float lo[3], const float hi[3]) {
+    float* rec = reinterpret_cast<float*>(nodes + 4 * size_t(node));
+    reinterpret_cast<float4*>(rec)[side] = make_float4(lo[0], lo[1], hi[0], hi[1]);      // q0 (left) / q1 (right)
+    rec[8 + side] = lo[2];                                                                   // q2 = (Lmin.z, Rmin.z, Lmax.z, Rmax.z)
+    rec[10 + side] = hi[2];
+}
+
+__global__ void __launch_bounds__(256) tree_refit_kernel(float4* nodes, int n_nodes, const int* __restrict__ parent, int* flags,
+                                                         const HostBox* __restrict__ slot_boxes) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_nodes) return;
+    const float4 q3 = __ldcg(nodes + 4 * size_t(i) + 3);
+    const int c[2] = { __float_as_int(q3.x), __float_as_int(q3.y) };
+    int nleaf = 0;
+#pragma unroll
+    for (int side = 0; side < 2; ++side) {
+        if (c[side] >= 0) continue;
+        const int leaf = ~c[side], first = leaf >> 3, count = (leaf & 7) + 1;
+        float lo[3] = { INFINITY, INFINITY, INFINITY }, hi[3] = { -INFINITY, -INFINITY, -INFINITY };
+        for (int k = 0; k < count; ++k) {
+            const HostBox b = slot_boxes[first + k];
+#pragma unroll
+            for (int a = 0; a < 3; ++a) { lo[a] = fminf(lo[a], b.lo[a]); hi[a] = fmaxf(hi[a], b.hi[a]); }
+        }
+        store_child_box(nodes, i, side, lo, hi);
+        ++nleaf;
+    }
+    if (nleaf == 0) return;
+    __threadfence();
+    int node = i;
+    int arrived = atomicAdd(&flags[node], nleaf) + nleaf;
+    while (arrived == 2) {                                      // both subtrees of `node` are done: its box goes up
+        __threadfence();
+        const int p = parent[node];
+        if (p < 0) break;                                       // the root
+        const float4 q0 = __ldcg(nodes + 4 * size_t(node) + 0), q1 = __ldcg(nodes + 4 * size_t(node) + 1), q2 = __ldcg(nodes + 4 * size_t(node) + 2);
+        const float lo[3] = { fminf(q0.x, q1.x), fminf(q0.y, q1.y), fminf(q2.x, q2.y) };
+        const float hi[3] = { fmaxf(q0.z, q1.z), fmaxf(q0.w, q1.w), fmaxf(q2.z, q2.w) };
+        store_child_box(nodes, p >> 1, p & 1, lo, hi);
+        __threadfence();
+        node = p >> 1;
+        arrived = atomicAdd(&flags[node], 1) + 1;
+    }
+}
+
 }  // namespace
 
 cudaError_t launch_top_first(const float4* nodes, int n_nodes, int root_ref, int k, int* newpos, int* top_ids, float4* nodes_out, cudaStream_t st) {
@@ -204,9 +266,20 @@ cudaError_t launch_scene_boxes(const rt_sphere* spheres, const int* ids, int n, 
 }
 
 cudaError_t launch_scene_fill(const rt_sphere* spheres, const rt_material* materials, const int* ids, const int* order, int n,
-                              float4* a32, float4* b32, float4* c32, double4* a64, double4* b64, double4* c64, int* meta, cudaStream_t st) {
+                              float4* a32, float4* b32, float4* c32, double4* a64, double4* b64, double4* c64, int* meta, cudaStream_t st,
+                              int* slot_sphere) {
     if (n <= 0) return cudaSuccess;
-    scene_fill_kernel<<<(n + 255) / 256, 256, 0, st>>>(spheres, materials, ids, order, n, a32, b32, c32, a64, b64, c64, meta);
+    scene_fill_kernel<<<(n + 255) / 256, 256, 0, st>>>(spheres, materials, ids, order, n, a32, b32, c32, a64, b64, c64, meta, slot_sphere);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_tree_refit(float4* nodes, int n_nodes, const HostBox* slot_boxes, int* parent, int* flags, cudaStream_t st) {
+    if (n_nodes <= 0) return cudaSuccess;
+    cudaError_t e = cudaMemsetAsync(parent, 0xff, sizeof(int) * size_t(n_nodes), st);
+    if (e == cudaSuccess) e = cudaMemsetAsync(flags, 0, sizeof(int) * size_t(n_nodes), st);
+    if (e != cudaSuccess) return e;
+    tree_parents_kernel<<<(n_nodes + 255) / 256, 256, 0, st>>>(nodes, n_nodes, parent);
+    tree_refit_kernel<<<(n_nodes + 255) / 256, 256, 0, st>>>(nodes, n_nodes, parent, flags, slot_boxes);
     return cudaGetLastError();
 }
 

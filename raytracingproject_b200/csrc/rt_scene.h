@@ -16,7 +16,12 @@ cudaError_t launch_scene_boxes(const rt_sphere* spheres, const int* ids, int n, 
 // float, meta = list_index << 3 | moving << 2 | material tag -- the same values the host fill of rt_upload_scene writes
 cudaError_t launch_scene_fill(const rt_sphere* spheres, const rt_material* materials, const int* ids, const int* order, int n,
                               float4* a32, float4* b32, float4* c32, double4* a64, double4* b64, double4* c64, int* meta,
-                              cudaStream_t st);
+                              cudaStream_t st, int* slot_sphere = nullptr);
+// (order == nullptr: slot s holds sphere ids[s]; slot_sphere, optional: receives the sphere index of every slot)
+
+// Refit (dynamic scenes): every box of the tree recomputed bottom-up from new per-slot boxes, topology unchanged.
+// parent and flags: n_nodes ints of scratch each.
+cudaError_t launch_tree_refit(float4* nodes, int n_nodes, const HostBox* slot_boxes, int* parent, int* flags, cudaStream_t st);
 
 // Renumbers the inner nodes so that the first min(k, n_nodes, RT_TOP_MAX) of them in breadth-first order from the
 // root become indices 0, 1, 2, ... (the root becomes node 0): nodes_out = the permuted records with renamed child refs.

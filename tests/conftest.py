@@ -44,8 +44,10 @@ def ctx(rt):
     c.close()
 
 
-@pytest.fixture(scope="session")
+@pytest.fixture
 def ctx_scene(ctx, scene, rt):
+    """the session's context with the final scene (reference src/main.cpp:11-53) uploaded -- again for every test that asks
+    for it, because other tests upload other worlds into the same context"""
     s, m = scene
     ctx.upload_scene(s.view(rt.SPHERE), m.view(rt.MATERIAL))
     return ctx

@@ -27,9 +27,12 @@ ctx = rt.Context(0)
 for name, spp in cfgs:
     g, pd, pm, W, b = SC[name]
     s, m = rt.scene_rtiow(g, pd, pm)
-    ctx.upload_scene(s, m, builder=rt.BVH_LBVH_GPU if b == "lbvh" else rt.BVH_SAH_HOST)
-    cam = rt.camera_rtiow(W, spp, 50, scale=g / 11.0)
     kw = json.loads(os.environ.get("AB_RENDER_KW", "{}"))
+    ukw = {k[2:]: v for k, v in kw.items() if k.startswith("u_")}            # u_max_leaf etc.: upload_scene keywords
+    kw = {k: v for k, v in kw.items() if not k.startswith("u_")}
+    if "builder" in ukw: b = ukw.pop("builder")
+    ctx.upload_scene(s, m, builder=rt.BVH_LBVH_GPU if b == "lbvh" else rt.BVH_SAH_HOST, **ukw)
+    cam = rt.camera_rtiow(W, spp, 50, scale=g / 11.0)
     ts = []
     for r in range(reps + 1):
         ctx.render(cam, precision=rt.F32, seed=0, variant=rt.WAVEFRONT, **kw)

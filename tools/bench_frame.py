@@ -1,8 +1,10 @@
 """Framebuffer passes (the only HBM-bound part of the path) against the measured HBM
 bandwidth: python tools/bench_frame.py   -> one JSON line per (image, slices, pass)
 
-  resolve : reads slices x W x H x 16 B (float4 sums), writes 3 B per pixel           (resolve_kernel)
-  encode  : reads the 3 B per pixel twice (count, write), writes the P3 text (<= 12 B) (encode_*_kernel)
+  resolve        : reads slices x W x H x 16 B (float4 sums), writes 3 B per pixel           (resolve_kernel)
+  resolve+encode : the same + the P3 text (<= 12 B per pixel) written, ONE kernel              (resolve_encode_kernel, round 2)
+  with RT_NO_FUSED_ENCODE=1 in the environment the text comes from the round-1 three-kernel encoder instead
+  (encode_count / scan / write: the 3 B per pixel read twice more), reported as pass "encode_p3"
 
 Times are rt_stats.resolve_ms (CUDA events on the context's stream around the passes), best of `reps`, with a
 256 MB write between repetitions so that nothing is served from the 126 MB L2."""
@@ -41,7 +43,10 @@ for width, slices in ((1920, 1), (1920, 8), (3840, 1), (3840, 4), (3840, 8)):
     t_enc = max(t_all - t_res, 1e-6)
     b_res = W * H * (16 * sl + 3)
     b_enc = W * H * 3 * 2 + text
-    for name, ms, nbytes in (("resolve", t_res, b_res), ("encode_p3", t_enc, b_enc)):
+    fused = not os.environ.get("RT_NO_FUSED_ENCODE")
+    rows = (("resolve", t_res, b_res), ("resolve+encode_p3 (one kernel)", t_all, b_res + text)) if fused else \
+           (("resolve", t_res, b_res), ("encode_p3", t_enc, b_enc), ("resolve+encode_p3 (four kernels)", t_all, b_res + text))
+    for name, ms, nbytes in rows:
         gbs = nbytes / ms / 1e6
         print(json.dumps({"pass": name, "image": f"{W}x{H}", "slices": sl, "ms": round(ms, 4), "algorithmic_bytes": nbytes,
                           "gb_per_s": round(gbs, 1), "hbm_peak_gb_per_s": peak, "frac": round(gbs / peak, 3)}), flush=True)
