@@ -225,9 +225,10 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--precision", default="f32", choices=["f32", "f64"])
     ap.add_argument("--combine", default="nccl", choices=["nccl", "ipc"], help="--shard samples: how the partial buffers are combined")
-    ap.add_argument("--shard", default="tiles", choices=["tiles", "samples"],
+    ap.add_argument("--shard", default="auto", choices=["auto", "tiles", "samples"],
                     help="N > 1: tile-interleaved shards (every rank writes its tiles' bytes into rank 0's image over NVLink) or "
-                         "sample-range shards (fold + reduce of float partial buffers)")
+                         "sample-range shards (fold + reduce of float partial buffers).  auto: tiles when every rank still owns at "
+                         "least twice as many tiles as it runs warps (4K frames), else samples (profiles/r2_tile_sharding_1gpu_diag.txt)")
     ap.add_argument("--variant", default="wavefront", choices=["wavefront", "megakernel", "lockstep"])
     ap.add_argument("--config", default="c3", choices=sorted(CONFIGS) + ["c2"], help="BASELINE.json config (default c3 = the headline one)")
     ap.add_argument("--spp", type=int, default=0, help="override spp (a non-default value is NOT the named config)")
@@ -282,7 +283,10 @@ def main():
         torch.cuda.synchronize()
 
     # warm-up render so buffers exist, then set up the combine
-    tiles = world > 1 and args.shard == "tiles" and args.variant == "wavefront"
+    n_tiles = ((W + 15) // 16) * ((H + 7) // 8)                          # 16 x 8 pixel tiles of the wavefront kernel's 128-path pools
+    resident_warps = torch.cuda.get_device_properties(local).multi_processor_count * 24
+    want_tiles = args.shard == "tiles" or (args.shard == "auto" and n_tiles // max(1, world) >= 2 * resident_warps)
+    tiles = world > 1 and want_tiles and args.variant == "wavefront"
     if tiles:
         ctx.render(cam, precision=prec, seed=0, tile_rank=rank, tile_world=world)
         ctx.synchronize()

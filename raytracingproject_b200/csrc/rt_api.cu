@@ -117,6 +117,9 @@ namespace {
 // rt_readback (resolve + encode + copies) / rt_fold_slices / rt_resolve_tiles.
 struct NvtxRange { explicit NvtxRange(const char* name) { nvtxRangePushA(name); } ~NvtxRange() { nvtxRangePop(); } };
 
+// A/B knobs read from the environment (set and not "0")
+bool env_on(const char* name) { const char* e = std::getenv(name); return e && *e && *e != '0'; }
+
 int fail(rt_ctx* c, int code, const std::string& msg) { if (c) c->err = msg; else g_create_error = msg; return code; }
 int cuda_fail(rt_ctx* c, cudaError_t e, const char* what) {
     return fail(c, RT_E_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
@@ -444,7 +447,7 @@ extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_s
     // top of the tree first: nodes 0 .. k-1 = the first levels in breadth-first order, so that a render whose scene stays in
     // global memory can keep them in shared memory (north_star item 2).  Parity is defined on hits, not on node numbers.
     ctx->top_ordered = 0;
-    if (ctx->n_nodes > 1 && ctx->root_ref >= 0 && !std::getenv("RT_NO_TOP_FIRST")) {       // (the env knob is for A/B measurements)
+    if (ctx->n_nodes > 1 && ctx->root_ref >= 0 && !env_on("RT_NO_TOP_FIRST")) {       // (the env knob is for A/B measurements)
         DevBuf<int> newpos, top_ids; DevBuf<float4> permuted;
         CK(newpos.resize(ctx->n_nodes)); CK(top_ids.resize(RT_TOP_MAX)); CK(permuted.resize(size_t(ctx->n_nodes) * 4));
         CK(launch_top_first(ctx->nodes.p, ctx->n_nodes, ctx->root_ref, RT_TOP_MAX, newpos.p, top_ids.p, permuted.p, ctx->stream));
@@ -764,7 +767,7 @@ extern "C" int rt_readback(rt_ctx* ctx, int spp_total, double* sum_rgb, uint8_t*
     const FrameViews no_views{nullptr, nullptr, 0, 0};
     const bool want_text = ppm || (ppm_len && !ppm);
     // whole frame on this GPU, text wanted, no per-pixel sums: ONE kernel from the accumulation layers to rgb8 + P3 text
-    const bool fused = want_text && !sum_rgb && ctx->tiles.world <= 1 && !std::getenv("RT_NO_FUSED_ENCODE");
+    const bool fused = want_text && !sum_rgb && ctx->tiles.world <= 1 && !env_on("RT_NO_FUSED_ENCODE");
     unsigned long long text_len = 0;
     bool waited = false;
     if (fused) {

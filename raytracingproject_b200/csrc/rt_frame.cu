@@ -5,6 +5,8 @@
 // and the header of src/camera.h:35.  Arithmetic is double as in the reference.
 #include "rt_frame.h"
 
+#include <cstdlib>
+
 namespace rt {
 
 __device__ __forceinline__ unsigned char write_color_byte(double sum, double scale) {
@@ -17,16 +19,19 @@ __device__ __forceinline__ unsigned char write_color_byte(double sum, double sca
 
 // The same byte without the double-precision square root on the common path.  The passes are HBM-bound on paper, but at
 // one sample layer the three IEEE double square roots per pixel (a ~30-instruction DFMA sequence each) cost more than
-// the memory traffic (measured: 54 of 78 us at 4K).  Here the root is taken in float and trusted only where it cannot
-// decide wrongly: y = 256 * sqrtf(float(v)) carries a relative error below 2e-7 (one rounding of v, one of the root, one
-// of the product), i.e. less than 6e-5 absolute, so unless y lies within 2.5e-4 of an integer its integer part is the
-// reference's; the few channels that do (0.05 %, plus NaN / negative input and exact zeros) take write_color_byte.
-// The clamp to 0.999 only matters through its byte, 255 = int(255.744).
-__device__ __forceinline__ unsigned char write_color_byte_fast(double sum, double scale) {
-    const float y = 256.0f * sqrtf(float(sum * scale));
-    if (!(fabsf(y - rintf(y)) >= 2.5e-4f)) return write_color_byte(sum, scale);      // near a byte boundary, or NaN
+// the memory traffic (measured: 54 of 78 us at 4K).  Here the root is taken in float by the special-function unit
+// (sqrt.approx: 2 ulp) and trusted only where it cannot decide wrongly: y = 256 * sqrt(float(v)) carries a relative error
+// below 4e-7 (one rounding of v, the approximate root), i.e. less than 1e-4 absolute, so unless y lies within 5e-4 of an
+// integer its integer part is the reference's; the few channels that do (0.1 %, plus NaN / negative input and exact zeros)
+// take write_color_byte.  The clamp to 0.999 only matters through its byte, 255 = int(255.744).
+__device__ __forceinline__ float sqrt_approx(float x) { float r; asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ unsigned char write_color_byte_fast(double sum, double scale, bool exact) {
+    const float y = 256.0f * sqrt_approx(float(sum * scale));
+    if (exact || !(fabsf(y - rintf(y)) >= 5e-4f)) return write_color_byte(sum, scale);      // near a byte boundary, or NaN
     return (unsigned char)min(int(y), 255);
 }
+// RT_EXACT_WRITE_COLOR=1 in the environment: every channel through the double path (same-box A/B of the above)
+static bool frame_exact() { const char* e = std::getenv("RT_EXACT_WRITE_COLOR"); static const bool v = e && *e && *e != '0'; return v; }
 
 // One thread = 4 consecutive pixels: 4 x Quad loads per slice/peer (64 or 128 contiguous bytes),
 // 3 x 32-bit stores of packed rgb.  Slices and peers are summed in a fixed order, so the image is
@@ -75,9 +80,9 @@ __global__ void resolve_kernel(const Q* __restrict__ accum, int slices, PeerList
     for (int k = 0; k < 4; ++k) {
         if (k < np && mine[k]) {
             const double sc = scale > 0.0 ? scale : 1.0 / s[k][3];       // spp_total = 0: samples actually accumulated
-            b[3 * k + 0] = write_color_byte_fast(s[k][0], sc);
-            b[3 * k + 1] = write_color_byte_fast(s[k][1], sc);
-            b[3 * k + 2] = write_color_byte_fast(s[k][2], sc);
+            b[3 * k + 0] = write_color_byte_fast(s[k][0], sc, views.exact != 0);
+            b[3 * k + 1] = write_color_byte_fast(s[k][1], sc, views.exact != 0);
+            b[3 * k + 2] = write_color_byte_fast(s[k][2], sc, views.exact != 0);
             if (sum_out) { sum_out[3 * (g + k) + 0] = s[k][0]; sum_out[3 * (g + k) + 1] = s[k][1]; sum_out[3 * (g + k) + 2] = s[k][2]; }
             if (views.pfm) {
                 const size_t y = (g + k) / size_t(views.width), x = (g + k) - y * size_t(views.width);
@@ -110,7 +115,9 @@ cudaError_t launch_resolve(const Q* accum, int slices, const PeerList& peers, si
                            double* sum_out, unsigned char* rgb8, Q* reduced_out, cudaStream_t st, const FrameViews& views, const TileOwner& owner) {
     if (n_pixels == 0) return cudaSuccess;
     const size_t threads = (n_pixels + 3) / 4;
-    resolve_kernel<Q><<<unsigned((threads + 255) / 256), 256, 0, st>>>(accum, slices, peers, n_pixels, scale, sum_out, rgb8, reduced_out, views, owner);
+    FrameViews v = views;
+    v.exact = frame_exact();
+    resolve_kernel<Q><<<unsigned((threads + 255) / 256), 256, 0, st>>>(accum, slices, peers, n_pixels, scale, sum_out, rgb8, reduced_out, v, owner);
     return cudaGetLastError();
 }
 template cudaError_t launch_resolve<float4>(const float4*, int, const PeerList&, size_t, double, double*, unsigned char*, float4*, cudaStream_t, const FrameViews&, const TileOwner&);
@@ -317,7 +324,7 @@ template <typename Q>
 __global__ void __launch_bounds__(ENC_BLOCK) resolve_encode_kernel(const Q* __restrict__ accum, int slices, PeerList peers, size_t n_pixels, double scale,
                                                                    unsigned char* __restrict__ rgb8, char* __restrict__ text, EncodeHeader hdr,
                                                                    unsigned* __restrict__ ticket, unsigned long long* __restrict__ tile_state,
-                                                                   unsigned long long* __restrict__ total_len, int n_tiles) {
+                                                                   unsigned long long* __restrict__ total_len, int n_tiles, bool exact) {
     __shared__ unsigned warp_sums[ENC_BLOCK / 32];
     __shared__ __align__(16) char stage[ENC_TILE * 12 + 16];
     __shared__ unsigned s_tile;
@@ -350,9 +357,9 @@ __global__ void __launch_bounds__(ENC_BLOCK) resolve_encode_kernel(const Q* __re
         for (int k = 0; k < 4; ++k) {
             if (k < np) {
                 const double sc = scale > 0.0 ? scale : 1.0 / s[k][3];
-                px[3 * k + 0] = write_color_byte_fast(s[k][0], sc);
-                px[3 * k + 1] = write_color_byte_fast(s[k][1], sc);
-                px[3 * k + 2] = write_color_byte_fast(s[k][2], sc);
+                px[3 * k + 0] = write_color_byte_fast(s[k][0], sc, exact);
+                px[3 * k + 1] = write_color_byte_fast(s[k][1], sc, exact);
+                px[3 * k + 2] = write_color_byte_fast(s[k][2], sc, exact);
                 len += line_len(px + 3 * k);
             } else {
                 px[3 * k] = px[3 * k + 1] = px[3 * k + 2] = 0;
@@ -445,7 +452,7 @@ cudaError_t launch_resolve_encode(const Q* accum, int slices, const PeerList& pe
     cudaError_t e = cudaMemsetAsync(tile_state, 0, (size_t(nb) + 1) * sizeof(unsigned long long), st);
     if (e != cudaSuccess) return e;
     resolve_encode_kernel<Q><<<nb, ENC_BLOCK, 0, st>>>(accum, slices, peers, n_pixels, scale, rgb8, text, hdr,
-                                                       reinterpret_cast<unsigned*>(tile_state + nb), tile_state, total_len, nb);
+                                                       reinterpret_cast<unsigned*>(tile_state + nb), tile_state, total_len, nb, frame_exact());
     return cudaGetLastError();
 }
 template cudaError_t launch_resolve_encode<float4>(const float4*, int, const PeerList&, size_t, double, unsigned char*, char*, const EncodeHeader&, unsigned long long*, unsigned long long*, cudaStream_t);

@@ -20,7 +20,7 @@ struct EncodeHeader { int len; char text[48]; };     // "P3\n<W> <H>\n255\n" (sr
 // optional extra views of the resolved frame, written by the same pass:
 //   pfm    3 floats per pixel, the mean radiance (sum / spp, before gamma), rows bottom-to-top as a PFM file stores them
 //   rgba8  the write_color bytes + alpha 255, 4 bytes per pixel: the headless stand-in for a presentable image
-struct FrameViews { float* pfm; uchar4* rgba8; int width, height; };
+struct FrameViews { float* pfm; uchar4* rgba8; int width, height; int exact = 0; };     // exact: set by launch_resolve (A/B knob)
 
 // tile-interleaved sharding: the resolve pass of a rank touches only the pixels of the tile groups it
 // rendered -- (tile / group) % world == rank, tiles of tile_w x tile_h pixels, tiles_x per row of an image `width` wide.

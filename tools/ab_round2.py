@@ -31,6 +31,7 @@ for name, spp in cfgs:
     ukw = {k[2:]: v for k, v in kw.items() if k.startswith("u_")}            # u_max_leaf etc.: upload_scene keywords
     kw = {k: v for k, v in kw.items() if not k.startswith("u_")}
     if "builder" in ukw: b = ukw.pop("builder")
+    if "width" in kw: W = kw.pop("width")
     ctx.upload_scene(s, m, builder=rt.BVH_LBVH_GPU if b == "lbvh" else rt.BVH_SAH_HOST, **ukw)
     cam = rt.camera_rtiow(W, spp, 50, scale=g / 11.0)
     ts = []
