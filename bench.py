@@ -326,10 +326,13 @@ def main():
                 return {"ppm_len": ctx.readback_into(args.spp, pin_rgb8, pin_ppm)}
             return ctx.readback(args.spp, want_sum=False, want_rgb8=False)   # resolve on device, nothing copied
 
+    rank_kernel_ms = []
+
     def timed(e2e, steps, warmup):
         for _ in range(warmup):
             step(e2e)
         times, rays, kernel_ms = [], 0, []
+        rank_kernel_ms.clear()
         sampler = ClockSampler(local)
         if rank == 0:
             sampler.start()
@@ -355,10 +358,15 @@ def main():
                 dist.all_reduce(t, op=dist.ReduceOp.MAX)
                 dist.all_reduce(r, op=dist.ReduceOp.SUM)
             times.append(t.item()); rays = int(r.item()); kernel_ms.append(st["render_ms"])
+            if world > 1:                                            # every rank's render kernel time: the skew the combine has to wait out
+                k = torch.zeros(world, dtype=torch.float64, device="cuda"); k[rank] = st["render_ms"]
+                dist.all_reduce(k)
+                rank_kernel_ms.append([round(x, 3) for x in k.tolist()])
         clocks = sampler.stop() if rank == 0 else None
         return times, rays, kernel_ms, clocks, out
 
     times, rays, kernel_ms, clocks, _ = timed(False, args.steps, args.warmup)
+    rank_kernels = [list(x) for x in rank_kernel_ms]
     e2e_times, _, _, _, e2e_out = timed(True, max(2, min(args.steps, 3)), 1)
     launches = ctx.stats()["kernel_launches"]
 
@@ -437,7 +445,9 @@ def main():
             # where a step's time goes (device-resident leg): rank 0's render kernel (CUDA events inside the library) and what
             # follows it until the frame is resolved on rank 0 -- tiles: wait for the peers' bytes + resolve of rank 0's tiles;
             # samples: fold + reduce + resolve; N = 1: resolve alone.  (NVTX ranges of the same names: rt_api.cu)
-            "phases_ms": {"render_kernel_rank0": kms, "after_render_until_frame_resolved": ms - kms},
+            "phases_ms": {"render_kernel_rank0": kms, "after_render_until_frame_resolved": ms - kms,
+                          "render_kernel_every_rank_last_step": rank_kernels[-1] if rank_kernels else None,
+                          "render_kernel_slowest_rank_mean": (sum(max(x) for x in rank_kernels) / len(rank_kernels)) if rank_kernels else None},
         }
         if check:
             line["image_check"] = check

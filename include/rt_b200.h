@@ -197,6 +197,8 @@ int rt_get_stats(rt_ctx *ctx, rt_stats *out);
 /* profiling aid: counters of the wavefront kernel's scheduler when the library was built with
  * -DRT_POOL_STATS (zeros otherwise); out[0] = rays of the last render */
 int rt_debug_counters(rt_ctx *ctx, uint64_t out[32]);
+/* profiling aid: per-warp timeline records of a -DRT_WARP_TIMES build (8 words per warp; zeros otherwise) */
+int rt_debug_warp_times(rt_ctx *ctx, uint64_t *out, size_t n_words);
 
 /* host logic, no device needed: the sample layers rt_render cuts a wavefront frame into when rt_render_opts.slices = 0
  * (bulk layers, then layers that halve).  sizes[] has room for 64 entries; returns how many were written

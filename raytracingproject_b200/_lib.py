@@ -72,6 +72,7 @@ SYMBOLS = {
     "rt_image_size": (_I, [_VP, _VP, _VP]),
     "rt_synchronize": (_I, [_VP]),
     "rt_debug_counters": (_I, [_VP, _VP]),
+    "rt_debug_warp_times": (_I, [_VP, _VP, _SZ]),
     "rt_get_stats": (_I, [_VP, _VP]),
     "rt_accum_buffer": (_I, [_VP, _VP, _VP, _VP]),
     "rt_stream": (_I, [_VP, _VP]),

@@ -196,6 +196,11 @@ class Context:
         self._ck(self._lib.rt_debug_counters(self._h, L.ptr(out)))
         return out
 
+    def debug_warp_times(self, n_warps=148 * 32):
+        out = np.zeros((n_warps, 8), np.uint64)
+        self._ck(self._lib.rt_debug_warp_times(self._h, L.ptr(out), out.size))
+        return out
+
     def accum_buffer(self):
         p, n, e = C.c_void_p(), C.c_size_t(), C.c_int()
         self._ck(self._lib.rt_accum_buffer(self._h, C.byref(p), C.byref(n), C.byref(e)))

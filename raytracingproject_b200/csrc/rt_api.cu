@@ -33,6 +33,7 @@ static_assert(sizeof(MatRec) == sizeof(rt_material), "MatRec mirrors rt_material
 
 namespace {
 
+const size_t RT_DEBUG_WORDS = 32 + 8 * 32 * 256;     // debug counters + 8 words per warp (up to 256 SMs x 32 warps)
 const size_t RT_MAX_BIG = 16;          // spheres kept out of the tree (tested by every ray, in double)
 
 std::string g_create_error;
@@ -254,7 +255,7 @@ int rt_create(rt_ctx** out, int device) {
     ctx->job_counter.resize(1);
     ctx->frame_timeout.resize(1);
     cudaMemset(ctx->frame_timeout.p, 0, sizeof(int));
-    ctx->ray_counter.resize(32);      // [0] rays; [1..] scheduler counters of a -DRT_POOL_STATS build
+    ctx->ray_counter.resize(RT_DEBUG_WORDS);      // [0] rays; [1..31] scheduler counters of a -DRT_POOL_STATS build; [32..] per-warp times of a -DRT_WARP_TIMES build
     *out = ctx;
     return RT_OK;
 }
@@ -601,7 +602,11 @@ int plan_layers(int sample_count, long long tiles, long long resident_warps, int
     const double tiles_per_warp = double(std::max<long long>(1, tiles)) / double(std::max<long long>(1, resident_warps));
     int bulk = std::max(8, int(std::ceil(sample_count * tiles_per_warp / double(jobs_per_warp))));
     bulk = std::max(bulk, (sample_count + RT_MAX_SLICES - 9) / (RT_MAX_SLICES - 8));       // all of them fit the buffer's 64 layers
-    const int small = std::max(2, bulk / 8);
+    // the frame ends on layers of `small` samples: a job of the last layer on an expensive tile (glass: 5 x the mean rays per
+    // sample) is what every other warp waits for (tools/warp_times.py)
+    int small_div = 8;
+    if (const char* e = std::getenv("RT_PLAN_SMALL_DIV")) small_div = std::max(1, std::atoi(e));      // (A/B knob)
+    const int small = std::max(2, bulk / small_div);
     int left = sample_count, n = 0;
     while (left > 2 * bulk && n < RT_MAX_SLICES - 8) { sizes[n++] = bulk; left -= bulk; }
     *n_bulk = n;
@@ -655,7 +660,7 @@ int render_impl(rt_ctx* ctx, const rt_camera& cam, const rt_render_opts& o, int 
     ctx->stats.scene_in_smem = staged ? 1 : (p.scene.n_top > 0 ? 2 : 0);
     ctx->stats.top_nodes_in_smem = p.scene.n_top;
     CK(cudaMemsetAsync(ctx->job_counter.p, 0, sizeof(unsigned int), ctx->stream));
-    CK(cudaMemsetAsync(ctx->ray_counter.p, 0, 32 * sizeof(unsigned long long), ctx->stream));
+    CK(cudaMemsetAsync(ctx->ray_counter.p, 0, RT_DEBUG_WORDS * sizeof(unsigned long long), ctx->stream));
     CK(cudaEventRecord(ctx->ev[0], ctx->stream));
     // section thresholds: o.sched = th_s | th_l << 8 (0 = defaults, tuned on B200: see DESIGN.md)
     p.th_s = (o.sched & 0xff) ? (o.sched & 0xff) : (o.variant == RT_WAVEFRONT ? 22 : 28);       // wavefront: idle lanes before a pull (profiles/r1_sched_tune_final.txt)
@@ -898,6 +903,16 @@ extern "C" int rt_debug_counters(rt_ctx* ctx, uint64_t out[32]) {
     CK(cudaSetDevice(ctx->device));
     CK(cudaStreamSynchronize(ctx->stream));
     CK(cudaMemcpy(out, ctx->ray_counter.p, 32 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+    return RT_OK;
+}
+
+// profiling aid: the per-warp records a -DRT_WARP_TIMES build writes (8 words per warp: start, out-of-jobs and exit times in
+// ns, rounds and rays before / after the frame ran out of jobs, valid flag); zeros otherwise.  n_words <= 8 * 32 * 256.
+extern "C" int rt_debug_warp_times(rt_ctx* ctx, uint64_t* out, size_t n_words) {
+    if (!ctx || !out || n_words > RT_DEBUG_WORDS - 32) return RT_E_INVALID;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpy(out, ctx->ray_counter.p + 32, n_words * sizeof(uint64_t), cudaMemcpyDeviceToHost));
     return RT_OK;
 }
 

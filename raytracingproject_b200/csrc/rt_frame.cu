@@ -58,10 +58,11 @@ __global__ void resolve_kernel(const Q* __restrict__ accum, int slices, PeerList
         for (int k = 0; k < 4; ++k) { mine[k] = g + k < n_pixels && owns_pixel(owner, g + k); any = any || mine[k]; all_mine = all_mine && mine[k]; }
         if (!any) return;
     }
+    const int np = int(min(size_t(4), n_pixels - g));
+    unsigned char b[12];
     double s[4][4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) s[k][0] = s[k][1] = s[k][2] = s[k][3] = 0.0;
-    const int np = int(min(size_t(4), n_pixels - g));
     for (int sl = 0; sl < slices; ++sl) {
         const Q* src = accum + size_t(sl) * n_pixels + g;
 #pragma unroll
@@ -75,7 +76,6 @@ __global__ void resolve_kernel(const Q* __restrict__ accum, int slices, PeerList
             for (int k = 0; k < 4; ++k) if (k < np) { const Q v = src[k]; s[k][0] += double(v.x); s[k][1] += double(v.y); s[k][2] += double(v.z); s[k][3] += double(v.w); }
         }
     }
-    unsigned char b[12];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
         if (k < np && mine[k]) {
@@ -239,21 +239,28 @@ __global__ void __launch_bounds__(ENC_BLOCK) encode_count_kernel(const unsigned 
     if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
 }
 
-// exclusive scan of block_sums in place (64-bit offsets out), single block
+// exclusive scan of block_sums (64-bit offsets out), single block: every thread takes one contiguous chunk, all its loads in
+// flight at once (the first version walked the array 256 entries at a time, one dependent load + three barriers per step:
+// 27 us at 4K, as long as the pass that writes 95 MB of text), then one scan over the 256 chunk totals
 __global__ void __launch_bounds__(ENC_BLOCK) encode_scan_kernel(const unsigned* __restrict__ block_sums, int n_blocks,
                                                                   unsigned long long* __restrict__ block_offsets, unsigned long long header_len,
                                                                   unsigned long long* __restrict__ total_len) {
-    __shared__ unsigned warp_sums[ENC_BLOCK / 32];
-    unsigned long long carry = header_len;
-    for (int base = 0; base < n_blocks; base += ENC_BLOCK) {
-        const int i = base + threadIdx.x;
-        const unsigned v = i < n_blocks ? block_sums[i] : 0;
-        unsigned total;
-        const unsigned ex = block_exclusive_scan(v, warp_sums, total);
-        if (i < n_blocks) block_offsets[i] = carry + ex;
-        carry += total;
-    }
-    if (threadIdx.x == 0) *total_len = carry;
+    __shared__ unsigned long long warp_tot[ENC_BLOCK / 32];
+    const int per = (n_blocks + ENC_BLOCK - 1) / ENC_BLOCK;
+    const int lo = min(n_blocks, int(threadIdx.x) * per), hi = min(n_blocks, lo + per);
+    unsigned long long mine = 0;
+    for (int i = lo; i < hi; ++i) mine += block_sums[i];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    unsigned long long x = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const unsigned long long y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    if (lane == 31) warp_tot[wid] = x;
+    __syncthreads();
+    unsigned long long base = header_len;
+    for (int w = 0; w < wid; ++w) base += warp_tot[w];
+    unsigned long long run = base + x - mine;                       // exclusive prefix of this thread's chunk
+    for (int i = lo; i < hi; ++i) { block_offsets[i] = run; run += block_sums[i]; }
+    if (threadIdx.x == ENC_BLOCK - 1) *total_len = base + x;
 }
 
 __device__ __forceinline__ int put_number(char* dst, unsigned v) {
@@ -365,15 +372,16 @@ __global__ void __launch_bounds__(ENC_BLOCK) resolve_encode_kernel(const Q* __re
                 px[3 * k] = px[3 * k + 1] = px[3 * k + 2] = 0;
             }
         }
-        if (rgb8) {
-            if (np == 4) {
-                unsigned int* dst = reinterpret_cast<unsigned int*>(rgb8 + 3 * p0);
-                dst[0] = px[0] | (px[1] << 8) | (px[2] << 16) | (unsigned(px[3]) << 24);
-                dst[1] = px[4] | (px[5] << 8) | (px[6] << 16) | (unsigned(px[7]) << 24);
-                dst[2] = px[8] | (px[9] << 8) | (px[10] << 16) | (unsigned(px[11]) << 24);
-            } else {
-                for (int k = 0; k < 3 * np; ++k) rgb8[3 * p0 + k] = px[k];
-            }
+    }
+    if (rgb8 && p0 < n_pixels) {
+        const int np = int(min(size_t(4), n_pixels - p0));
+        if (np == 4) {
+            unsigned int* dst = reinterpret_cast<unsigned int*>(rgb8 + 3 * p0);
+            dst[0] = px[0] | (px[1] << 8) | (px[2] << 16) | (unsigned(px[3]) << 24);
+            dst[1] = px[4] | (px[5] << 8) | (px[6] << 16) | (unsigned(px[7]) << 24);
+            dst[2] = px[8] | (px[9] << 8) | (px[10] << 16) | (unsigned(px[11]) << 24);
+        } else {
+            for (int k = 0; k < 3 * np; ++k) rgb8[3 * p0 + k] = px[k];
         }
     }
     unsigned total;

@@ -60,7 +60,12 @@ inline void pool_shape(int shape, int* paths, int* block) {
     if (shape < 0 || shape >= RT_POOL_SHAPES) shape = 0;
     *paths = P[shape]; *block = B[shape];
 }
-template <typename T> inline size_t pool_warp_bytes(int paths) { return size_t(paths) * (11 * sizeof(T) + 4 + 2 * 2 + 4) + 16 * RT_RING; }   // + the warp's job descriptors
+#ifndef RT_DYNAMIC_ITEMS
+#define RT_DYNAMIC_ITEMS 1             // (rt_wavefront.cuh)
+#endif
+template <typename T> inline size_t pool_warp_bytes(int paths) {      // + the warp's job descriptors (dynamic mode, float: 4 entries of 32 bytes)
+    return size_t(paths) * (11 * sizeof(T) + 4 + 2 * 2 + 4) + ((RT_DYNAMIC_ITEMS != 0 && sizeof(T) == 4) ? 80 : 16 * RT_RING);
+}
 #define RT_POOL_DEFAULT_SHAPE(T) (sizeof(T) == 4 ? 3 : 0)
 #define RT_POOL_UNSTAGED_SHAPE(T) (sizeof(T) == 4 ? 9 : 0)
 template <typename T> cudaError_t launch_render_pool(const RenderParams<T>& p, int shape, bool staged, int sm_count, cudaStream_t st);

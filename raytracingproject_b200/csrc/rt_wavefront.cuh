@@ -41,6 +41,14 @@ namespace rt {
 #define RT_RING 2                      // jobs a warp keeps open (2 or 4)
 #endif
 
+#ifndef RT_DYNAMIC_ITEMS
+#define RT_DYNAMIC_ITEMS 1             // fast mode: pool slots take (pixel, sample) work items of the open jobs dynamically (A/B: make DYN=0)
+#endif
+
+#ifndef RT_FETCH_MULT
+#define RT_FETCH_MULT 1                // jobs taken from the frame's counter at a time = RT_FETCH_MULT x job_group (consecutive indices: in the bulk
+#endif                                 // phase 2 x 2 = the same tile pair, two consecutive layers -- for the RING=4 experiment)
+
 #ifndef RT_PHILOX_TABLE
 #define RT_PHILOX_TABLE 0              // 1: Philox round keys precomputed in the parameter block (LDCU into uniform registers) instead of two uniform
 #endif                                 // additions per round -- measured 0.7 % SLOWER on C3 / C4 (profiles/r2_ab_merge_table_top.txt), so off; make TABLE=1
@@ -53,8 +61,10 @@ template <typename T, int P> struct Pool {
     enum { OX, OY, OZ, TM, DX, DY, DZ, TR, TG, TB, TBEST, NF };        // T arrays [P]
     enum { BEST, NI };                                                  // int arrays [P]
     enum { SAMPLE, DEPTH, NH };                                         // 16-bit arrays [P]: ring entry (top 1 or 2 bits) | next sample relative to the job's first (all ones: done with that job); bounces left
-    enum { QUEUE, LOPAQUE, LGLASS, LEND, NL };                          // byte lists [P]
-    static constexpr int ring = RT_RING, ring_bytes = 16 * ring;        // job descriptors (int4) of the warp, after the lists
+    enum { QUEUE, LOPAQUE, LPIXEL, LEND, NL };                          // byte lists [P]; LPIXEL (dynamic mode): the pixel of the tile a slot is working on
+    // dynamic mode (fast mode only, see the END stage): slots take (pixel, sample) items of the open jobs instead of owning a pixel
+    static constexpr bool dyn = RT_DYNAMIC_ITEMS != 0 && sizeof(T) == 4;
+    static constexpr int ring = dyn ? 4 : RT_RING, ring_bytes = dyn ? 16 * ring + 16 : 16 * ring;   // job descriptors (int4) of the warp (+ counters), after the lists
     static constexpr int bytes = NF * P * int(sizeof(T)) + NI * P * 4 + NH * P * 2 + NL * P + ring_bytes;
     static constexpr int tile_w = 16, tile_h = P / 16;
     static_assert(P % 32 == 0 && P <= 128, "pool: path id is 7 bits, lists are filled 32 at a time");
@@ -120,6 +130,12 @@ render_pool_kernel(const RenderParams<T> p) {
 #else
 #define RT_STAT(k, v) ((void)0)
 #endif
+#ifdef RT_WARP_TIMES
+    // profiling build (make TIMES=1): when a warp starts, runs out of jobs and exits, how many rounds it ran and how many rays
+    // they traced, before and after the frame ran out of jobs -- the frame's tail, measured (tools/warp_times.py)
+    unsigned long long wt_first = 0, wt_exhausted = 0, wt_rounds = 0, wt_nq = 0, wt_rounds_tail = 0, wt_nq_tail = 0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(wt_first));
+#endif
     int stack[RT_STACK];
 
     // Ring state (warp-uniform).  Every slot goes through every job of its warp, in order: `newest` is the
@@ -137,6 +153,8 @@ render_pool_kernel(const RenderParams<T> p) {
         B[L::LEND * P + k] = (unsigned char)(k | 0x80);               // 0x80: nothing to add
     }
     int n_q = 0, n_end = P, n_opq = 0, n_gls = 0;
+    int dyn_n = 0, dyn_e0 = 0, dyn_e1 = 0, dyn_left0 = 0, dyn_left1 = 0;   // dynamic mode: the (at most two) jobs that still have items to hand out
+    if (L::dyn && lane < 4) reinterpret_cast<int*>(ring + 4)[lane] = 0;
     __syncwarp();
 
     {
@@ -146,9 +164,48 @@ render_pool_kernel(const RenderParams<T> p) {
             // (camera::render's sample loop + get_ray, src/camera.h:41-44,87-100) in its job or in the next one
             bool progress = false;
             int n_idle = 0;
+            if (L::dyn) {
+            // ---- dynamic mode (fast mode).  A slot does not own a pixel: every free slot takes the next (pixel, sample) ITEM of
+            // the open jobs -- item k of a job = sample k / P of the tile's pixel k % P -- so a pool stays full until its jobs
+            // run out of items, however unequal the paths of its pixels are (a pixel inside a glass sphere costs 5 x the mean;
+            // with slots bound to pixels the other slots of its job had to wait for it: 121 of 128 slots busy at 500 spp, 107 at
+            // 62 spp, 89 at 16 spp, and a frame ended on the slowest pixel of its last jobs: tools/warp_times.py).  The sums
+            // of a pixel are then formed by whichever slots took its samples, in any order: float RED.ADD, fast mode only --
+            // parity mode keeps the slot-per-pixel loop below, whose sum has the reference's order.
+            // Up to 4 jobs are open: the two newest hand out items, older ones only wait for their last paths to end.
+            int* const pend = reinterpret_cast<int*>(ring + 4);        // per entry: items not completed yet (0: the entry is free)
             for (int b = 0; b < n_end; b += 32) {
-                // fetch one job ahead of the first slot, no more: jobs a warp holds unstarted are the frame's tail
-                if (!exhausted && ((joined >> (8 * newest)) & 0xffu) != 0u && ((joined >> (8 * ((newest + 2) & (R - 1)))) & 0xffu) == unsigned(P)) {
+                const int idx = b + lane;
+                const bool valid = idx < n_end;
+                int pid = 0, jb = -1;
+                if (valid) {
+                    const int e = B[L::LEND * P + idx];
+                    pid = e & 0x7f;
+                    const int sw = S[L::SAMPLE * P + pid];
+                    if (sw != 0xffff) {                                // a path ended here: its item is complete
+                        jb = sw >> 14;
+                        if (!(e & 0x80)) {                             // a miss: thr * sky goes to its pixel
+                            const int4 J = ring[jb];
+                            const int pix = B[L::LPIXEL * P + pid];
+                            const int i = (J.x & 0xffff) + (pix & 15), j = (J.x >> 16) + (pix >> 4);
+                            const Vec<T> d = mk<T>(F[L::DX * P + pid], F[L::DY * P + pid], F[L::DZ * P + pid]);
+                            const Vec<T> thr = mk<T>(F[L::TR * P + pid], F[L::TG * P + pid], F[L::TB * P + pid]);
+                            accum_add(p.accum + size_t(J.w) * layer + size_t(j) * size_t(W) + size_t(i), thr * sky<T>(d));
+                        }
+                    }
+                }
+                if (__any_sync(FULL, jb >= 0)) {
+                    const int c0 = __popc(__ballot_sync(FULL, jb == 0)), c1 = __popc(__ballot_sync(FULL, jb == 1));
+                    const int c2 = __popc(__ballot_sync(FULL, jb == 2)), c3 = __popc(__ballot_sync(FULL, jb == 3));
+                    if (lane < 4) pend[lane] -= lane == 0 ? c0 : (lane == 1 ? c1 : (lane == 2 ? c2 : c3));
+                    __syncwarp();
+                    progress = true;
+                }
+                // keep two jobs with items to hand out
+                while (!exhausted && dyn_n < 2) {
+                    const unsigned fm = __ballot_sync(FULL, lane < 4 && pend[lane] == 0) & 0xfu;
+                    if (fm == 0u) break;                               // four jobs still have paths in flight
+                    const int ef = __ffs(fm) - 1;
                     int job = 0;
                     if (pend_left > 0) { job = pend_next++; --pend_left; }
                     else {
@@ -156,7 +213,106 @@ render_pool_kernel(const RenderParams<T> p) {
                         job = __shfl_sync(FULL, job, 0);
                         pend_next = job + 1; pend_left = group - 1;
                     }
-                    if (job >= njobs) exhausted = true;
+                    if (job >= njobs) {
+                        exhausted = true;
+#ifdef RT_WARP_TIMES
+                        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(wt_exhausted));
+#endif
+                        break;
+                    }
+                    int slice, tile;
+                    if (job < nbulk) { const int gl = group * p.bulk_layers, g = job / gl, r = job - g * gl; slice = r / group; tile = group * (g * tw + tr) + (r - slice * group); }
+                    else { const int r = job - nbulk; slice = r / ntiles_l; const int tl = r - slice * ntiles_l, g = tl / group; tile = group * (g * tw + tr) + (tl - g * group); slice += p.bulk_layers; }
+                    progress = true;
+                    if (tile >= ntiles) continue;                      // the last group may be short of tiles
+                    const int bx = (tile % p.tiles_x) * L::tile_w, by = (tile / p.tiles_x) * L::tile_h;
+                    const int s_begin = p.slice_begin[slice], s_end = p.slice_begin[slice + 1];
+                    // the job's accumulator: every pixel of the tile gets its sample count (src/camera.h:41 starts from zero)
+                    for (int q = lane; q < P; q += 32) {
+                        const int i = bx + (q & 15), j = by + (q >> 4);
+                        if (i < W && j < H) {
+                            Q* dst = p.accum + size_t(slice) * layer + size_t(j) * size_t(W) + size_t(i);
+                            Q v;
+                            if (p.accumulate) { v = *dst; } else { v.x = 0; v.y = 0; v.z = 0; v.w = 0; }
+                            v.w += decltype(v.x)(s_end - s_begin);
+                            *dst = v;
+                        }
+                    }
+                    const int items = p.max_depth > 0 ? (s_end - s_begin) * P : 0;     // max_depth <= 0: black (src/camera_cpu.h:12-13)
+                    if (items > 0) {
+                        if (lane == 0) { ring[ef] = make_int4(bx | (by << 16), s_begin, s_end, slice); pend[ef] = items; }
+                        if (dyn_n == 0) { dyn_e0 = ef; dyn_left0 = items; } else { dyn_e1 = ef; dyn_left1 = items; }
+                        ++dyn_n;
+                    }
+                    __syncwarp();
+                }
+                // hand the next items to the slots of this batch, the older job's first
+                const unsigned mv = __ballot_sync(FULL, valid);
+                const int rank = __popc(mv & lt), nreq = __popc(mv);
+                const int a0 = dyn_n > 0 ? dyn_left0 : 0, a1 = dyn_n > 1 ? dyn_left1 : 0;
+                bool push = false; int skipped = -1;
+                if (valid) {
+                    int ent = -1, left = 0, rr = 0;
+                    if (rank < a0) { ent = dyn_e0; left = dyn_left0; rr = rank; }
+                    else if (rank < a0 + a1) { ent = dyn_e1; left = dyn_left1; rr = rank - a0; }
+                    if (ent >= 0) {
+                        const int4 J = ring[ent];
+                        const int item = (J.z - J.y) * P - left + rr;
+                        const int srel = item / P, pix = item - srel * P;
+                        const int i = (J.x & 0xffff) + (pix & 15), j = (J.x >> 16) + (pix >> 4);
+                        if (i < W && j < H) {
+                            PhiloxT<RT_PHILOX_TABLE != 0> rng; if (RT_PHILOX_TABLE) rng.init(p.keys); else rng.init(p.seed);
+                            rng.set(uint32_t(j) * uint32_t(W) + uint32_t(i), uint32_t(J.y + srel), 0u);
+                            const Ray<T> ray = get_ray<T>(p.cam, i, j, rng);
+                            F[L::OX * P + pid] = ray.o.x; F[L::OY * P + pid] = ray.o.y; F[L::OZ * P + pid] = ray.o.z; F[L::TM * P + pid] = ray.tm;
+                            F[L::DX * P + pid] = ray.d.x; F[L::DY * P + pid] = ray.d.y; F[L::DZ * P + pid] = ray.d.z;
+                            F[L::TR * P + pid] = T(1); F[L::TG * P + pid] = T(1); F[L::TB * P + pid] = T(1);
+                            S[L::SAMPLE * P + pid] = (unsigned short)((ent << 14) | srel); S[L::DEPTH * P + pid] = (unsigned short)p.max_depth;
+                            B[L::LPIXEL * P + pid] = (unsigned char)pix;
+                            push = true;
+                        } else {
+                            skipped = ent;                             // a pixel position outside the image: nothing to trace
+                        }
+                    }
+                    if (!push) S[L::SAMPLE * P + pid] = (unsigned short)0xffff;
+                }
+                {
+                    const int t0 = min(nreq, a0), t1 = min(nreq - t0, a1);
+                    dyn_left0 -= t0; dyn_left1 -= t1;
+                    if (dyn_n == 2 && dyn_left1 == 0) dyn_n = 1;
+                    if (dyn_n >= 1 && dyn_left0 == 0) { dyn_e0 = dyn_e1; dyn_left0 = dyn_left1; dyn_left1 = 0; --dyn_n; }
+                }
+                if (__any_sync(FULL, skipped >= 0)) {
+                    const int c0 = __popc(__ballot_sync(FULL, skipped == 0)), c1 = __popc(__ballot_sync(FULL, skipped == 1));
+                    const int c2 = __popc(__ballot_sync(FULL, skipped == 2)), c3 = __popc(__ballot_sync(FULL, skipped == 3));
+                    __syncwarp();
+                    if (lane < 4) pend[lane] -= lane == 0 ? c0 : (lane == 1 ? c1 : (lane == 2 ? c2 : c3));
+                    progress = true;
+                }
+                __syncwarp();                                          // the batch has read its entries: the list is refilled in place below
+                const unsigned m = __ballot_sync(FULL, push), mi = __ballot_sync(FULL, valid && !push);
+                if (push) B[L::QUEUE * P + n_q + __popc(m & lt)] = (unsigned char)pid;
+                if (valid && !push) B[L::LEND * P + n_idle + __popc(mi & lt)] = (unsigned char)(pid | 0x80);
+                n_q += __popc(m); n_idle += __popc(mi);
+                progress = progress || m != 0u;
+            }
+            } else {
+            for (int b = 0; b < n_end; b += 32) {
+                // fetch one job ahead of the first slot, no more: jobs a warp holds unstarted are the frame's tail
+                if (!exhausted && ((joined >> (8 * newest)) & 0xffu) != 0u && ((joined >> (8 * ((newest + 2) & (R - 1)))) & 0xffu) == unsigned(P)) {
+                    int job = 0;
+                    if (pend_left > 0) { job = pend_next++; --pend_left; }
+                    else {
+                        if (lane == 0) job = int(atomicAdd(p.job_counter, unsigned(group * RT_FETCH_MULT)));
+                        job = __shfl_sync(FULL, job, 0);
+                        pend_next = job + 1; pend_left = group * RT_FETCH_MULT - 1;
+                    }
+                    if (job >= njobs) {
+                        exhausted = true;
+#ifdef RT_WARP_TIMES
+                        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(wt_exhausted));
+#endif
+                    }
                     else {
                         // job order: the bulk layers group of tiles by group of tiles (layer by layer over the whole image -- the
                         // open jobs of a warp 30 tile rows apart -- measured 4 % slower), then the short layers one after the
@@ -231,9 +387,13 @@ render_pool_kernel(const RenderParams<T> p) {
                 }
                 progress = progress || m != 0u;
             }
+            }
             n_end = n_idle;
             __syncwarp();
             if (n_q == 0) { if (progress) continue; break; }   // nothing in flight, nothing left to start: the frame is done
+#ifdef RT_WARP_TIMES
+            if (exhausted) { ++wt_rounds_tail; wt_nq_tail += n_q; } else { ++wt_rounds; wt_nq += n_q; }
+#endif
 
             // ------------------------------------------------------------------ BIG stage
             // every queued ray against the spheres kept out of the tree (the r = 1000 ground), in
@@ -367,13 +527,14 @@ render_pool_kernel(const RenderParams<T> p) {
 #endif
                         const int sw = S[L::SAMPLE * P + pid];
                         const int4 J = ring[sw >> SH];
-                        const int i = (J.x & 0xffff) + (pid & 15), j = (J.x >> 16) + (pid >> 4);
+                        const int pix = L::dyn ? int(B[L::LPIXEL * P + pid]) : pid;            // dynamic mode: the slot's current pixel
+                        const int i = (J.x & 0xffff) + (pix & 15), j = (J.x >> 16) + (pix >> 4);
                         Ray<T> ray;
                         ray.o = mk<T>(F[L::OX * P + pid], F[L::OY * P + pid], F[L::OZ * P + pid]);
                         ray.d = mk<T>(F[L::DX * P + pid], F[L::DY * P + pid], F[L::DZ * P + pid]);
                         ray.tm = F[L::TM * P + pid];
                         T t = F[L::TBEST * P + pid];
-                        const int slot = I[L::BEST * P + pid], s = J.y + (sw & DONE);
+                        const int slot = I[L::BEST * P + pid], s = J.y + (sw & DONE) + (L::dyn ? 1 : 0);   // (static mode keeps "next sample" here)
                         int depth = S[L::DEPTH * P + pid];
                         const Surface<T> sf = surface_at<T>(sv, st.sa, st.sb, st.sc, st.meta, ray, t, slot);
                         PhiloxT<RT_PHILOX_TABLE != 0> rng; if (RT_PHILOX_TABLE) rng.init(p.keys); else rng.init(p.seed);
@@ -406,6 +567,14 @@ render_pool_kernel(const RenderParams<T> p) {
     if (lane == 0 && my_rays) atomicAdd(p.ray_counter, my_rays);
 #ifdef RT_POOL_STATS
     if (lane == 0) for (int k = 0; k < 24; ++k) if (stat[k]) atomicAdd(p.ray_counter + 1 + k, stat[k]);
+#endif
+#ifdef RT_WARP_TIMES
+    if (lane == 0) {
+        unsigned long long wt_exit;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(wt_exit));
+        unsigned long long* o = p.ray_counter + 32 + 8 * (size_t(blockIdx.x) * 32 + warp);
+        o[0] = wt_first; o[1] = wt_exhausted; o[2] = wt_exit; o[3] = wt_rounds; o[4] = wt_nq; o[5] = wt_rounds_tail; o[6] = wt_nq_tail; o[7] = 1;
+    }
 #endif
 }
 

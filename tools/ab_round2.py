@@ -61,6 +61,8 @@ def main():
             if "+" in path:                                   # lib+{"top_cap": -1}: extra render keywords
                 path, extra = path.split("+", 1)
                 kw = json.loads(extra)
+            for k in [k for k in kw if k.startswith("e_")]:           # e_NAME: environment variable NAME for the child
+                env[k[2:]] = str(kw.pop(k))
             env["AB_RENDER_KW"] = json.dumps(kw)
             if path.startswith("@"):
                 env["AB_ROOT"] = os.path.join(ROOT, "ab", path[1:])
