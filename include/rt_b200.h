@@ -273,6 +273,20 @@ int rt_bench_closest(rt_ctx *ctx, const rt_camera *cam, size_t n, uint64_t seed,
 int rt_write_color(rt_ctx *ctx, const double *sums_rgb, size_t n, int samples_per_pixel, uint8_t *rgb8);
 int rt_encode_p3(rt_ctx *ctx, const uint8_t *rgb8, int width, int height, char *ppm, size_t *ppm_len);
 
+/* The P3 encoder for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid allocation).  NO COUNTERPART IN THE REFERENCE.  Same text as
+ * rt_encode_p3, but every buffer is the caller's and lives on the context's device: dev_rgb8 (width*height*3 bytes, read
+ * exactly, no padding needed), dev_ppm (ppm_capacity >= 32 + 12*width*height bytes: the worst case is required up front,
+ * the length is not known before the pass), *dev_ppm_len (device, 8 bytes: the text's length).  Asynchronous on the
+ * context's stream (rt_stream / rt_synchronize).  The prefix-sum scratch is a static __device__ array inside the library
+ * (128 KB on every GPU that loads it, until exit) sized for RT_STATIC_MAX_PIXELS; larger images are refused with
+ * RT_E_INVALID and a message.  The call allocates nothing on host or device (no cudaMalloc / cudaFree, no library that
+ * does).  All calls share the one array per GPU: calls on the same stream are ordered and safe, calls that overlap on a
+ * GPU (two contexts, two streams) race on it -- serialise them. */
+#define RT_STATIC_MAX_PIXELS (1 << 24)
+int rt_encode_p3_static(rt_ctx *ctx, const uint8_t *dev_rgb8, int width, int height, char *dev_ppm, size_t ppm_capacity,
+                        unsigned long long *dev_ppm_len);
+
 /* ---- next row 8f-3: the demo's compute shader as a CUDA kernel ---------------------------------- */
 
 /* `Sphere` of the windowed demo, src/common_objects.h:17-22 (glm::vec3 center; float radius; glm::vec4 color) */

@@ -91,6 +91,7 @@ SYMBOLS = {
     "rt_bench_closest": (_I, [_VP, _VP, _SZ, _U64, _I, _I, _I, _VP, _VP, _VP, _VP, _SZ]),
     "rt_write_color": (_I, [_VP, _VP, _SZ, _I, _VP]),
     "rt_encode_p3": (_I, [_VP, _VP, _I, _I, _VP, _VP]),
+    "rt_encode_p3_static": (_I, [_VP, _VP, _I, _I, _VP, _SZ, _VP]),
     "rt_demo_compute": (_I, [_VP, _VP, _SZ, _I, _I, _VP]),
     "rt_build_bvh_host": (_I, [_VP, _SZ, _I, _VP, _VP, _VP, _VP, _VP]),
     "rt_scene_rtiow": (_SZ, [_I, _D, _D, C.c_uint32, _VP, _VP, _SZ]),

@@ -296,6 +296,12 @@ class Context:
         self._ck(self._lib.rt_encode_p3(self._h, L.ptr(rgb8), W, H, buf, C.byref(cap)))
         return buf.raw[:cap.value]
 
+    def encode_p3_static(self, dev_rgb8, width, height, dev_ppm, ppm_capacity, dev_ppm_len):
+        """rt_encode_p3_static: the allocation-free encoder.  Every buffer is a DEVICE address (int) of the caller's, on this
+        context's device; asynchronous on the context's stream (synchronize() before reading the results)."""
+        self._ck(self._lib.rt_encode_p3_static(self._h, C.c_void_p(dev_rgb8), width, height, C.c_void_p(dev_ppm),
+                                               C.c_size_t(ppm_capacity), C.c_void_p(dev_ppm_len)))
+
 
 def plan_layers(sample_count, tiles, resident_warps, jobs_per_warp=0):
     """Host logic alone (no device): the sample layers of a wavefront frame in auto mode -> (sizes, n_bulk)."""

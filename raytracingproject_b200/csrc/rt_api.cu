@@ -21,6 +21,7 @@
 #include "rt_kernels.cuh"
 #include "rt_lbvh.h"
 #include "rt_scene.h"
+#include "rt_static.h"
 
 using namespace rt;
 
@@ -1291,6 +1292,17 @@ extern "C" int rt_encode_p3(rt_ctx* ctx, const uint8_t* rgb8, int width, int hei
     d_b.release(); d_s.release(); d_o.release(); d_t.release();
     if (e != cudaSuccess) return cuda_fail(ctx, e, "rt_encode_p3");
     return rc;
+}
+
+// No counterpart in the reference: the encoder for callers that may not allocate (rt_static.cu holds the scratch in a
+// file-scope __device__ array).  Nothing here or below it calls cudaMalloc / cudaFree; asynchronous on the context's stream.
+extern "C" int rt_encode_p3_static(rt_ctx* ctx, const uint8_t* dev_rgb8, int width, int height, char* dev_ppm, size_t ppm_capacity,
+                                   unsigned long long* dev_ppm_len) {
+    if (!ctx) return RT_E_INVALID;
+    char msg[256] = "";
+    const int rc = encode_p3_static(ctx->device, ctx->stream, dev_rgb8, width, height, dev_ppm, ppm_capacity, dev_ppm_len, msg, sizeof msg);
+    if (rc != 0) return fail(ctx, rc == -2 ? RT_E_CUDA : RT_E_INVALID, msg);
+    return RT_OK;
 }
 
 extern "C" int rt_demo_compute(rt_ctx* ctx, const rt_demo_sphere* spheres, size_t n, int width, int height, uint8_t* rgba8) {

@@ -4,6 +4,7 @@
 // Restates src/color.h:9-12,14-35 (1/spp, sqrt gamma, clamp [0,0.999], int(256*x), "r g b\n")
 // and the header of src/camera.h:35.  Arithmetic is double as in the reference.
 #include "rt_frame.h"
+#include "rt_encode.cuh"
 
 #include <cstdlib>
 
@@ -187,33 +188,6 @@ template cudaError_t launch_fold<double4>(double4*, int, size_t, cudaStream_t);
 // "r g b\n" with variable-width decimals (src/color.h:32-34) needs a prefix sum of line lengths:
 // pass 1 per-block totals, pass 2 scan of the totals (one block), pass 3 block-local scan,
 // text staged in shared memory and copied out with consecutive threads writing consecutive bytes.
-#define ENC_BLOCK 256
-#define ENC_PPT 4                      // pixels per thread
-#define ENC_TILE (ENC_BLOCK * ENC_PPT)
-
-__device__ __forceinline__ int ndigits(unsigned v) { return v >= 100 ? 3 : (v >= 10 ? 2 : 1); }
-__device__ __forceinline__ int line_len(const unsigned char* p) { return ndigits(p[0]) + ndigits(p[1]) + ndigits(p[2]) + 3; }
-
-__device__ __forceinline__ unsigned block_exclusive_scan(unsigned v, unsigned* warp_sums, unsigned& total) {
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    unsigned x = v;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { const unsigned y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
-    if (lane == 31) warp_sums[wid] = x;
-    __syncthreads();
-    if (wid == 0) {
-        unsigned w = lane < (ENC_BLOCK / 32) ? warp_sums[lane] : 0;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { const unsigned y = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += y; }
-        if (lane < (ENC_BLOCK / 32)) warp_sums[lane] = w;       // inclusive
-    }
-    __syncthreads();
-    total = warp_sums[ENC_BLOCK / 32 - 1];
-    const unsigned base = wid > 0 ? warp_sums[wid - 1] : 0;
-    __syncthreads();
-    return base + x - v;
-}
-
 // the ENC_PPT = 4 pixels of a thread are 12 consecutive bytes at a 4-byte aligned address: three 32-bit loads
 // (a warp reads 384 contiguous bytes) instead of twelve byte loads.  The caller's rgb8 buffer is padded by
 // >= 12 bytes, so the last thread may read past pixel n_pixels - 1; it never uses those bytes.
@@ -261,14 +235,6 @@ __global__ void __launch_bounds__(ENC_BLOCK) encode_scan_kernel(const unsigned* 
     unsigned long long run = base + x - mine;                       // exclusive prefix of this thread's chunk
     for (int i = lo; i < hi; ++i) { block_offsets[i] = run; run += block_sums[i]; }
     if (threadIdx.x == ENC_BLOCK - 1) *total_len = base + x;
-}
-
-__device__ __forceinline__ int put_number(char* dst, unsigned v) {
-    int n = 0;
-    if (v >= 100) { dst[n++] = char('0' + v / 100); v %= 100; dst[n++] = char('0' + v / 10); dst[n++] = char('0' + v % 10); }
-    else if (v >= 10) { dst[n++] = char('0' + v / 10); dst[n++] = char('0' + v % 10); }
-    else dst[n++] = char('0' + v);
-    return n;
 }
 
 // The block's text is staged in shared memory at the SAME 16-byte misalignment its destination has, so that
