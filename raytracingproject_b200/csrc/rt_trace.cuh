@@ -11,6 +11,9 @@ namespace rt {
 
 #define RT_SENTINEL ((int)0x80000000)
 #define RT_STACK 64
+#ifndef RT_PREFETCH_FAR
+#define RT_PREFETCH_FAR 0               // tree in global memory: prefetch the pushed far child into L1 (1: its first 32 bytes, 2: all 64)
+#endif
 
 // Node record (one per inner node, 64 B = 4 x float4), boxes of BOTH children, padded outwards:
 //   q0 = (Lmin.x, Lmin.y, Lmax.x, Lmax.y)   q1 = (Rmin.x, Rmin.y, Rmax.x, Rmax.y)
@@ -228,6 +231,15 @@ __device__ __forceinline__ void trav_node_top(const float4* __restrict__ nodes, 
     const int cl = __float_as_int(q3.x), cr = __float_as_int(q3.y);
     const bool left_first = !hr || (hl && tl <= tr);
     const int near = left_first ? cl : cr, far = left_first ? cr : cl;
+#if RT_PREFETCH_FAR
+    // a far child that is pushed will be fetched many visits later, after a pop: ask for its record now, so that the pop finds
+    // it in L1 instead of paying an L2 round trip on the walk's critical path (A/B knob, make PF=1 / 2)
+    if (hl && hr && far >= n_top) {
+        const float4* f = nodes + 4 * size_t(far);
+        asm volatile("prefetch.global.L1 [%0];" :: "l"(f));
+        if (RT_PREFETCH_FAR >= 2) asm volatile("prefetch.global.L1 [%0];" :: "l"(f + 2));
+    }
+#endif
     if (hl && hr && tv.sp < RT_STACK) { stack[tv.sp++] = far; tv.tos = far; }
     int next = near;
     if (!(hl || hr)) {
