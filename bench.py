@@ -285,7 +285,10 @@ def main():
     # warm-up render so buffers exist, then set up the combine
     n_tiles = ((W + 15) // 16) * ((H + 7) // 8)                          # 16 x 8 pixel tiles of the wavefront kernel's 128-path pools
     resident_warps = torch.cuda.get_device_properties(local).multi_processor_count * 24
-    want_tiles = args.shard == "tiles" or (args.shard == "auto" and n_tiles // max(1, world) >= 2 * resident_warps)
+    # auto: tiles cost the kernel ~3 % at 8100 tiles per rank, 11 % at 2025 (a rank's last layers have fewer jobs than warps:
+    # profiles/r2_tile_sharding_1gpu_diag.txt) and save the fold + NCCL reduce (~1 % of a C3 frame at N = 2), so they only pay where
+    # the sample shards would be short as well: C5's 64 spp over 8 ranks, not C3's 500 (N = 2: 141.6 ms by tiles, 134.9 by samples)
+    want_tiles = args.shard == "tiles" or (args.shard == "auto" and n_tiles // max(1, world) >= 2 * resident_warps and args.spp // max(1, world) < 32)
     tiles = world > 1 and want_tiles and args.variant == "wavefront"
     if tiles:
         ctx.render(cam, precision=prec, seed=0, tile_rank=rank, tile_world=world)
@@ -420,7 +423,9 @@ def main():
             "config": {"workload": workload if args.spp == cfg_spp else f"NOT the named config: {args.config} at spp={args.spp}",
                        "variant": args.variant, "n_spheres": n_spheres,
                        "bvh": ("host SAH" if builder == "sah" else "GPU Morton LBVH") + f", depth {st_scene['bvh_depth']}, " +
-                              ("whole scene staged in shared memory" if st_scene["scene_in_smem"] else "nodes and spheres in global memory (L2 / HBM)"),
+                              ("whole scene staged in shared memory" if st_scene["scene_in_smem"] == 1 else
+                               f"nodes and spheres in global memory (L2 / HBM), first {st_scene.get('top_nodes_in_smem', 0)} nodes of the tree also in shared memory"
+                               if st_scene["scene_in_smem"] == 2 else "nodes and spheres in global memory (L2 / HBM)"),
                        "seed": 0,
                        "parallelism": (f"tile-interleaved sharding x{world} (pairs of 16x8 tiles), every rank's resolve kernel writes its tiles' "
                                        f"bytes into rank 0's image over NVLink" if tiles else

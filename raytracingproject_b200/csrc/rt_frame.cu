@@ -301,7 +301,8 @@ __global__ void __launch_bounds__(ENC_BLOCK) resolve_encode_kernel(const Q* __re
     __shared__ unsigned warp_sums[ENC_BLOCK / 32];
     __shared__ __align__(16) char stage[ENC_TILE * 12 + 16];
     __shared__ unsigned s_tile;
-    __shared__ unsigned long long s_base;
+    __shared__ unsigned long long s_part[ENC_BLOCK / 32];
+    __shared__ int s_inc[ENC_BLOCK / 32];
     if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
     __syncthreads();
     const unsigned tile = s_tile;
@@ -352,45 +353,44 @@ __global__ void __launch_bounds__(ENC_BLOCK) resolve_encode_kernel(const Q* __re
     }
     unsigned total;
     const unsigned local = block_exclusive_scan(len, warp_sums, total);
-    // ---- where does this tile's text start: header + the totals of all tiles before it
-    if (threadIdx.x < 32) {
-        const unsigned lane = threadIdx.x;
+    // ---- where does this tile's text start: header + the totals of all tiles before it.  The WHOLE block looks back, 256
+    // tiles per step (thread k reads the state of tile - 1 - k): all tiles of a wave start together, so none of the ~600
+    // tiles in front of a tile has an inclusive prefix yet when it gets here, and a 32-wide window walked that distance in
+    // ~18 dependent L2 round trips with seven warps waiting at the barrier (45 % of the kernel's stall samples at 4K)
+    unsigned long long base = (unsigned long long)hdr.len;
+    {
         volatile unsigned long long* st = tile_state;
-        if (lane == 0) {
-            if (tile == 0) st[0] = (LB_INC << 62) | (unsigned long long)(hdr.len + total);
-            else st[tile] = (LB_AGG << 62) | (unsigned long long)total;
-        }
-        unsigned long long base = 0;
-        if (tile == 0) base = (unsigned long long)hdr.len;
-        else {
+        const unsigned lane = threadIdx.x & 31u, wid = threadIdx.x >> 5;
+        if (tile == 0) {
+            if (threadIdx.x == 0) st[0] = (LB_INC << 62) | (base + total);
+        } else {
+            if (threadIdx.x == 0) st[tile] = (LB_AGG << 62) | (unsigned long long)total;
             unsigned long long run = 0;
-            int look = int(tile) - 1;                                  // the window [look - 31, look], lane 0 nearest
+            int look = int(tile) - 1;
             for (;;) {
-                const int idx = look - int(lane);
-                unsigned long long v = 0;
+                const int idx = look - int(threadIdx.x);
+                unsigned long long v = LB_INC << 62;                   // before tile 0: an inclusive prefix of 0
                 if (idx >= 0) { do { v = st[idx]; } while ((v >> 62) == 0ull); }
-                else v = LB_INC << 62;                                 // before tile 0: an inclusive prefix of 0
                 const unsigned inc = __ballot_sync(0xffffffffu, (v >> 62) == LB_INC);
-                const unsigned long long val = v & ((1ull << 62) - 1);
-                // add the aggregates of the lanes nearer than the first inclusive prefix, and that prefix itself
-                const int first = inc ? __ffs(inc) - 1 : 32;
-                unsigned long long mine = int(lane) <= first ? val : 0ull;
+                const int first = inc ? __ffs(inc) - 1 : 32;           // aggregates nearer than the first inclusive prefix + that prefix
+                unsigned long long mine = int(lane) <= first ? (v & ((1ull << 62) - 1)) : 0ull;
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
-                run += mine;
-                if (inc) break;
-                look -= 32;
+                if (lane == 0) { s_part[wid] = mine; s_inc[wid] = inc != 0u; }
+                __syncthreads();
+                bool done = false;
+#pragma unroll
+                for (int w = 0; w < ENC_BLOCK / 32; ++w) if (!done) { run += s_part[w]; done = s_inc[w] != 0; }
+                __syncthreads();                                       // s_part / s_inc are rewritten by the next step
+                if (done) break;
+                look -= ENC_BLOCK;
             }
             base = run;
-            if (lane == 0) { __threadfence(); st[tile] = (LB_INC << 62) | (base + total); }
+            if (threadIdx.x == 0) { __threadfence(); st[tile] = (LB_INC << 62) | (base + total); }
         }
-        if (lane == 0) {
-            s_base = base;
-            if (int(tile) == n_tiles - 1) *total_len = base + total;
-        }
+        if (threadIdx.x == 0 && int(tile) == n_tiles - 1) *total_len = base + total;
     }
-    __syncthreads();
-    char* dst = text + s_base;
+    char* dst = text + base;
     const unsigned mis = unsigned(reinterpret_cast<unsigned long long>(dst) & 15ull);
     unsigned off = mis + local;
     if (p0 < n_pixels) {
