@@ -268,6 +268,15 @@ def main():
     builder_id = rt.BVH_LBVH_GPU if builder == "lbvh" else rt.BVH_SAH_HOST
     ctx = rt.Context(local)
     s, m = rt.scene_rtiow(g, p_diffuse, p_metal)
+    # the caller's world lives in pinned host memory (the end-to-end leg uploads it every step)
+    pins = []
+    def pinned(a):
+        t = torch.empty(a.nbytes, dtype=torch.uint8, pin_memory=True)
+        v = t.numpy().view(a.dtype).reshape(a.shape)
+        v[...] = a
+        pins.append(t)
+        return v
+    s, m = pinned(s), pinned(m)
     ctx.upload_scene(s, m, builder=builder_id)
     cam = rt.camera_rtiow(W, args.spp, DEPTH, scale=g / 11.0)
     n_spheres = len(s)
@@ -445,7 +454,7 @@ def main():
             "e2e": {"value": samples / e2e_ms / 1e3, "unit": "Msamples/s", "ms_per_step": e2e_ms,
                     "h2d_bytes_per_step": int(s.nbytes + m.nbytes + 104),
                     "d2h_bytes_per_step": int(W * H * 3 + (e2e_out["ppm_len"] if e2e_out else 0)),
-                    "api": "rt_upload_scene + rt_render + rt_readback(rgb8 + P3 text) per step; scene from host arrays, results into pinned host buffers"},
+                    "api": "rt_upload_scene + rt_render + rt_readback(rgb8 + P3 text) per step; scene from pinned host arrays, results into pinned host buffers"},
             "gpu_launches": int(launches) * args.steps, "clocks": clocks,
             # where a step's time goes (device-resident leg): rank 0's render kernel (CUDA events inside the library) and what
             # follows it until the frame is resolved on rank 0 -- tiles: wait for the peers' bytes + resolve of rank 0's tiles;

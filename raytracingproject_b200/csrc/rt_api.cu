@@ -11,6 +11,7 @@
 #include <cstring>
 #include <random>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include <nvtx3/nvToolsExt.h>          // header-only: ranges show up in an Nsight Systems timeline, no-ops otherwise
@@ -50,7 +51,18 @@ template <typename T> struct DevBuf {
         if (e == cudaSuccess) n = count;
         return e;
     }
-    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+    // scratch that lives for one call: stream-ordered allocation from the device's memory pool, which keeps freed blocks
+    // (rt_create raises its release threshold), so the 17 temporaries of a 1 M-sphere upload cost no cudaMalloc / cudaFree
+    // after the first call (each of those takes a driver lock that eight ranks of a node fight over)
+    cudaStream_t pool_stream = nullptr; bool pooled = false;
+    cudaError_t scratch(size_t count, cudaStream_t st) {
+        release();
+        if (count == 0) return cudaSuccess;
+        cudaError_t e = cudaMallocAsync(&p, count * sizeof(T), st);
+        if (e == cudaSuccess) { n = count; pooled = true; pool_stream = st; }
+        return e;
+    }
+    void release() { if (p) { if (pooled) cudaFreeAsync(p, pool_stream); else cudaFree(p); } p = nullptr; n = 0; pooled = false; }
     DevBuf() = default;
     DevBuf(const DevBuf&) = delete;
     DevBuf& operator=(const DevBuf&) = delete;
@@ -253,6 +265,14 @@ int rt_create(rt_ctx** out, int device) {
     ctx->smem_optin = prop.sharedMemPerBlockOptin;
     ctx->smem_per_sm = prop.sharedMemPerMultiprocessor;
     for (auto& ev : ctx->ev) cudaEventCreate(&ev);
+    {   // scratch of a call is allocated stream-ordered; freed blocks stay in the device's pool for the next call
+        cudaMemPool_t pool = nullptr;
+        if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess && pool) {
+            unsigned long long keep = ~0ull;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        }
+        cudaGetLastError();
+    }
     ctx->job_counter.resize(1);
     ctx->frame_timeout.resize(1);
     cudaMemset(ctx->frame_timeout.p, 0, sizeof(int));
@@ -320,19 +340,38 @@ extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_s
     // (an error exit must not leave the old counts and root paired with new node / slot data)
     ctx->has_scene = false; ctx->root_ref = RT_SENTINEL; ctx->n_nodes = 0; ctx->n_slots = 0; ctx->n_big = 0;
 
-    for (size_t i = 0; i < n_spheres; ++i) {
-        if (spheres[i].material < 0 || size_t(spheres[i].material) >= n_materials)
-            return fail(ctx, RT_E_INVALID, "rt_upload_scene: sphere material index out of range");
-        const int ty = materials[spheres[i].material].type;
-        if (ty < RT_LAMBERTIAN || ty > RT_DIELECTRIC) return fail(ctx, RT_E_INVALID, "rt_upload_scene: unknown material type");
-    }
-
+    // one pass over the caller's arrays: material indices / types are checked and the outsized spheres found (large worlds:
+    // in parallel over a few host threads -- three serial passes over 1 M spheres were a third of the upload)
     // split: outsized spheres stay out of the tree (tested first, in double)
     // (every ray tests every one of them: at most RT_MAX_BIG, the LARGEST ones; further candidates go into the tree like
     // any sphere -- same hits, float boxes around a huge sphere just prune less -- and are reported in rt_stats.big_in_tree)
     std::vector<int> tree_ids, big_ids;
-    for (size_t i = 0; i < n_spheres; ++i)
-        if (std::fabs(spheres[i].radius) >= big_radius) big_ids.push_back(int(i));
+    {
+        const int nthr = n_spheres >= 65536 ? int(std::min<size_t>(8, std::max(1u, std::thread::hardware_concurrency()))) : 1;
+        std::vector<std::vector<int>> big_of(nthr);
+        std::vector<int> bad(nthr, 0);
+        auto scan = [&](int t) {
+            const size_t lo = n_spheres * size_t(t) / nthr, hi = n_spheres * size_t(t + 1) / nthr;
+            for (size_t i = lo; i < hi; ++i) {
+                const int mi = spheres[i].material;
+                if (mi < 0 || size_t(mi) >= n_materials) { bad[t] = 1; return; }
+                const int ty = materials[mi].type;
+                if (ty < RT_LAMBERTIAN || ty > RT_DIELECTRIC) { bad[t] = 2; return; }
+                if (std::fabs(spheres[i].radius) >= big_radius) big_of[t].push_back(int(i));
+            }
+        };
+        if (nthr == 1) scan(0);
+        else {
+            std::vector<std::thread> th;
+            for (int t = 0; t < nthr; ++t) th.emplace_back(scan, t);
+            for (auto& x : th) x.join();
+        }
+        for (int t = 0; t < nthr; ++t) {
+            if (bad[t] == 1) return fail(ctx, RT_E_INVALID, "rt_upload_scene: sphere material index out of range");
+            if (bad[t] == 2) return fail(ctx, RT_E_INVALID, "rt_upload_scene: unknown material type");
+        }
+        for (int t = 0; t < nthr; ++t) big_ids.insert(big_ids.end(), big_of[t].begin(), big_of[t].end());     // list order
+    }
     int big_in_tree = 0;
     if (big_ids.size() > RT_MAX_BIG) {
         std::vector<int> by_radius = big_ids;
@@ -343,10 +382,11 @@ extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_s
         big_ids.swap(by_radius);
     }
     {
-        size_t k = 0;
+        tree_ids.resize(n_spheres - big_ids.size());
+        size_t k = 0, o = 0;
         for (size_t i = 0; i < n_spheres; ++i) {
             if (k < big_ids.size() && big_ids[k] == int(i)) ++k;
-            else tree_ids.push_back(int(i));
+            else tree_ids[o++] = int(i);
         }
     }
     const int n_tree = int(tree_ids.size());
@@ -378,8 +418,8 @@ extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_s
         // Device path (large scenes): the caller's AoS arrays go to the device as they are; boxes, tree and
         // the SoA slots in leaf order are made there (rt_scene.cu) -- no per-sphere host loop after the split
         DevBuf<rt_sphere> d_sph; DevBuf<rt_material> d_mat; DevBuf<int> d_ids; DevBuf<HostBox> d_boxes; DevBuf<int> d_order;
-        CK(d_sph.resize(n_spheres)); CK(d_mat.resize(n_materials)); CK(d_ids.resize(n_tree));
-        CK(d_boxes.resize(n_tree)); CK(d_order.resize(n_tree)); CK(ctx->nodes.resize(size_t(n_tree - 1) * 4));
+        CK(d_sph.scratch(n_spheres, ctx->stream)); CK(d_mat.scratch(n_materials, ctx->stream)); CK(d_ids.scratch(n_tree, ctx->stream));
+        CK(d_boxes.scratch(n_tree, ctx->stream)); CK(d_order.scratch(n_tree, ctx->stream)); CK(ctx->nodes.resize(size_t(n_tree - 1) * 4));
         CK(cudaMemcpyAsync(d_sph.p, spheres, sizeof(rt_sphere) * n_spheres, cudaMemcpyHostToDevice, ctx->stream));
         CK(cudaMemcpyAsync(d_mat.p, materials, sizeof(rt_material) * n_materials, cudaMemcpyHostToDevice, ctx->stream));
         CK(cudaMemcpyAsync(d_ids.p, tree_ids.data(), sizeof(int) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
@@ -451,7 +491,7 @@ extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_s
     ctx->top_ordered = 0;
     if (ctx->n_nodes > 1 && ctx->root_ref >= 0 && !env_on("RT_NO_TOP_FIRST")) {       // (the env knob is for A/B measurements)
         DevBuf<int> newpos, top_ids; DevBuf<float4> permuted;
-        CK(newpos.resize(ctx->n_nodes)); CK(top_ids.resize(RT_TOP_MAX)); CK(permuted.resize(size_t(ctx->n_nodes) * 4));
+        CK(newpos.scratch(ctx->n_nodes, ctx->stream)); CK(top_ids.scratch(RT_TOP_MAX, ctx->stream)); CK(permuted.scratch(size_t(ctx->n_nodes) * 4, ctx->stream));
         CK(launch_top_first(ctx->nodes.p, ctx->n_nodes, ctx->root_ref, RT_TOP_MAX, newpos.p, top_ids.p, permuted.p, ctx->stream));
         CK(cudaMemcpyAsync(ctx->nodes.p, permuted.p, size_t(ctx->n_nodes) * 64, cudaMemcpyDeviceToDevice, ctx->stream));
         CK(cudaStreamSynchronize(ctx->stream));

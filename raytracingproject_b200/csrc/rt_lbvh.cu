@@ -188,15 +188,17 @@ cudaError_t build_lbvh_gpu(const HostBox* d_boxes, int n, int max_leaf, float4* 
     // ints: left | right | parent_inner | parent_leaf(n) | flags | root_depth
     const size_t ni = size_t(n - 1) * 4 + size_t(n) + 1;
     auto cleanup = [&]() {
-        cudaFree(keys); cudaFree(keys_sorted); cudaFree(vals); cudaFree(vals_sorted); cudaFree(ints); cudaFree(nbox); cudaFree(bounds); cudaFree(tmp); cudaFree(range);
+        // stream-ordered: the device's memory pool keeps the blocks for the next build (rt_create raises its release threshold)
+        void* all[] = { keys, keys_sorted, vals, vals_sorted, ints, nbox, bounds, tmp, range };
+        for (void* q : all) if (q) cudaFreeAsync(q, st);
     };
 #define LB(call) do { e = (call); if (e != cudaSuccess) { cleanup(); return e; } } while (0)
-    LB(cudaMalloc(&keys, sizeof(*keys) * n)); LB(cudaMalloc(&keys_sorted, sizeof(*keys) * n));
-    LB(cudaMalloc(&vals, sizeof(int) * n)); LB(cudaMalloc(&vals_sorted, sizeof(int) * n));
-    LB(cudaMalloc(&ints, sizeof(int) * ni)); LB(cudaMalloc(&nbox, sizeof(NodeBox) * (n - 1))); LB(cudaMalloc(&bounds, sizeof(Bounds)));
-    LB(cudaMalloc(&range, sizeof(int2) * (n - 1)));
+    LB(cudaMallocAsync(&keys, sizeof(*keys) * n, st)); LB(cudaMallocAsync(&keys_sorted, sizeof(*keys) * n, st));
+    LB(cudaMallocAsync(&vals, sizeof(int) * n, st)); LB(cudaMallocAsync(&vals_sorted, sizeof(int) * n, st));
+    LB(cudaMallocAsync(&ints, sizeof(int) * ni, st)); LB(cudaMallocAsync(&nbox, sizeof(NodeBox) * (n - 1), st)); LB(cudaMallocAsync(&bounds, sizeof(Bounds), st));
+    LB(cudaMallocAsync(&range, sizeof(int2) * (n - 1), st));
     LB(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys_sorted, vals, vals_sorted, n, 0, 63, st));
-    LB(cudaMalloc(&tmp, tmp_bytes ? tmp_bytes : 1));
+    LB(cudaMallocAsync(&tmp, tmp_bytes ? tmp_bytes : 1, st));
     int* left = ints; int* right = left + (n - 1); int* parent_inner = right + (n - 1); int* parent_leaf = parent_inner + (n - 1);
     int* flags = parent_leaf + n; int* root_depth = flags + (n - 1);
     LB(cudaMemsetAsync(flags, 0, sizeof(int) * size_t(n), st));          // flags + root_depth
