@@ -813,10 +813,24 @@ extern "C" int rt_readback(rt_ctx* ctx, int spp_total, double* sum_rgb, uint8_t*
     const FrameViews no_views{nullptr, nullptr, 0, 0};
     const bool want_text = ppm || (ppm_len && !ppm);
     // whole frame on this GPU, text wanted, no per-pixel sums: ONE kernel from the accumulation layers to rgb8 + P3 text
-    const bool fused = want_text && !sum_rgb && ctx->tiles.world <= 1 && !env_on("RT_NO_FUSED_ENCODE");
+    // ... unless the float fast path applies (few layers, no peers): then resolve + count in one kernel and the text in a second
+    // one that reads the bytes back from L2 -- no look-back chain between tiles; measured faster at every size (profiles/)
+    const bool two_pass = want_text && !sum_rgb && ctx->tiles.world <= 1 && ctx->precision == RT_F32 &&
+                          fast_f32_eligible(live_slices(ctx), live_peers(ctx)) && !env_on("RT_NO_TWO_PASS_ENCODE");
+    const bool fused = want_text && !sum_rgb && ctx->tiles.world <= 1 && !two_pass && !env_on("RT_NO_FUSED_ENCODE");
     unsigned long long text_len = 0;
     bool waited = false;
-    if (fused) {
+    if (two_pass) {
+        EncodeHeader hdr;
+        hdr.len = std::snprintf(hdr.text, sizeof hdr.text, "P3\n%d %d\n255\n", ctx->W, ctx->H);   // src/camera.h:35
+        const int nb = encode_blocks(npix);
+        CK(ctx->enc_sums.resize(nb + 1)); CK(ctx->enc_offsets.resize(nb + 3));
+        CK(ctx->text.resize(npix * 12 + 64));
+        CK(launch_resolve_count_f32(reinterpret_cast<const float4*>(ctx->accum.p), live_slices(ctx), npix, scale, ctx->rgb8.p, ctx->enc_sums.p, ctx->stream));
+        CK(launch_encode_p3(ctx->rgb8.p, npix, hdr, ctx->enc_sums.p, ctx->enc_offsets.p, ctx->enc_offsets.p + nb + 1, ctx->text.p, ctx->stream, true));
+        launches = 3;
+        CK(cudaMemcpyAsync(&text_len, ctx->enc_offsets.p + nb + 1, sizeof text_len, cudaMemcpyDeviceToHost, ctx->stream));
+    } else if (fused) {
         EncodeHeader hdr;
         hdr.len = std::snprintf(hdr.text, sizeof hdr.text, "P3\n%d %d\n255\n", ctx->W, ctx->H);   // src/camera.h:35
         const int nb = encode_blocks(npix);

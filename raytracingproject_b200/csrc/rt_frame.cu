@@ -25,7 +25,7 @@ __device__ __forceinline__ unsigned char write_color_byte(double sum, double sca
 // below 4e-7 (one rounding of v, the approximate root), i.e. less than 1e-4 absolute, so unless y lies within 5e-4 of an
 // integer its integer part is the reference's; the few channels that do (0.1 %, plus NaN / negative input and exact zeros)
 // take write_color_byte.  The clamp to 0.999 only matters through its byte, 255 = int(255.744).
-__device__ __forceinline__ float sqrt_approx(float x) { float r; asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float sqrt_approx(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }   // ftz: a denormal argument is a byte 0 either way
 __device__ __forceinline__ unsigned char write_color_byte_fast(double sum, double scale, bool exact) {
     const float y = 256.0f * sqrt_approx(float(sum * scale));
     if (exact || !(fabsf(y - rintf(y)) >= 5e-4f)) return write_color_byte(sum, scale);      // near a byte boundary, or NaN
@@ -111,6 +111,123 @@ __global__ void resolve_kernel(const Q* __restrict__ accum, int slices, PeerList
     }
 }
 
+// ------------------------------------------------- float fast paths (few layers, no peers) --
+// A float buffer with at most RT_FAST_LAYERS layers (every frame after rt_fold_slices, every short frame): the layers are
+// summed in FLOAT and the byte comes from y = 256 * sqrt.approx(sum * scale): every step carries a relative error below
+// 1e-7, y an absolute one below 1.5e-4, so unless y lies within RT_FAST_MARGIN of an integer its integer part is the
+// reference's byte.  The channels that do (0.05 %), NaN and negative input take the reference arithmetic in double on the
+// exact sum (write_color_byte, one copy of the code, driven by a bit mask).  No double adds, no conversions: the general
+// kernels spend more issue slots on those than on memory (ncu: 42 % issue utilisation at 1.05 TB/s on a 4K frame).
+#define RT_FAST_LAYERS 8
+#define RT_FAST_MARGIN 2.5e-4f
+
+// bytes of pixels p0 .. p0+3 packed little-endian into w[0..2] (= the 12 bytes of rgb8 + 3 * p0); np = how many exist
+__device__ __forceinline__ void pixels4_bytes_f32(const float4* __restrict__ accum, int slices, size_t n_pixels, size_t p0, int np,
+                                                  double scale, unsigned w[3]) {
+    float s[4][4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) s[k][0] = s[k][1] = s[k][2] = s[k][3] = 0.0f;
+    for (int sl = 0; sl < slices; ++sl) {
+        const float4* src = accum + size_t(sl) * n_pixels + p0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) if (k < np) { const float4 v = src[k]; s[k][0] += v.x; s[k][1] += v.y; s[k][2] += v.z; s[k][3] += v.w; }
+    }
+    unsigned need = 0u;
+    w[0] = w[1] = w[2] = 0u;
+    // y = 256 * sqrt(sum * scale) = sqrt(sum * (65536 * scale)), clamped to [0.25, 255.5]: below 0.5 the byte is 0 and from
+    // 255 on it is 255 whatever the rounding (0.999 * 256 = 255.74, src/color.h:31), and neither clamp value is near an integer;
+    // a NaN or negative sum becomes 0.25 -> byte 0, which is what write_color_byte makes of it
+    const bool fixed = scale > 0.0;
+    const float sc_fixed = float(scale * 65536.0);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        if (k < np) {
+            float sc = sc_fixed;
+            if (!fixed) sc = 65536.0f / s[k][3];
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                const float y = fminf(fmaxf(sqrt_approx(s[k][c] * sc), 0.25f), 255.5f);
+                const float r = (y + 12582912.0f) - 12582912.0f;               // nearest integer for 0 <= y < 2^22
+                const int at = 3 * k + c;
+                w[at >> 2] |= unsigned(int(y)) << (8 * (at & 3));
+                if (!(fabsf(y - r) >= RT_FAST_MARGIN)) need |= 1u << at;
+            }
+        }
+    }
+    while (need) {                                                              // the reference's arithmetic on the exact sum
+        const int at = __ffs(need) - 1;
+        need &= need - 1u;
+        const int k = at / 3, c = at - 3 * k;
+        double sum = 0.0, cnt = 0.0;
+        for (int sl = 0; sl < slices; ++sl) {
+            const float4 v = accum[size_t(sl) * n_pixels + p0 + k];
+            sum += double(c == 0 ? v.x : (c == 1 ? v.y : v.z)); cnt += double(v.w);
+        }
+        const unsigned b = write_color_byte(sum, scale > 0.0 ? scale : 1.0 / cnt);
+        const unsigned sh = 8u * (at & 3), m = ~(0xffu << sh);
+        if (at < 4) w[0] = (w[0] & m) | (b << sh); else if (at < 8) w[1] = (w[1] & m) | (b << sh); else w[2] = (w[2] & m) | (b << sh);
+    }
+}
+
+__device__ __forceinline__ void store_bytes12(unsigned char* __restrict__ rgb8, size_t p0, int np, const unsigned w[3]) {
+    if (np == 4) {
+        unsigned* dst = reinterpret_cast<unsigned*>(rgb8 + 3 * p0);             // p0 % 4 == 0: 12-byte groups, 4-aligned
+        dst[0] = w[0]; dst[1] = w[1]; dst[2] = w[2];
+    } else {
+        for (int i = 0; i < 3 * np; ++i) rgb8[3 * p0 + i] = (unsigned char)(w[i >> 2] >> (8 * (i & 3)));
+    }
+}
+
+// bytes (+ optionally the number of P3 characters of every block's 1024 pixels = one tile of the encoder, so that the encoder
+// needs no counting pass): 16 B per layer read, 3 B written per pixel, one thread = 4 pixels
+__global__ void __launch_bounds__(ENC_BLOCK) resolve_bytes_f32_kernel(const float4* __restrict__ accum, int slices, size_t n_pixels, double scale,
+                                                                      unsigned char* __restrict__ rgb8, unsigned* __restrict__ block_sums) {
+    __shared__ unsigned warp_sums[ENC_BLOCK / 32];
+    const size_t p0 = (size_t(blockIdx.x) * ENC_BLOCK + threadIdx.x) * 4;
+    const int np = p0 < n_pixels ? int(min(size_t(4), n_pixels - p0)) : 0;
+    unsigned len = 0;
+    if (np > 0) {
+        unsigned w[3];
+        pixels4_bytes_f32(accum, slices, n_pixels, p0, np, scale, w);
+        store_bytes12(rgb8, p0, np, w);
+        if (block_sums) {
+#pragma unroll
+            for (int i = 0; i < 12; ++i) if (i < 3 * np) { const unsigned v = (w[i >> 2] >> (8 * (i & 3))) & 0xffu; len += 1u + (v >= 10u) + (v >= 100u); }
+            len += 3u * unsigned(np);                                           // two blanks and the newline of every line
+        }
+    }
+    if (block_sums) {                                                           // block-uniform
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) len += __shfl_xor_sync(0xffffffffu, len, o);
+        if ((threadIdx.x & 31) == 0) warp_sums[threadIdx.x >> 5] = len;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned t = 0;
+#pragma unroll
+            for (int q = 0; q < ENC_BLOCK / 32; ++q) t += warp_sums[q];
+            block_sums[blockIdx.x] = t;
+        }
+    }
+}
+
+// digits of a byte for the text: entry v = its decimal characters in the low bytes (first character lowest) | count << 24
+__device__ __forceinline__ unsigned digits_entry(unsigned v) {
+    const unsigned h = v / 100u, t = (v / 10u) % 10u, o = v % 10u;
+    if (v >= 100u) return ('0' + h) | (('0' + t) << 8) | (('0' + o) << 16) | (3u << 24);
+    if (v >= 10u) return ('0' + t) | (('0' + o) << 8) | (2u << 24);
+    return ('0' + o) | (1u << 24);
+}
+// one number and the separator that follows it: at most four byte stores, no division, no branch on the digit count
+__device__ __forceinline__ unsigned put_entry(char* dst, unsigned e, unsigned sep) {
+    const unsigned n = e >> 24;
+    const unsigned word = (e & 0xffffffu) | (sep << (8u * n));
+    dst[0] = char(word);
+    dst[1] = char(word >> 8);
+    if (n >= 2u) dst[2] = char(word >> 16);
+    if (n >= 3u) dst[3] = char(word >> 24);
+    return n + 1u;
+}
+
 template <typename Q>
 cudaError_t launch_resolve(const Q* accum, int slices, const PeerList& peers, size_t n_pixels, double scale,
                            double* sum_out, unsigned char* rgb8, Q* reduced_out, cudaStream_t st, const FrameViews& views, const TileOwner& owner) {
@@ -118,6 +235,11 @@ cudaError_t launch_resolve(const Q* accum, int slices, const PeerList& peers, si
     const size_t threads = (n_pixels + 3) / 4;
     FrameViews v = views;
     v.exact = frame_exact();
+    if (sizeof(Q) == sizeof(float4) && !v.exact && rgb8 && !sum_out && !reduced_out && !v.pfm && !v.rgba8 && owner.world <= 1 && peers.n == 0 &&
+        slices <= RT_FAST_LAYERS) {
+        resolve_bytes_f32_kernel<<<unsigned((threads + ENC_BLOCK - 1) / ENC_BLOCK), ENC_BLOCK, 0, st>>>(reinterpret_cast<const float4*>(accum), slices, n_pixels, scale, rgb8, nullptr);
+        return cudaGetLastError();
+    }
     resolve_kernel<Q><<<unsigned((threads + 255) / 256), 256, 0, st>>>(accum, slices, peers, n_pixels, scale, sum_out, rgb8, reduced_out, v, owner);
     return cudaGetLastError();
 }
@@ -216,11 +338,12 @@ __global__ void __launch_bounds__(ENC_BLOCK) encode_count_kernel(const unsigned 
 // exclusive scan of block_sums (64-bit offsets out), single block: every thread takes one contiguous chunk, all its loads in
 // flight at once (the first version walked the array 256 entries at a time, one dependent load + three barriers per step:
 // 27 us at 4K, as long as the pass that writes 95 MB of text), then one scan over the 256 chunk totals
-__global__ void __launch_bounds__(ENC_BLOCK) encode_scan_kernel(const unsigned* __restrict__ block_sums, int n_blocks,
+#define ENC_SCAN_BLOCK 1024             // 8100 tiles of a 4K frame: 8 entries per thread (256 threads took 18 us, all latency)
+__global__ void __launch_bounds__(ENC_SCAN_BLOCK) encode_scan_kernel(const unsigned* __restrict__ block_sums, int n_blocks,
                                                                   unsigned long long* __restrict__ block_offsets, unsigned long long header_len,
                                                                   unsigned long long* __restrict__ total_len) {
-    __shared__ unsigned long long warp_tot[ENC_BLOCK / 32];
-    const int per = (n_blocks + ENC_BLOCK - 1) / ENC_BLOCK;
+    __shared__ unsigned long long warp_tot[ENC_SCAN_BLOCK / 32];
+    const int per = (n_blocks + ENC_SCAN_BLOCK - 1) / ENC_SCAN_BLOCK;
     const int lo = min(n_blocks, int(threadIdx.x) * per), hi = min(n_blocks, lo + per);
     unsigned long long mine = 0;
     for (int i = lo; i < hi; ++i) mine += block_sums[i];
@@ -234,7 +357,7 @@ __global__ void __launch_bounds__(ENC_BLOCK) encode_scan_kernel(const unsigned* 
     for (int w = 0; w < wid; ++w) base += warp_tot[w];
     unsigned long long run = base + x - mine;                       // exclusive prefix of this thread's chunk
     for (int i = lo; i < hi; ++i) { block_offsets[i] = run; run += block_sums[i]; }
-    if (threadIdx.x == ENC_BLOCK - 1) *total_len = base + x;
+    if (threadIdx.x == ENC_SCAN_BLOCK - 1) *total_len = base + x;
 }
 
 // The block's text is staged in shared memory at the SAME 16-byte misalignment its destination has, so that
@@ -245,27 +368,24 @@ __global__ void __launch_bounds__(ENC_BLOCK) encode_write_kernel(const unsigned 
                                                                    char* __restrict__ text, EncodeHeader hdr) {
     __shared__ unsigned warp_sums[ENC_BLOCK / 32];
     __shared__ __align__(16) char stage[ENC_TILE * 12 + 16];
+    __shared__ unsigned s_lut[256];
+    s_lut[threadIdx.x] = digits_entry(threadIdx.x);                             // ENC_BLOCK == 256
     const size_t p0 = size_t(blockIdx.x) * ENC_TILE + size_t(threadIdx.x) * ENC_PPT;
+    const int np = p0 < n_pixels ? int(min(size_t(ENC_PPT), n_pixels - p0)) : 0;
     unsigned char px[12];
-    unsigned len = 0;
-    if (p0 < n_pixels) {
-        load_pixels(rgb8, p0, px);
+    if (np > 0) load_pixels(rgb8, p0, px);
+    __syncthreads();
+    unsigned e[12];                                                             // characters | count << 24 of every number
+    unsigned len = 3u * unsigned(np);                                           // two blanks and the newline of every line
 #pragma unroll
-        for (int k = 0; k < ENC_PPT; ++k) if (p0 + k < n_pixels) len += line_len(px + 3 * k);
-    }
+    for (int i = 0; i < 12; ++i) { e[i] = i < 3 * np ? s_lut[px[i]] : 0u; len += e[i] >> 24; }
     unsigned total;
     char* dst = text + block_offsets[blockIdx.x];
     const unsigned mis = unsigned(reinterpret_cast<unsigned long long>(dst) & 15ull);
     unsigned off = mis + block_exclusive_scan(len, warp_sums, total);
-    if (p0 < n_pixels) {
 #pragma unroll
-        for (int k = 0; k < ENC_PPT; ++k) {
-            if (p0 + k >= n_pixels) break;
-            off += put_number(stage + off, px[3 * k + 0]); stage[off++] = ' ';
-            off += put_number(stage + off, px[3 * k + 1]); stage[off++] = ' ';
-            off += put_number(stage + off, px[3 * k + 2]); stage[off++] = '\n';
-        }
-    }
+    for (int i = 0; i < 12; ++i)
+        if (i < 3 * np) off += put_entry(stage + off, e[i], (i % 3) == 2 ? unsigned('\n') : unsigned(' '));
     __syncthreads();
     const unsigned begin = mis, end = mis + total;
     const unsigned c0 = (begin + 15u) >> 4, c1 = end >> 4;              // full 16-byte chunks [c0, c1)
@@ -433,11 +553,19 @@ template cudaError_t launch_resolve_encode<float4>(const float4*, int, const Pee
 template cudaError_t launch_resolve_encode<double4>(const double4*, int, const PeerList&, size_t, double, unsigned char*, char*, const EncodeHeader&, unsigned long long*, unsigned long long*, cudaStream_t);
 
 
-cudaError_t launch_encode_p3(const unsigned char* rgb8, size_t n_pixels, const EncodeHeader& hdr, unsigned* block_sums,
-                             unsigned long long* block_offsets, unsigned long long* total_len, char* text, cudaStream_t st) {
+bool fast_f32_eligible(int slices, const PeerList& peers) { return slices <= RT_FAST_LAYERS && peers.n == 0 && !frame_exact(); }
+
+cudaError_t launch_resolve_count_f32(const float4* accum, int slices, size_t n_pixels, double scale, unsigned char* rgb8, unsigned* block_sums, cudaStream_t st) {
     const int nb = encode_blocks(n_pixels);
-    if (nb > 0) encode_count_kernel<<<nb, ENC_BLOCK, 0, st>>>(rgb8, n_pixels, block_sums);
-    encode_scan_kernel<<<1, ENC_BLOCK, 0, st>>>(block_sums, nb, block_offsets, (unsigned long long)hdr.len, total_len);
+    if (nb > 0) resolve_bytes_f32_kernel<<<nb, ENC_BLOCK, 0, st>>>(accum, slices, n_pixels, scale, rgb8, block_sums);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_encode_p3(const unsigned char* rgb8, size_t n_pixels, const EncodeHeader& hdr, unsigned* block_sums,
+                             unsigned long long* block_offsets, unsigned long long* total_len, char* text, cudaStream_t st, bool counted) {
+    const int nb = encode_blocks(n_pixels);
+    if (nb > 0 && !counted) encode_count_kernel<<<nb, ENC_BLOCK, 0, st>>>(rgb8, n_pixels, block_sums);
+    encode_scan_kernel<<<1, ENC_SCAN_BLOCK, 0, st>>>(block_sums, nb, block_offsets, (unsigned long long)hdr.len, total_len);
     if (nb > 0) encode_write_kernel<<<nb, ENC_BLOCK, 0, st>>>(rgb8, n_pixels, block_offsets, text, hdr);
     return cudaGetLastError();
 }

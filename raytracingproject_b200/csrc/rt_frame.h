@@ -50,7 +50,13 @@ template <typename Q>
 cudaError_t launch_resolve_encode(const Q* accum, int slices, const PeerList& peers, size_t n_pixels, double scale, unsigned char* rgb8,
                                   char* text, const EncodeHeader& hdr, unsigned long long* tile_state, unsigned long long* total_len, cudaStream_t st);
 // rgb8 must be readable up to 12 bytes past its last pixel (32-bit loads of 4-pixel groups)
+// counted: block_sums already holds the character count of every 1024-pixel tile (launch_resolve_count_f32)
 cudaError_t launch_encode_p3(const unsigned char* rgb8, size_t n_pixels, const EncodeHeader& hdr, unsigned* block_sums,
-                             unsigned long long* block_offsets, unsigned long long* total_len, char* text, cudaStream_t st);
+                             unsigned long long* block_offsets, unsigned long long* total_len, char* text, cudaStream_t st, bool counted = false);
+// Float buffers with few layers and no peers: the bytes come from float sums + sqrt.approx, exact write_color only near a byte
+// boundary (same bytes; rt_frame.cu).  launch_resolve takes that path by itself; this form also leaves the P3 character
+// count of every tile in block_sums, so that resolve + launch_encode_p3(counted) is two passes, the second one over L2-resident bytes.
+bool fast_f32_eligible(int slices, const PeerList& peers);
+cudaError_t launch_resolve_count_f32(const float4* accum, int slices, size_t n_pixels, double scale, unsigned char* rgb8, unsigned* block_sums, cudaStream_t st);
 
 }  // namespace rt
