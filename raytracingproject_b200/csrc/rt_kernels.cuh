@@ -152,7 +152,7 @@ render_sched_kernel(const RenderParams<T> p) {
     const int njobs = p.tiles_x * p.tiles_y * p.slices;
     const int th_s = p.th_s, th_l = p.th_l;
     unsigned long long my_rays = 0;
-    int stack[RT_STACK];
+    StackEntry stack[RT_STACK];
 
     for (;;) {
         int job = 0;
@@ -171,7 +171,7 @@ render_sched_kernel(const RenderParams<T> p) {
         double acc_r = 0.0, acc_g = 0.0, acc_b = 0.0;
         Ray<T> ray; ray.o = mk<T>(0, 0, 0); ray.d = mk<T>(0, 0, 1); ray.tm = 0;
         Vec<T> thr = mk<T>(1, 1, 1);
-        Trav<T> tv; tv.cur = RT_SENTINEL; tv.sp = 0; tv.tos = RT_SENTINEL; tv.tbest = 0; tv.best_id = -1; tv.best_slot = -1; tv.qa = 1; slab_clear<T>(tv.slab);
+        Trav<T> tv; tv.cur = RT_SENTINEL; tv.sp = 0; tv.tos = RT_SENTINEL; tv.tos_t = -INFINITY; tv.tbest = 0; tv.best_id = -1; tv.best_slot = -1; tv.qa = 1; slab_clear<T>(tv.slab);
         int depth = 0;                       // bounces left for the current path; 0 = start the next sample
         bool alive = in_image && s < s_end;
 

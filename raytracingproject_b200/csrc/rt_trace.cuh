@@ -11,6 +11,12 @@ namespace rt {
 
 #define RT_SENTINEL ((int)0x80000000)
 #define RT_STACK 64
+#ifndef RT_STACK_T
+#define RT_STACK_T 0                   // 1: stack entries carry the entry distance of their box, so that a popped node which the closest hit found meanwhile
+#endif                                 // has put out of reach is dropped at the pop instead of costing a node visit.  Parity-clean, but measured 1.8 % (C3) to
+                                       // 4-6 % (C5) SLOWER (profiles/r2_stack_entry_distance_ab.txt): such pops are rare here -- a far child is only pushed if
+                                       // its box is within the t_best of that moment, which the BIG stage has already set to the ground hit -- and the 64-bit
+                                       // entries + the pop loop cost more than the few visits saved.  make ST=1 builds it
 #ifndef RT_PREFETCH_FAR
 #define RT_PREFETCH_FAR 0               // tree in global memory: prefetch the pushed far child into L1 (1: its first 32 bytes, 2: all 64)
 #endif
@@ -118,6 +124,12 @@ __device__ __forceinline__ bool leaf_sphere(const double4& a, const double4& b, 
 // node visit, leaf visit -- so that the render kernel can schedule them per warp (rt_kernels.cuh);
 // trace_closest() below simply runs them to completion for one ray.
 //   cur >= 0: inner node to visit; cur < 0 and != RT_SENTINEL: leaf to test; RT_SENTINEL: finished.
+#if RT_STACK_T
+typedef int2 StackEntry;     // (child ref, float bits of a lower bound of the distance at which the ray enters the child's box)
+#else
+typedef int StackEntry;
+#endif
+
 template <typename T> struct Trav {
     SlabRay<T> slab;         // per-ray constants of the box test
     T qa;                    // fast mode: 1 / |d|^2; parity mode: |d|^2 (what each sphere test wants)
@@ -125,7 +137,53 @@ template <typename T> struct Trav {
     int best_id, best_slot;  // list index (tie rule) and slot (tree slot, or n_slots + k for big sphere k)
     int cur, sp;
     int tos;                 // copy of stack[sp - 1]: a pop takes it from the register and reloads it off the critical path
+    float tos_t;             // RT_STACK_T: the entry distance stored with it (-inf below the bottom of the stack)
 };
+
+// The far child of a visit waits on the stack while the near one is walked; by the time it is popped the closest hit has
+// often moved in front of its box (a ray that hits a sphere in its first leaf leaves 3-4 such entries behind).  Without the
+// stored distance each of them cost a whole node visit -- both of ITS children fail against the new t_best -- before the next
+// pop.  The test at the pop is the box test of the visit that pushed the entry, repeated with today's t_best (same slack in
+// fast mode; in parity mode the stored float is rounded down and t_best up), so nothing that can hold a closer hit, or an equal
+// one of a lower list index, is dropped: hits, images and ray counts are unchanged.
+__device__ __forceinline__ float cull_limit(const Trav<float>& tv) { return fmaf(tv.tbest, 1.000001f, tv.slab.delta); }
+__device__ __forceinline__ float cull_limit(const Trav<double>& tv) { return __double2float_ru(tv.tbest); }
+__device__ __forceinline__ float entry_bound(float t) { return t; }
+__device__ __forceinline__ float entry_bound(double t) { return __double2float_rd(t); }
+
+template <typename T>
+__device__ __forceinline__ void trav_push(Trav<T>& tv, StackEntry* stack, int ref, T t_entry) {
+#if RT_STACK_T
+    const float t = entry_bound(t_entry);
+    stack[tv.sp++] = make_int2(ref, __float_as_int(t)); tv.tos = ref; tv.tos_t = t;
+#else
+    (void)t_entry;
+    stack[tv.sp++] = ref; tv.tos = ref;
+#endif
+}
+
+// next node / leaf to walk, or RT_SENTINEL when the stack is empty (the top of the stack is in a register)
+template <typename T>
+__device__ __forceinline__ int trav_pop(Trav<T>& tv, const StackEntry* stack) {
+#if RT_STACK_T
+    const float lim = cull_limit(tv);
+    int next;
+    for (;;) {
+        next = tv.tos;
+        const float t = tv.tos_t;
+        if (tv.sp > 0) --tv.sp;
+        if (tv.sp > 0) { const StackEntry e = stack[tv.sp - 1]; tv.tos = e.x; tv.tos_t = __int_as_float(e.y); }
+        else { tv.tos = RT_SENTINEL; tv.tos_t = -INFINITY; }
+        if (!(t > lim)) break;               // (the sentinel carries -inf)
+    }
+    return next;
+#else
+    const int next = tv.tos;
+    if (tv.sp > 0) --tv.sp;
+    tv.tos = tv.sp > 0 ? stack[tv.sp - 1] : RT_SENTINEL;
+    return next;
+#endif
+}
 
 // big spheres first, in double in both modes (the r = 1000 ground sphere): a tight t_max for the
 // tree and no float cancellation in |oc|^2 - r^2
@@ -184,7 +242,7 @@ __device__ __forceinline__ void trav_setup(const SceneView<T>& sv, const Ray<T>&
     const T a_len2 = len2(r.d);
     tv.qa = sizeof(T) == 4 ? T(1) / a_len2 : a_len2;
     slab_setup(r, tv.slab);
-    tv.cur = sv.root_ref; tv.sp = 0; tv.tos = RT_SENTINEL;
+    tv.cur = sv.root_ref; tv.sp = 0; tv.tos = RT_SENTINEL; tv.tos_t = -INFINITY;
 }
 
 template <typename T>
@@ -195,7 +253,7 @@ __device__ __forceinline__ void trav_init(const SceneView<T>& sv, const Ray<T>& 
 
 // one inner node: both child boxes, near child next, far child pushed (src/bvh.h:16-24 contract)
 template <typename T>
-__device__ __forceinline__ void trav_node(const float4* __restrict__ nodes, const Ray<T>& r, T tmin, Trav<T>& tv, int* stack) {
+__device__ __forceinline__ void trav_node(const float4* __restrict__ nodes, const Ray<T>& r, T tmin, Trav<T>& tv, StackEntry* stack) {
     const int cur = tv.cur;
     const float4 q0 = nodes[4 * cur + 0], q1 = nodes[4 * cur + 1], q2 = nodes[4 * cur + 2], q3 = nodes[4 * cur + 3];
     T tl, tr;
@@ -206,13 +264,9 @@ __device__ __forceinline__ void trav_node(const float4* __restrict__ nodes, cons
     // blocks instead of a four-way branch, so the lanes of a warp stay together through the step
     const bool left_first = !hr || (hl && tl <= tr);
     const int near = left_first ? cl : cr, far = left_first ? cr : cl;
-    if (hl && hr && tv.sp < RT_STACK) { stack[tv.sp++] = far; tv.tos = far; }
+    if (hl && hr && tv.sp < RT_STACK) trav_push<T>(tv, stack, far, left_first ? tr : tl);
     int next = near;
-    if (!(hl || hr)) {                      // pop: the top of the stack is in a register (RT_SENTINEL when the stack is empty)
-        next = tv.tos;
-        if (tv.sp > 0) --tv.sp;
-        tv.tos = tv.sp > 0 ? stack[tv.sp - 1] : RT_SENTINEL;
-    }
+    if (!(hl || hr)) next = trav_pop<T>(tv, stack);
     tv.cur = next;
 }
 
@@ -221,7 +275,7 @@ __device__ __forceinline__ void trav_node(const float4* __restrict__ nodes, cons
 // (LDS latency), the rest from L2 / HBM.  One generic-address load path for both, no divergence.
 template <typename T>
 __device__ __forceinline__ void trav_node_top(const float4* __restrict__ nodes, const float4* top, int n_top, const Ray<T>& r, T tmin,
-                                              Trav<T>& tv, int* stack) {
+                                              Trav<T>& tv, StackEntry* stack) {
     const int cur = tv.cur;
     const float4* rec = (cur < n_top ? top : nodes) + 4 * size_t(cur);
     const float4 q0 = rec[0], q1 = rec[1], q2 = rec[2], q3 = rec[3];
@@ -240,13 +294,9 @@ __device__ __forceinline__ void trav_node_top(const float4* __restrict__ nodes, 
         if (RT_PREFETCH_FAR >= 2) asm volatile("prefetch.global.L1 [%0];" :: "l"(f + 2));
     }
 #endif
-    if (hl && hr && tv.sp < RT_STACK) { stack[tv.sp++] = far; tv.tos = far; }
+    if (hl && hr && tv.sp < RT_STACK) trav_push<T>(tv, stack, far, left_first ? tr : tl);
     int next = near;
-    if (!(hl || hr)) {
-        next = tv.tos;
-        if (tv.sp > 0) --tv.sp;
-        tv.tos = tv.sp > 0 ? stack[tv.sp - 1] : RT_SENTINEL;
-    }
+    if (!(hl || hr)) next = trav_pop<T>(tv, stack);
     tv.cur = next;
 }
 
@@ -289,7 +339,7 @@ __device__ __forceinline__ void node4_boxes(const float4* q, const SlabRay<doubl
 
 // one 4-wide node: the children the ray enters, nearest next, the others pushed farthest first
 template <typename T>
-__device__ __forceinline__ void trav_node4(const float4* __restrict__ nodes4, const Ray<T>& r, T tmin, Trav<T>& tv, int* stack) {
+__device__ __forceinline__ void trav_node4(const float4* __restrict__ nodes4, const Ray<T>& r, T tmin, Trav<T>& tv, StackEntry* stack) {
     const float4* rec = nodes4 + 8 * size_t(tv.cur);
     float4 q[7];
 #pragma unroll
@@ -307,23 +357,20 @@ __device__ __forceinline__ void trav_node4(const float4* __restrict__ nodes4, co
     RT_CSWAP(0, 1) RT_CSWAP(2, 3) RT_CSWAP(0, 2) RT_CSWAP(1, 3) RT_CSWAP(1, 2)
 #undef RT_CSWAP
 #define RT_REF_OF(k) ((key[k] & 2) ? ((key[k] & 1) ? ref[3] : ref[2]) : ((key[k] & 1) ? ref[1] : ref[0]))
+#define RT_TN_OF(k) ((key[k] & 2) ? ((key[k] & 1) ? tn[3] : tn[2]) : ((key[k] & 1) ? tn[1] : tn[0]))
 #pragma unroll
     for (int k = 3; k >= 1; --k)
-        if (key[k] != 0x7fffffff && tv.sp < RT_STACK) { const int f = RT_REF_OF(k); stack[tv.sp++] = f; tv.tos = f; }
-    if (key[0] != 0x7fffffff) {
-        tv.cur = RT_REF_OF(0);
-    } else {                                // nothing entered: pop (top of the stack is in a register)
-        tv.cur = tv.tos;
-        if (tv.sp > 0) --tv.sp;
-        tv.tos = tv.sp > 0 ? stack[tv.sp - 1] : RT_SENTINEL;
-    }
+        if (key[k] != 0x7fffffff && tv.sp < RT_STACK) trav_push<T>(tv, stack, RT_REF_OF(k), RT_TN_OF(k));
+    if (key[0] != 0x7fffffff) tv.cur = RT_REF_OF(0);
+    else tv.cur = trav_pop<T>(tv, stack);       // nothing entered
+#undef RT_TN_OF
 #undef RT_REF_OF
 }
 
 // one leaf: its 1..8 sphere slots
 template <typename T>
 __device__ __forceinline__ void trav_leaf(const typename Quad<T>::type* __restrict__ sa, const typename Quad<T>::type* __restrict__ sb,
-                                          const int* __restrict__ meta, const Ray<T>& r, T tmin, Trav<T>& tv, const int* stack) {
+                                          const int* __restrict__ meta, const Ray<T>& r, T tmin, Trav<T>& tv, const StackEntry* stack) {
     const int leaf = ~tv.cur;
     const int first = leaf >> 3, count = (leaf & 7) + 1;
     for (int k = 0; k < count; ++k) {
@@ -335,9 +382,7 @@ __device__ __forceinline__ void trav_leaf(const typename Quad<T>::type* __restri
             tv.tbest = t; tv.best_id = id; tv.best_slot = slot;
         }
     }
-    tv.cur = tv.tos;
-    if (tv.sp > 0) --tv.sp;
-    tv.tos = tv.sp > 0 ? stack[tv.sp - 1] : RT_SENTINEL;
+    tv.cur = trav_pop<T>(tv, stack);
 }
 
 // Closest hit in (tmin, tmax).  slot_out: tree slot, n_slots + k for big sphere k, or -1.
@@ -349,7 +394,7 @@ __device__ __forceinline__ void trace_closest(const SceneView<T>& sv, const floa
                                               const int* __restrict__ meta,
                                               const Ray<T>& r, T tmin, T tmax, T& t_out, int& slot_out) {
     Trav<T> tv;
-    int stack[RT_STACK];
+    StackEntry stack[RT_STACK];
     trav_init<T>(sv, r, tmin, tmax, tv);
     if (sv.nodes4 && nodes == sv.nodes) {          // tree in global memory with 4-wide records
         while (tv.cur != RT_SENTINEL) {

@@ -136,7 +136,7 @@ render_pool_kernel(const RenderParams<T> p) {
     unsigned long long wt_first = 0, wt_exhausted = 0, wt_rounds = 0, wt_nq = 0, wt_rounds_tail = 0, wt_nq_tail = 0;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(wt_first));
 #endif
-    int stack[RT_STACK];
+    StackEntry stack[RT_STACK];
 
     // Ring state (warp-uniform).  Every slot goes through every job of its warp, in order: `newest` is the
     // entry fetched last, byte e of `joined` the number of slots that have moved into entry e's job.  A slot
@@ -419,7 +419,7 @@ render_pool_kernel(const RenderParams<T> p) {
             {
                 int head = 0, pid = 0;
                 Ray<T> ray; ray.o = mk<T>(0, 0, 0); ray.d = mk<T>(0, 0, 1); ray.tm = 0;
-                Trav<T> tv; tv.cur = RT_SENTINEL; tv.sp = 0; tv.tos = RT_SENTINEL; tv.tbest = 0; tv.best_id = -1; tv.best_slot = -1; tv.qa = 1; slab_clear<T>(tv.slab);
+                Trav<T> tv; tv.cur = RT_SENTINEL; tv.sp = 0; tv.tos = RT_SENTINEL; tv.tos_t = -INFINITY; tv.tbest = 0; tv.best_id = -1; tv.best_slot = -1; tv.qa = 1; slab_clear<T>(tv.slab);
                 for (;;) {
                     const bool isN = tv.cur >= 0;
                     const bool isP = tv.cur == RT_SENTINEL;
