@@ -122,12 +122,13 @@ template <typename T, typename R> __device__ __forceinline__ Vec<T> random_in_un
 // draw site -- the triplets (z, y, x) of iteration i are draws 3i..3i+2, so block b completes one
 // triplet (b % 3 == 0, 1) or two (b % 3 == 2).  Smaller code (the kernels are I-cache bound) and
 // the lanes of a warp stay converged on the expensive part.
-template <typename T, typename R> __device__ __forceinline__ Vec<T> random_in_unit_sphere_from0(R& rng) {
+// BLOCK0_READY: the caller has generated block 0 already (scatter does, for opaque and glass hits in one go).
+template <typename T, typename R, bool BLOCK0_READY = false> __device__ __forceinline__ Vec<T> random_in_unit_sphere_from0(R& rng) {
     uint32_t c0 = 0, c1 = 0;
     int nc = 0;
     Vec<T> v = mk<T>(T(0), T(0), T(0));
     for (uint32_t b = 0;; ++b) {
-        rng.generate(b);
+        if (!BLOCK0_READY || b > 0u) rng.generate(b);
         const uint32_t w0 = rng.w0 >> 8, w1 = rng.w1 >> 8, w2 = rng.w2 >> 8, w3 = rng.w3 >> 8;
         if (nc == 0) {
             if (ball_accept<T>(w0, w1, w2, v)) break;
@@ -297,10 +298,14 @@ template <typename T> __device__ __forceinline__ T reflectance(T cosine, T ref_i
 
 template <typename T, typename R> __device__ __forceinline__ bool scatter(int type, Vec<T> albedo, T param, const Vec<T>& d_in, const Vec<T>& n,
                                                                           bool front_face, R& rng, Vec<T>& attenuation, Vec<T>& d_out) {
+    // block 0 of the stage's stream for every lane at once: the first ball attempt of an opaque hit, the one uniform of a glass
+    // hit (drawn below only if the ray can refract; generating it commits to nothing, the stream is a pure function of its
+    // counter).  In a batch that mixes the two, glass lanes used to run their own ten rounds at 2-3 lanes.
+    rng.generate(0u);
     if (type < 2) {
         // both opaque materials draw one point in the unit ball first (3k draws, metal even when
         // fuzz == 0, :38); the sampler is instantiated once for the two of them
-        const Vec<T> ball = random_in_unit_sphere_from0<T, R>(rng);
+        const Vec<T> ball = random_in_unit_sphere_from0<T, R, true>(rng);
         attenuation = albedo;
         if (type == 0) {                               // lambertian, no near_zero guard (:21)
             d_out = n + unit_vector(ball);
@@ -318,7 +323,7 @@ template <typename T, typename R> __device__ __forceinline__ bool scatter(int ty
         const bool cannot_refract = refraction_ratio * sin_theta > T(1);
         // `||` short-circuit (:64): the uniform is drawn only when refraction is possible
         bool do_reflect = cannot_refract;
-        if (!do_reflect) { rng.generate(0u); do_reflect = reflectance(cos_theta, refraction_ratio) > u01<T>(rng.w0 >> 8); }
+        if (!do_reflect) do_reflect = reflectance(cos_theta, refraction_ratio) > u01<T>(rng.w0 >> 8);
         if (do_reflect)
             d_out = reflect(unit_direction, n);
         else
