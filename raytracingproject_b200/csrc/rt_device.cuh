@@ -52,6 +52,11 @@ template <typename T> __device__ __forceinline__ Vec<T> refract(Vec<T> uv, Vec<T
 // TABLE = true: the ten round keys (key + r * Weyl constant, the same for every block of a launch) come precomputed
 // from the kernel's parameter block -- a constant-bank operand of the XOR, no instruction -- instead of two additions
 // per round: 4 instead of 6 issue slots per round in the render kernels, whose hottest lines these are.
+#ifndef RT_PHILOX_UNROLL
+#define RT_PHILOX_UNROLL 10            // rounds per pass of the loop in generate() (10 = fully unrolled; the render kernels hold four copies of it)
+#endif
+#define RT_PRAGMA_(x) _Pragma(#x)
+#define RT_PRAGMA(x) RT_PRAGMA_(x)
 struct PhiloxKeys { uint32_t k[20]; };     // k[2r], k[2r + 1] = round keys of round r
 inline void philox_round_keys(uint64_t seed, PhiloxKeys& out) {
     uint32_t k0 = uint32_t(seed), k1 = uint32_t(seed >> 32);
@@ -71,7 +76,7 @@ template <bool TABLE> struct PhiloxT {
     __device__ __forceinline__ void generate(uint32_t block) {
         uint32_t c0 = pixel, c1 = sample, c2 = stage, c3 = block;
         uint32_t k0 = key0, k1 = key1;
-#pragma unroll
+        RT_PRAGMA(unroll RT_PHILOX_UNROLL)
         for (int r = 0; r < 10; ++r) {
             const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
             const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;

@@ -373,6 +373,7 @@ __device__ __forceinline__ void trav_leaf(const typename Quad<T>::type* __restri
                                           const int* __restrict__ meta, const Ray<T>& r, T tmin, Trav<T>& tv, const StackEntry* stack) {
     const int leaf = ~tv.cur;
     const int first = leaf >> 3, count = (leaf & 7) + 1;
+#pragma unroll 1                        // (the compiler unrolled it four times: 4 KB of sphere tests in a kernel that misses its instruction cache)
     for (int k = 0; k < count; ++k) {
         const int slot = first + k;
         const typename Quad<T>::type a = sa[slot], b = sb[slot];

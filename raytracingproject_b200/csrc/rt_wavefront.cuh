@@ -34,7 +34,7 @@
 namespace rt {
 
 #ifndef RT_NODE_VISITS
-#define RT_NODE_VISITS 3               // node visits per head-count ballot of the TRACE stage (3 measured best of 2 / 3 / 4 / 6: profiles/r1_node_visits_ab.txt)
+#define RT_NODE_VISITS 2               // node visits per head-count ballot of the TRACE stage: 2 since the code diet of round 2 (profiles/r2_code_size_ab.txt; round 1 measured 3 best of 2 / 3 / 4 / 6 on a larger kernel: r1_node_visits_ab.txt)
 #endif
 
 #ifndef RT_RING
@@ -174,6 +174,7 @@ render_pool_kernel(const RenderParams<T> p) {
             // parity mode keeps the slot-per-pixel loop below, whose sum has the reference's order.
             // Up to 4 jobs are open: the two newest hand out items, older ones only wait for their last paths to end.
             int* const pend = reinterpret_cast<int*>(ring + 4);        // per entry: items not completed yet (0: the entry is free)
+            #pragma unroll 1                        // (stage loops stay rolled: code size, see trav_leaf)
             for (int b = 0; b < n_end; b += 32) {
                 const int idx = b + lane;
                 const bool valid = idx < n_end;
@@ -399,6 +400,7 @@ render_pool_kernel(const RenderParams<T> p) {
             // every queued ray against the spheres kept out of the tree (the r = 1000 ground), in
             // double, with a full warp: gives the tree walk a tight t_max from its first node on
             if (sv.n_big > 0) {
+                #pragma unroll 1                        // (stage loops stay rolled: code size, see trav_leaf)
                 for (int b = 0; b < n_q; b += 32) {
                     const int idx = b + lane;
                     if (idx < n_q) {
@@ -484,6 +486,7 @@ render_pool_kernel(const RenderParams<T> p) {
             // ONE shading list, opaque ones (lambertian + metal: they share the ball sampler) filled from its front, glass from
             // its back.  With RT_MERGE_HITS the HIT stage walks that list as one sequence, so the last few opaque hits and the
             // few glass hits of a round share a batch (and its surface / ray load-store code) instead of taking one batch each.
+            #pragma unroll 1                        // (stage loops stay rolled: code size, see trav_leaf)
             for (int b = 0; b < n_q; b += 32) {
                 const int idx = b + lane;
                 int key = -1, pid = 0;
@@ -516,6 +519,7 @@ render_pool_kernel(const RenderParams<T> p) {
                 const unsigned char* list = B + L::LOPAQUE * P;
                 const int n = l ? n_gls : n_opq;
 #endif
+                #pragma unroll 1                        // (stage loops stay rolled: code size, see trav_leaf)
                 for (int b = 0; b < n; b += 32) {
                     const int idx = b + lane;
                     bool cont = false, ended = false; int pid = 0;
