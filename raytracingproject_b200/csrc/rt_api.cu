@@ -431,7 +431,7 @@ extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_s
         if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
         d_sph.release(); d_mat.release(); d_ids.release(); d_boxes.release(); d_order.release();
         if (e != cudaSuccess) return cuda_fail(ctx, e, "rt_upload_scene: device scene build");
-        if (depth > RT_STACK) return fail(ctx, RT_E_INVALID, "rt_upload_scene: LBVH deeper than the traversal stack");
+        if (depth > RT_STACK - 2) return fail(ctx, RT_E_INVALID, "rt_upload_scene: LBVH deeper than the traversal stack");
         ctx->root_ref = root; ctx->depth = depth; ctx->n_nodes = n_tree - 1;
         ctx->build_ms = ms_since(t_build);
     } else {
@@ -442,7 +442,7 @@ extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_s
         }
         HostBVH bvh;
         build_bvh_sah(boxes, max_leaf, bvh);
-        if (bvh.depth > RT_STACK) return fail(ctx, RT_E_INVALID, "rt_upload_scene: BVH deeper than the traversal stack");
+        if (bvh.depth > RT_STACK - 2) return fail(ctx, RT_E_INVALID, "rt_upload_scene: BVH deeper than the traversal stack");
         ctx->root_ref = bvh.root_ref; ctx->depth = bvh.depth; ctx->n_nodes = bvh.n_inner;
         CK(ctx->nodes.resize(std::max<size_t>(1, size_t(bvh.n_inner) * 4)));
         if (bvh.n_inner)
@@ -507,7 +507,7 @@ extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_s
         ctx->wide = ctx->n_nodes > 0 && want > 0;
         // the 4-wide walk pushes up to 3 refs per record = per two levels of the binary tree: a tree the binary walk
         // can hold (depth <= RT_STACK) may still overflow here
-        if (ctx->wide && 3 * ((ctx->depth + 1) / 2) > RT_STACK)
+        if (ctx->wide && 3 * ((ctx->depth + 1) / 2) > RT_STACK - 2)
             return fail(ctx, RT_E_INVALID, "rt_upload_scene: tree too deep for the 4-wide walk (3 * ceil(depth / 2) > traversal stack); use wide = 0");
         if (ctx->wide) {
             CK(ctx->nodes4.resize(size_t(ctx->n_nodes) * 8));

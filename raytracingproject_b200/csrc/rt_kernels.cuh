@@ -153,6 +153,7 @@ render_sched_kernel(const RenderParams<T> p) {
     const int th_s = p.th_s, th_l = p.th_l;
     unsigned long long my_rays = 0;
     StackEntry stack[RT_STACK];
+    stack_init(stack);
 
     for (;;) {
         int job = 0;

@@ -136,7 +136,7 @@ template <typename T> struct Trav {
     T tbest;
     int best_id, best_slot;  // list index (tie rule) and slot (tree slot, or n_slots + k for big sphere k)
     int cur, sp;
-    int tos;                 // copy of stack[sp - 1]: a pop takes it from the register and reloads it off the critical path
+    int tos;                 // copy of stack[sp] (the top entry; the sentinel of stack[0] when the stack is empty): a pop takes it from the register and reloads it off the critical path
     float tos_t;             // RT_STACK_T: the entry distance stored with it (-inf below the bottom of the stack)
 };
 
@@ -151,18 +151,31 @@ __device__ __forceinline__ float cull_limit(const Trav<double>& tv) { return __d
 __device__ __forceinline__ float entry_bound(float t) { return t; }
 __device__ __forceinline__ float entry_bound(double t) { return __double2float_rd(t); }
 
+// The stack of a walk.  stack[0] holds a sentinel for good (stack_init, once per thread), entries live at 1 .. sp, and the top
+// entry is mirrored in a register (tos == stack[sp]): a push is `stack[++sp] = ref`, a pop `cur = tos; sp = max(sp - 1, 0);
+// tos = stack[sp]` -- no test for an empty stack, no branch (the first form took 11 instructions and a branch per pop, and a pop
+// happens on almost every second visit).  Nothing checks for overflow here: rt_upload_scene refuses trees deeper than
+// RT_STACK - 2 (a binary walk pushes at most one entry per level).
+__device__ __forceinline__ void stack_init(StackEntry* stack) {
+#if RT_STACK_T
+    stack[0] = make_int2(RT_SENTINEL, __float_as_int(-INFINITY));
+#else
+    stack[0] = RT_SENTINEL;
+#endif
+}
+
 template <typename T>
 __device__ __forceinline__ void trav_push(Trav<T>& tv, StackEntry* stack, int ref, T t_entry) {
 #if RT_STACK_T
     const float t = entry_bound(t_entry);
-    stack[tv.sp++] = make_int2(ref, __float_as_int(t)); tv.tos = ref; tv.tos_t = t;
+    stack[++tv.sp] = make_int2(ref, __float_as_int(t)); tv.tos = ref; tv.tos_t = t;
 #else
     (void)t_entry;
-    stack[tv.sp++] = ref; tv.tos = ref;
+    stack[++tv.sp] = ref; tv.tos = ref;
 #endif
 }
 
-// next node / leaf to walk, or RT_SENTINEL when the stack is empty (the top of the stack is in a register)
+// next node / leaf to walk, or RT_SENTINEL when the stack is empty
 template <typename T>
 __device__ __forceinline__ int trav_pop(Trav<T>& tv, const StackEntry* stack) {
 #if RT_STACK_T
@@ -171,16 +184,15 @@ __device__ __forceinline__ int trav_pop(Trav<T>& tv, const StackEntry* stack) {
     for (;;) {
         next = tv.tos;
         const float t = tv.tos_t;
-        if (tv.sp > 0) --tv.sp;
-        if (tv.sp > 0) { const StackEntry e = stack[tv.sp - 1]; tv.tos = e.x; tv.tos_t = __int_as_float(e.y); }
-        else { tv.tos = RT_SENTINEL; tv.tos_t = -INFINITY; }
+        tv.sp = max(tv.sp - 1, 0);
+        const StackEntry e = stack[tv.sp]; tv.tos = e.x; tv.tos_t = __int_as_float(e.y);
         if (!(t > lim)) break;               // (the sentinel carries -inf)
     }
     return next;
 #else
     const int next = tv.tos;
-    if (tv.sp > 0) --tv.sp;
-    tv.tos = tv.sp > 0 ? stack[tv.sp - 1] : RT_SENTINEL;
+    tv.sp = max(tv.sp - 1, 0);
+    tv.tos = stack[tv.sp];
     return next;
 #endif
 }
@@ -264,7 +276,7 @@ __device__ __forceinline__ void trav_node(const float4* __restrict__ nodes, cons
     // blocks instead of a four-way branch, so the lanes of a warp stay together through the step
     const bool left_first = !hr || (hl && tl <= tr);
     const int near = left_first ? cl : cr, far = left_first ? cr : cl;
-    if (hl && hr && tv.sp < RT_STACK) trav_push<T>(tv, stack, far, left_first ? tr : tl);
+    if (hl && hr) trav_push<T>(tv, stack, far, left_first ? tr : tl);
     int next = near;
     if (!(hl || hr)) next = trav_pop<T>(tv, stack);
     tv.cur = next;
@@ -294,7 +306,7 @@ __device__ __forceinline__ void trav_node_top(const float4* __restrict__ nodes, 
         if (RT_PREFETCH_FAR >= 2) asm volatile("prefetch.global.L1 [%0];" :: "l"(f + 2));
     }
 #endif
-    if (hl && hr && tv.sp < RT_STACK) trav_push<T>(tv, stack, far, left_first ? tr : tl);
+    if (hl && hr) trav_push<T>(tv, stack, far, left_first ? tr : tl);
     int next = near;
     if (!(hl || hr)) next = trav_pop<T>(tv, stack);
     tv.cur = next;
@@ -360,7 +372,7 @@ __device__ __forceinline__ void trav_node4(const float4* __restrict__ nodes4, co
 #define RT_TN_OF(k) ((key[k] & 2) ? ((key[k] & 1) ? tn[3] : tn[2]) : ((key[k] & 1) ? tn[1] : tn[0]))
 #pragma unroll
     for (int k = 3; k >= 1; --k)
-        if (key[k] != 0x7fffffff && tv.sp < RT_STACK) trav_push<T>(tv, stack, RT_REF_OF(k), RT_TN_OF(k));
+        if (key[k] != 0x7fffffff) trav_push<T>(tv, stack, RT_REF_OF(k), RT_TN_OF(k));
     if (key[0] != 0x7fffffff) tv.cur = RT_REF_OF(0);
     else tv.cur = trav_pop<T>(tv, stack);       // nothing entered
 #undef RT_TN_OF
@@ -396,6 +408,7 @@ __device__ __forceinline__ void trace_closest(const SceneView<T>& sv, const floa
                                               const Ray<T>& r, T tmin, T tmax, T& t_out, int& slot_out) {
     Trav<T> tv;
     StackEntry stack[RT_STACK];
+    stack_init(stack);
     trav_init<T>(sv, r, tmin, tmax, tv);
     if (sv.nodes4 && nodes == sv.nodes) {          // tree in global memory with 4-wide records
         while (tv.cur != RT_SENTINEL) {

@@ -137,6 +137,7 @@ render_pool_kernel(const RenderParams<T> p) {
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(wt_first));
 #endif
     StackEntry stack[RT_STACK];
+    stack_init(stack);
 
     // Ring state (warp-uniform).  Every slot goes through every job of its warp, in order: `newest` is the
     // entry fetched last, byte e of `joined` the number of slots that have moved into entry e's job.  A slot
