@@ -214,13 +214,24 @@ template <typename T> __device__ __forceinline__ Vec<T> sphere_center(const type
 // mode uses for big spheres).  `a` = direction.length_squared() is hoisted per ray.  Returns the
 // accepted root or a negative value.  Tie rule of src/hittable_list.h:31 (strict <, first in
 // list wins) is restated order-independently: a root equal to tbest is accepted only from a
-// sphere with a smaller list index than the current best.
-template <typename T> __device__ __forceinline__ bool root_ok(T root, T tmin, T tbest, int id, int best_id) {
-    return tmin < root && (root < tbest || (root == tbest && id < best_id));
+// sphere with a smaller list index than the current best.  The walk carries SLOTS, not list indices: `tie()` looks the two
+// indices up and is called only when a root equals tbest exactly -- almost never -- so a sphere test pays neither the
+// load of its index nor a register for the best one.
+template <typename T, typename Tie> __device__ __forceinline__ bool root_ok(T root, T tmin, T tbest, const Tie& tie) {
+    return tmin < root && (root < tbest || (root == tbest && tie()));
 }
 
+// list index of `slot` < that of `best_slot` (tree slots: meta; slots >= n_slots: the big spheres kept out of the tree;
+// best_slot < 0: there is no best yet, t_best is the caller's t_max and an equal root is not inside (tmin, tmax))
+struct TieBySlot {
+    const int* meta; const int* big_meta; int n_slots, slot, best_slot;
+    __device__ __forceinline__ int id_of(int s) const { return RT_META_ID(s < n_slots ? meta[s] : big_meta[s - n_slots]); }
+    __device__ __forceinline__ bool operator()() const { return best_slot >= 0 && id_of(slot) < id_of(best_slot); }
+};
+
+template <typename Tie>
 __device__ __forceinline__ bool sphere_hit_ref(const Vec<double>& o, const Vec<double>& d, double a, const Vec<double>& center,
-                                               double rr, double tmin, double tbest, int id, int best_id, double& t_out) {
+                                               double rr, double tmin, double tbest, const Tie& tie, double& t_out) {
     const Vec<double> oc = o - center;
     const double half_b = dot(oc, d);
     const double c = len2(oc) - rr;
@@ -228,9 +239,9 @@ __device__ __forceinline__ bool sphere_hit_ref(const Vec<double>& o, const Vec<d
     if (discriminant < 0) return false;
     const double sqrtd = sqrt(discriminant);
     double root = (-half_b - sqrtd) / a;
-    if (!root_ok(root, tmin, tbest, id, best_id)) {
+    if (!root_ok(root, tmin, tbest, tie)) {
         root = (-half_b + sqrtd) / a;
-        if (!root_ok(root, tmin, tbest, id, best_id)) return false;
+        if (!root_ok(root, tmin, tbest, tie)) return false;
     }
     t_out = root;
     return true;
@@ -254,8 +265,9 @@ __device__ __forceinline__ double sqrt_newton(double x) {                 // x >
 // Fast-mode test of a BIG sphere (kept out of the tree, e.g. the r = 1000 ground): the quadratic of
 // sphere_hit_ref in double -- |oc|^2 - r^2 must not cancel in float and the self-intersection root
 // has to stay below tmin = 0.001 -- with inv_a = 1/|d|^2 hoisted per ray.
+template <typename Tie>
 __device__ __forceinline__ bool sphere_hit_big(const Vec<double>& o, const Vec<double>& d, double a, double inv_a, const Vec<double>& center,
-                                               double rr, double tmin, double tbest, int id, int best_id, double& t_out) {
+                                               double rr, double tmin, double tbest, const Tie& tie, double& t_out) {
     const Vec<double> oc = o - center;
     const double half_b = dot(oc, d);
     const double c = len2(oc) - rr;
@@ -263,9 +275,9 @@ __device__ __forceinline__ bool sphere_hit_big(const Vec<double>& o, const Vec<d
     if (discriminant < 0) return false;
     const double sqrtd = sqrt_newton(discriminant);
     double root = (-half_b - sqrtd) * inv_a;
-    if (!root_ok(root, tmin, tbest, id, best_id)) {
+    if (!root_ok(root, tmin, tbest, tie)) {
         root = (-half_b + sqrtd) * inv_a;
-        if (!root_ok(root, tmin, tbest, id, best_id)) return false;
+        if (!root_ok(root, tmin, tbest, tie)) return false;
     }
     t_out = root;
     return true;
@@ -273,8 +285,9 @@ __device__ __forceinline__ bool sphere_hit_big(const Vec<double>& o, const Vec<d
 
 // Fast-mode sphere test (float): the same quadratic, solved around the closest-approach point
 // so that r^2 - |l|^2 does not cancel catastrophically (l = oc - (oc.d/a) d).  inv_a = 1/a.
+template <typename Tie>
 __device__ __forceinline__ bool sphere_hit_f32(const Vec<float>& o, const Vec<float>& d, float inv_a, const Vec<float>& center,
-                                               float rr, float tmin, float tbest, int id, int best_id, float& t_out) {
+                                               float rr, float tmin, float tbest, const Tie& tie, float& t_out) {
     const Vec<float> oc = o - center;
     const float tca = -dot(oc, d) * inv_a;
     const Vec<float> l = oc + tca * d;
@@ -282,9 +295,9 @@ __device__ __forceinline__ bool sphere_hit_f32(const Vec<float>& o, const Vec<fl
     if (disc < 0.0f) return false;
     const float s = sqrtf(disc * inv_a);
     float root = tca - s;
-    if (!root_ok(root, tmin, tbest, id, best_id)) {
+    if (!root_ok(root, tmin, tbest, tie)) {
         root = tca + s;
-        if (!root_ok(root, tmin, tbest, id, best_id)) return false;
+        if (!root_ok(root, tmin, tbest, tie)) return false;
     }
     t_out = root;
     return true;

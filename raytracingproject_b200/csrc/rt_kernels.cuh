@@ -172,7 +172,7 @@ render_sched_kernel(const RenderParams<T> p) {
         double acc_r = 0.0, acc_g = 0.0, acc_b = 0.0;
         Ray<T> ray; ray.o = mk<T>(0, 0, 0); ray.d = mk<T>(0, 0, 1); ray.tm = 0;
         Vec<T> thr = mk<T>(1, 1, 1);
-        Trav<T> tv; tv.cur = RT_SENTINEL; tv.sp = 0; tv.tos = RT_SENTINEL; tv.tos_t = -INFINITY; tv.tbest = 0; tv.best_id = -1; tv.best_slot = -1; tv.qa = 1; slab_clear<T>(tv.slab);
+        Trav<T> tv; tv.cur = RT_SENTINEL; tv.sp = 0; tv.tos = RT_SENTINEL; tv.tos_t = -INFINITY; tv.tbest = 0; tv.best_slot = -1; tv.qa = 1; slab_clear<T>(tv.slab);
         int depth = 0;                       // bounces left for the current path; 0 = start the next sample
         bool alive = in_image && s < s_end;
 
@@ -232,7 +232,7 @@ render_sched_kernel(const RenderParams<T> p) {
                 }
             } else if (nL >= th_l || nL > nN) {
                 // ---------------------------------------------------------------- section L
-                if (isL) trav_leaf<T>(st.sa, st.sb, st.meta, ray, T(0.001), tv, stack);
+                if (isL) trav_leaf<T>(sv, st.sa, st.sb, st.meta, ray, T(0.001), tv, stack);
             } else {
                 // ---------------------------------------------------------------- section N
                 if (isN) trav_node<T>(st.nodes, ray, T(0.001), tv, stack);

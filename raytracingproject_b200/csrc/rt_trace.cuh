@@ -109,15 +109,17 @@ __device__ __forceinline__ void node_boxes(const float4& q0, const float4& q1, c
     hr = slab(q1.x, q1.y, q2.y, q1.z, q1.w, q2.w, s.o, s.inv, tmin, tmax, tr);
 }
 
+template <typename Tie>
 __device__ __forceinline__ bool leaf_sphere(const float4& a, const float4& b, const Ray<float>& r, float a_len2, float inv_a,
-                                            float tmin, float tbest, int id, int best_id, float& t) {
+                                            float tmin, float tbest, const Tie& tie, float& t) {
     (void)a_len2;
-    return sphere_hit_f32(r.o, r.d, inv_a, sphere_center<float>(a, b, r.tm), b.w, tmin, tbest, id, best_id, t);
+    return sphere_hit_f32(r.o, r.d, inv_a, sphere_center<float>(a, b, r.tm), b.w, tmin, tbest, tie, t);
 }
+template <typename Tie>
 __device__ __forceinline__ bool leaf_sphere(const double4& a, const double4& b, const Ray<double>& r, double a_len2, double inv_a,
-                                            double tmin, double tbest, int id, int best_id, double& t) {
+                                            double tmin, double tbest, const Tie& tie, double& t) {
     (void)inv_a;
-    return sphere_hit_ref(r.o, r.d, a_len2, sphere_center<double>(a, b, r.tm), b.w, tmin, tbest, id, best_id, t);
+    return sphere_hit_ref(r.o, r.d, a_len2, sphere_center<double>(a, b, r.tm), b.w, tmin, tbest, tie, t);
 }
 
 // Traversal state of one ray.  The traversal is cut into three steps -- init (big spheres, root),
@@ -134,7 +136,7 @@ template <typename T> struct Trav {
     SlabRay<T> slab;         // per-ray constants of the box test
     T qa;                    // fast mode: 1 / |d|^2; parity mode: |d|^2 (what each sphere test wants)
     T tbest;
-    int best_id, best_slot;  // list index (tie rule) and slot (tree slot, or n_slots + k for big sphere k)
+    int best_slot;           // tree slot, or n_slots + k for big sphere k, of the closest hit so far (-1: none)
     int cur, sp;
     int tos;                 // copy of stack[sp] (the top entry; the sentinel of stack[0] when the stack is empty): a pop takes it from the register and reloads it off the critical path
     float tos_t;             // RT_STACK_T: the entry distance stored with it (-inf below the bottom of the stack)
@@ -200,8 +202,8 @@ __device__ __forceinline__ int trav_pop(Trav<T>& tv, const StackEntry* stack) {
 // big spheres first, in double in both modes (the r = 1000 ground sphere): a tight t_max for the
 // tree and no float cancellation in |oc|^2 - r^2
 template <typename T>
-__device__ __forceinline__ void trav_big(const SceneView<T>& sv, const Ray<T>& r, T tmin, T tmax, T& tbest, int& best_id, int& best_slot) {
-    tbest = tmax; best_id = -1; best_slot = -1;
+__device__ __forceinline__ void trav_big(const SceneView<T>& sv, const Ray<T>& r, T tmin, T tmax, T& tbest, int& best_slot) {
+    tbest = tmax; best_slot = -1;
     if (sv.n_big > 0) {
         const Vec<double> od = mk<double>(r.o.x, r.o.y, r.o.z), dd = mk<double>(r.d.x, r.d.y, r.d.z);
         const double ad = len2(dd);
@@ -209,12 +211,12 @@ __device__ __forceinline__ void trav_big(const SceneView<T>& sv, const Ray<T>& r
         double tb = double(tbest);
         for (int k = 0; k < sv.n_big; ++k) {
             const double4 a = sv.big_a[k], b = sv.big_b[k];
-            const int id = RT_META_ID(sv.big_meta[k]);
+            const TieBySlot tie = { sv.meta, sv.big_meta, sv.n_slots, sv.n_slots + k, best_slot };
             double t;
             const bool hit = sizeof(T) == 4
-                ? sphere_hit_big(od, dd, ad, inv_ad, sphere_center<double>(a, b, double(r.tm)), b.w, double(tmin), tb, id, best_id, t)
-                : sphere_hit_ref(od, dd, ad, sphere_center<double>(a, b, double(r.tm)), b.w, double(tmin), tb, id, best_id, t);
-            if (hit) { tb = t; best_id = id; best_slot = sv.n_slots + k; }
+                ? sphere_hit_big(od, dd, ad, inv_ad, sphere_center<double>(a, b, double(r.tm)), b.w, double(tmin), tb, tie, t)
+                : sphere_hit_ref(od, dd, ad, sphere_center<double>(a, b, double(r.tm)), b.w, double(tmin), tb, tie, t);
+            if (hit) { tb = t; best_slot = sv.n_slots + k; }
         }
         tbest = T(tb);
     }
@@ -248,7 +250,7 @@ template <typename T> __device__ __forceinline__ void slab_clear(SlabRay<T>& s);
 template <> __device__ __forceinline__ void slab_clear<float>(SlabRay<float>& s) { s.pxy = s.qxy = s.oxy = s.pzz = s.qzz = s.ozz = 0ull; s.delta = 0.0f; }
 template <> __device__ __forceinline__ void slab_clear<double>(SlabRay<double>& s) { s.o = mk<double>(0, 0, 0); s.inv = mk<double>(0, 0, 0); }
 
-// per-ray constants of the tree walk; tbest / best_id / best_slot are already set (trav_big)
+// per-ray constants of the tree walk; tbest / best_slot are already set (trav_big)
 template <typename T>
 __device__ __forceinline__ void trav_setup(const SceneView<T>& sv, const Ray<T>& r, Trav<T>& tv) {
     const T a_len2 = len2(r.d);
@@ -259,7 +261,7 @@ __device__ __forceinline__ void trav_setup(const SceneView<T>& sv, const Ray<T>&
 
 template <typename T>
 __device__ __forceinline__ void trav_init(const SceneView<T>& sv, const Ray<T>& r, T tmin, T tmax, Trav<T>& tv) {
-    trav_big<T>(sv, r, tmin, tmax, tv.tbest, tv.best_id, tv.best_slot);
+    trav_big<T>(sv, r, tmin, tmax, tv.tbest, tv.best_slot);
     trav_setup<T>(sv, r, tv);
 }
 
@@ -381,7 +383,7 @@ __device__ __forceinline__ void trav_node4(const float4* __restrict__ nodes4, co
 
 // one leaf: its 1..8 sphere slots
 template <typename T>
-__device__ __forceinline__ void trav_leaf(const typename Quad<T>::type* __restrict__ sa, const typename Quad<T>::type* __restrict__ sb,
+__device__ __forceinline__ void trav_leaf(const SceneView<T>& sv, const typename Quad<T>::type* __restrict__ sa, const typename Quad<T>::type* __restrict__ sb,
                                           const int* __restrict__ meta, const Ray<T>& r, T tmin, Trav<T>& tv, const StackEntry* stack) {
     const int leaf = ~tv.cur;
     const int first = leaf >> 3, count = (leaf & 7) + 1;
@@ -389,10 +391,10 @@ __device__ __forceinline__ void trav_leaf(const typename Quad<T>::type* __restri
     for (int k = 0; k < count; ++k) {
         const int slot = first + k;
         const typename Quad<T>::type a = sa[slot], b = sb[slot];
-        const int id = RT_META_ID(meta[slot]);
+        const TieBySlot tie = { meta, sv.big_meta, sv.n_slots, slot, tv.best_slot };
         T t;
-        if (leaf_sphere(a, b, r, tv.qa, tv.qa, tmin, tv.tbest, id, tv.best_id, t)) {
-            tv.tbest = t; tv.best_id = id; tv.best_slot = slot;
+        if (leaf_sphere(a, b, r, tv.qa, tv.qa, tmin, tv.tbest, tie, t)) {
+            tv.tbest = t; tv.best_slot = slot;
         }
     }
     tv.cur = trav_pop<T>(tv, stack);
@@ -413,12 +415,12 @@ __device__ __forceinline__ void trace_closest(const SceneView<T>& sv, const floa
     if (sv.nodes4 && nodes == sv.nodes) {          // tree in global memory with 4-wide records
         while (tv.cur != RT_SENTINEL) {
             if (tv.cur >= 0) trav_node4<T>(sv.nodes4, r, tmin, tv, stack);
-            else trav_leaf<T>(sa, sb, meta, r, tmin, tv, stack);
+            else trav_leaf<T>(sv, sa, sb, meta, r, tmin, tv, stack);
         }
     } else {
         while (tv.cur != RT_SENTINEL) {
             if (tv.cur >= 0) trav_node<T>(nodes, r, tmin, tv, stack);
-            else trav_leaf<T>(sa, sb, meta, r, tmin, tv, stack);
+            else trav_leaf<T>(sv, sa, sb, meta, r, tmin, tv, stack);
         }
     }
     t_out = tv.tbest;
@@ -431,16 +433,16 @@ __device__ __forceinline__ void trace_closest(const SceneView<T>& sv, const floa
 template <typename T>
 __device__ __forceinline__ void brute_closest(const SceneView<T>& sv, const Ray<T>& r, T tmin, T tmax, T& t_out, int& slot_out) {
     T tbest;
-    int best_id, best_slot;
-    trav_big<T>(sv, r, tmin, tmax, tbest, best_id, best_slot);
+    int best_slot;
+    trav_big<T>(sv, r, tmin, tmax, tbest, best_slot);
     const T a_len2 = len2(r.d);
     const T inv_a = T(1) / a_len2;
     for (int slot = 0; slot < sv.n_slots; ++slot) {
         const typename Quad<T>::type a = sv.sa[slot], b = sv.sb[slot];
-        const int id = RT_META_ID(sv.meta[slot]);
+        const TieBySlot tie = { sv.meta, sv.big_meta, sv.n_slots, slot, best_slot };
         T t;
-        if (leaf_sphere(a, b, r, a_len2, inv_a, tmin, tbest, id, best_id, t)) {
-            tbest = t; best_id = id; best_slot = slot;
+        if (leaf_sphere(a, b, r, a_len2, inv_a, tmin, tbest, tie, t)) {
+            tbest = t; best_slot = slot;
         }
     }
     t_out = tbest;

@@ -410,8 +410,8 @@ render_pool_kernel(const RenderParams<T> p) {
                         ray.o = mk<T>(F[L::OX * P + pid], F[L::OY * P + pid], F[L::OZ * P + pid]);
                         ray.d = mk<T>(F[L::DX * P + pid], F[L::DY * P + pid], F[L::DZ * P + pid]);
                         ray.tm = F[L::TM * P + pid];
-                        T tb; int bid, bslot;
-                        trav_big<T>(sv, ray, T(0.001), T(INFINITY), tb, bid, bslot);
+                        T tb; int bslot;
+                        trav_big<T>(sv, ray, T(0.001), T(INFINITY), tb, bslot);
                         F[L::TBEST * P + pid] = tb; I[L::BEST * P + pid] = bslot;
                     }
                 }
@@ -422,7 +422,7 @@ render_pool_kernel(const RenderParams<T> p) {
             {
                 int head = 0, pid = 0;
                 Ray<T> ray; ray.o = mk<T>(0, 0, 0); ray.d = mk<T>(0, 0, 1); ray.tm = 0;
-                Trav<T> tv; tv.cur = RT_SENTINEL; tv.sp = 0; tv.tos = RT_SENTINEL; tv.tos_t = -INFINITY; tv.tbest = 0; tv.best_id = -1; tv.best_slot = -1; tv.qa = 1; slab_clear<T>(tv.slab);
+                Trav<T> tv; tv.cur = RT_SENTINEL; tv.sp = 0; tv.tos = RT_SENTINEL; tv.tos_t = -INFINITY; tv.tbest = 0; tv.best_slot = -1; tv.qa = 1; slab_clear<T>(tv.slab);
                 for (;;) {
                     const bool isN = tv.cur >= 0;
                     const bool isP = tv.cur == RT_SENTINEL;
@@ -442,10 +442,9 @@ render_pool_kernel(const RenderParams<T> p) {
                             ray.o = mk<T>(F[L::OX * P + pid], F[L::OY * P + pid], F[L::OZ * P + pid]);
                             ray.d = mk<T>(F[L::DX * P + pid], F[L::DY * P + pid], F[L::DZ * P + pid]);
                             ray.tm = F[L::TM * P + pid];
-                            tv.tbest = T(INFINITY); tv.best_slot = -1; tv.best_id = -1;
+                            tv.tbest = T(INFINITY); tv.best_slot = -1;
                             if (sv.n_big > 0) {
                                 tv.tbest = F[L::TBEST * P + pid]; tv.best_slot = I[L::BEST * P + pid];
-                                if (tv.best_slot >= 0) tv.best_id = RT_META_ID(sv.big_meta[tv.best_slot - sv.n_slots]);
                             }
                             trav_setup<T>(sv, ray, tv);
                             if (tv.cur == RT_SENTINEL) { F[L::TBEST * P + pid] = tv.tbest; I[L::BEST * P + pid] = tv.best_slot; }   // no tree
@@ -455,7 +454,7 @@ render_pool_kernel(const RenderParams<T> p) {
                     } else if (nL >= th_l || nL > nN) {
                         RT_STAT(8, 1); RT_STAT(9, nL); RT_STAT(10, nN); RT_STAT(11, nP);
                         if (!isN && !isP) {
-                            trav_leaf<T>(st.sa, st.sb, st.meta, ray, T(0.001), tv, stack);
+                            trav_leaf<T>(sv, st.sa, st.sb, st.meta, ray, T(0.001), tv, stack);
                             if (tv.cur == RT_SENTINEL) { F[L::TBEST * P + pid] = tv.tbest; I[L::BEST * P + pid] = tv.best_slot; }
                         }
                     } else {
