@@ -27,14 +27,22 @@ template <typename T> __host__ __device__ __forceinline__ Vec<T> operator*(T t, 
 template <typename T> __host__ __device__ __forceinline__ T dot(Vec<T> a, Vec<T> b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 template <typename T> __host__ __device__ __forceinline__ T len2(Vec<T> a) { return a.x * a.x + a.y * a.y + a.z * a.z; }
 
-__device__ __forceinline__ float  rt_sqrt(float x)  { return sqrtf(x); }   // fast mode: the f32 TU is built with -prec-sqrt=false (MUFU + one step, 2 ulp)
+__device__ __forceinline__ float  rt_sqrt(float x)  { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }   // fast mode: one MUFU (sqrtf adds a range-scaling sequence even with -prec-sqrt=false)
 __device__ __forceinline__ double rt_sqrt(double x) { return sqrt(x); }
 __device__ __forceinline__ float  rt_fmin(float a, float b)   { return fminf(a, b); }
 __device__ __forceinline__ double rt_fmin(double a, double b) { return fmin(a, b); }
 __device__ __forceinline__ float  rt_fabs(float a)  { return fabsf(a); }
 __device__ __forceinline__ double rt_fabs(double a) { return fabs(a); }
 
-template <typename T> __device__ __forceinline__ Vec<T> unit_vector(Vec<T> v) { return (T(1) / rt_sqrt(len2(v))) * v; }   // src/vec3.h:117-119
+// fast mode: reciprocal and reciprocal square root straight from the special-function unit (1-2 ulp, one instruction; `1.0f / x`
+// and `1.0f / sqrtf(x)` compile to range-scaled sequences of 7 and 11 even with -prec-div=false).  A denormal argument gives
+// +-inf: the callers clamp (slab_setup) or cannot meet one (squared lengths of directions)
+__device__ __forceinline__ float  rt_rcp(float x)  { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ double rt_rcp(double x) { return 1.0 / x; }
+__device__ __forceinline__ float  rt_rsqrt(float x)  { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ double rt_rsqrt(double x) { return 1.0 / sqrt(x); }     // parity mode: the reference's 1 / sqrt (src/vec3.h:117-119, :101-103)
+
+template <typename T> __device__ __forceinline__ Vec<T> unit_vector(Vec<T> v) { return rt_rsqrt(len2(v)) * v; }   // src/vec3.h:117-119
 template <typename T> __device__ __forceinline__ Vec<T> reflect(Vec<T> v, Vec<T> n) { return v - (T(2) * dot(v, n)) * n; }   // src/vec3.h:149-151
 
 // src/vec3.h:153-158
@@ -251,12 +259,12 @@ __device__ __forceinline__ bool sphere_hit_ref(const Vec<double>& o, const Vec<d
 // two Newton steps (8 and 10 instructions instead of the ~70 / ~85 of the IEEE-rounded routines).
 // Only the fast mode uses them; parity mode keeps `/` and sqrt().
 __device__ __forceinline__ double rcp_newton(double x) {
-    double r = double(__fdividef(1.0f, float(x)));
+    double r = double(rt_rcp(float(x)));
     r = fma(r, fma(-x, r, 1.0), r);
     return fma(r, fma(-x, r, 1.0), r);
 }
 __device__ __forceinline__ double sqrt_newton(double x) {                 // x >= 0
-    const double y0 = double(rsqrtf(fmaxf(float(x), 1e-36f)));
+    const double y0 = double(rt_rsqrt(fmaxf(float(x), 1e-36f)));
     const double y = y0 * fma(-0.5 * x * y0, y0, 1.5);                    // 1/sqrt(x) to ~1e-14
     const double s = x * y;
     return fma(0.5 * y, fma(-s, s, x), s);
@@ -293,7 +301,7 @@ __device__ __forceinline__ bool sphere_hit_f32(const Vec<float>& o, const Vec<fl
     const Vec<float> l = oc + tca * d;
     const float disc = rr - len2(l);
     if (disc < 0.0f) return false;
-    const float s = sqrtf(disc * inv_a);
+    const float s = rt_sqrt(disc * inv_a);
     float root = tca - s;
     if (!root_ok(root, tmin, tbest, tie)) {
         root = tca + s;

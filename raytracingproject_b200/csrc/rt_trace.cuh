@@ -224,7 +224,7 @@ __device__ __forceinline__ void trav_big(const SceneView<T>& sv, const Ray<T>& r
 
 // per-ray constants of the box test
 __device__ __forceinline__ void slab_setup(const Ray<float>& r, SlabRay<float>& s) {
-    Vec<float> inv = mk<float>(1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z);
+    Vec<float> inv = mk<float>(rt_rcp(r.d.x), rt_rcp(r.d.y), rt_rcp(r.d.z));
     // keep the reciprocals finite: with +-inf the FMA form gives plane * inf - o * inf = NaN or an infinity
     // whose sign depends on the plane alone.  At 1e18 the axis is effectively switched off through delta
     // (boxes are accepted conservatively, as the NaN-dropping min/max of the reference's form would)
@@ -254,7 +254,7 @@ template <> __device__ __forceinline__ void slab_clear<double>(SlabRay<double>& 
 template <typename T>
 __device__ __forceinline__ void trav_setup(const SceneView<T>& sv, const Ray<T>& r, Trav<T>& tv) {
     const T a_len2 = len2(r.d);
-    tv.qa = sizeof(T) == 4 ? T(1) / a_len2 : a_len2;
+    tv.qa = sizeof(T) == 4 ? rt_rcp(a_len2) : a_len2;
     slab_setup(r, tv.slab);
     tv.cur = sv.root_ref; tv.sp = 0; tv.tos = RT_SENTINEL; tv.tos_t = -INFINITY;
 }
