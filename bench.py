@@ -443,10 +443,10 @@ def main():
             "mrays_per_s": rays / ms / 1e3, "rays_per_sample": rays / samples,
             "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak,
                          # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of this kernel on this workload, from the
-                         # ncu --set full capture profiles/r2_wavefront_c3_500spp_ncu_summary.txt (5.5 MB + 223.6 MB: the 8 sample
+                         # ncu --set full capture profiles/r2_wavefront_c3_500spp_ncu_summary.txt (6.3 MB + 227.8 MB: the 8 sample
                          # layers of the frame written once; fast mode adds samples with RED.ADD, so nothing is read back); the
                          # bounce loop itself reads nothing from HBM (scene staged on chip), this is the accumulator traffic
-                         "traffic": 229.0e6 if (headline and args.variant == "wavefront" and world == 1 and args.spp == SPP and args.precision == "f32") else None,
+                         "traffic": 234.1e6 if (headline and args.variant == "wavefront" and world == 1 and args.spp == SPP and args.precision == "f32") else None,
                          "kernel": kernel_name, "kernel_ms": kms,
                          "note": f"algorithmic {f_ray:.0f} flop/ray x {rank_rays:.3e} rays per launch (SURVEY 8d); peak = 148 SMs x 128 "
                                  f"FP32 lanes x 2 x {sm_mhz:.0f} MHz observed under load (not in MEASURED_PEAKS.json); L2-side figure "
