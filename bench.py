@@ -225,7 +225,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--precision", default="f32", choices=["f32", "f64"])
     ap.add_argument("--combine", default="nccl", choices=["nccl", "ipc"], help="--shard samples: how the partial buffers are combined")
-    ap.add_argument("--shard", default="auto", choices=["auto", "tiles", "samples"],
+    ap.add_argument("--shard", default="auto", choices=["auto", "tiles", "samples", "jobs"],
                     help="N > 1: tile-interleaved shards (every rank writes its tiles' bytes into rank 0's image over NVLink) or "
                          "sample-range shards (fold + reduce of float partial buffers).  auto: tiles when every rank still owns at "
                          "least twice as many tiles as it runs warps (4K frames), else samples (profiles/r2_tile_sharding_1gpu_diag.txt)")
@@ -298,8 +298,14 @@ def main():
     # profiles/r2_tile_sharding_1gpu_diag.txt) and save the fold + NCCL reduce (~1 % of a C3 frame at N = 2), so they only pay where
     # the sample shards would be short as well: C5's 64 spp over 8 ranks, not C3's 500 (N = 2: 141.6 ms by tiles, 134.9 by samples)
     want_tiles = args.shard == "tiles" or (args.shard == "auto" and n_tiles // max(1, world) >= 2 * resident_warps and args.spp // max(1, world) < 32)
-    tiles = world > 1 and want_tiles and args.variant == "wavefront"
-    if tiles:
+    tiles = world > 1 and want_tiles and args.variant == "wavefront" and args.shard != "jobs"
+    # jobs: one job counter for all GPUs (dynamic sharding over NVLink atomics), buffers combined like sample shards
+    # (measured: loses to sample shards by 5 % at N = 2 -- profiles/r2_dynamic_sharding.txt -- so only on request)
+    jobs = world > 1 and args.shard == "jobs" and args.variant == "wavefront" and args.precision == "f32"
+    if jobs:
+        sharding.setup_shared_jobs(ctx, rank, world)
+        sharding.render_shared(ctx, cam, prec, world)
+    elif tiles:
         ctx.render(cam, precision=prec, seed=0, tile_rank=rank, tile_world=world)
         ctx.synchronize()
         sharding.setup_tile_frame(ctx, rank, world)
@@ -320,7 +326,9 @@ def main():
         """one frame; returns nothing, everything is enqueued on ctx's stream"""
         if e2e:
             ctx.upload_scene(s, m, builder=builder_id)               # H2D: the world, every step (BVH build included)
-        if tiles:
+        if jobs:
+            sharding.render_shared(ctx, cam, prec, world)            # whatever jobs of the frame this rank gets from the shared counter
+        elif tiles:
             # every rank renders all samples of its tiles; ranks != 0 resolve them into rank 0's image over NVLink and signal;
             # rank 0's readback below waits for the signals on its stream.  No host synchronisation inside the step.
             sharding.render_tiles(ctx, cam, rank, world, prec)
@@ -398,7 +406,7 @@ def main():
             multi_check = {"combined_vs_single_gpu_max_byte_diff": int(d.max()),
                            "combined_vs_single_gpu_psnr_db": 99.0 if mse == 0 else float(10 * np.log10(255.0 ** 2 / mse)),
                            "frac_pixels_identical": float((d == 0).mean()), "ranks": world,
-                           "combine": "tiles over NVLink" if tiles else args.combine}
+                           "combine": "tiles over NVLink" if tiles else args.combine, "sharding": "jobs" if jobs else ("tiles" if tiles else "samples")}
         barrier()
 
     # untimed: the fast mode against parity mode on this very frame (north_star image tolerance)
@@ -438,6 +446,8 @@ def main():
                        "seed": 0,
                        "parallelism": (f"tile-interleaved sharding x{world} (pairs of 16x8 tiles), every rank's resolve kernel writes its tiles' "
                                        f"bytes into rank 0's image over NVLink" if tiles else
+                                       f"dynamic sharding x{world}: (tile, sample layer) jobs of the frame from one counter in rank 0's memory "
+                                       f"(system-scope atomics over NVLink), combine={args.combine}" if jobs else
                                        f"sample-range sharding x{world}, combine={args.combine if world > 1 else 'none'}"),
                        "l2": f"256 MB buffer written between timed iterations (L2 flushed); scene inputs are {(s.nbytes + m.nbytes) / 1e3:.0f} KB"},
             "mrays_per_s": rays / ms / 1e3, "rays_per_sample": rays / samples,

@@ -117,8 +117,8 @@ typedef struct {
     int32_t  tile_rank;      /* tile-interleaved sharding: with tile_world > 1 this call renders ALL its samples, but only of the */
     int32_t  tile_world;     /* tile pairs whose index is tile_rank modulo tile_world (RT_WAVEFRONT only; 0 or 1 = the whole image) */
     int32_t  top_cap;        /* tuning: cap on the tree nodes staged in shared memory for a scene in global memory (0 = all that fits, -1 = none) */
-    int32_t  pad;
-} rt_render_opts;
+    int32_t  shared_jobs;    /* N >= 1: this call renders whatever (tile, sample range) jobs of the WHOLE frame it gets from the job counter it */
+} rt_render_opts;            /*    shares with N - 1 other GPUs (rt_jobs_export / rt_jobs_open / rt_jobs_share); 0: the call's own counter */
 
 typedef struct {
     uint64_t rays;           /* path segments traced by the last render (ray_color entries, depth > 0) */
@@ -238,6 +238,23 @@ int rt_ipc_close_peers(rt_ctx *ctx);
  *   peer:  rt_frame_open(blob); per frame rt_render(tile_rank = r, tile_world = N), rt_resolve_tiles(spp_total)
  * A peer must not start frame k + 1 before the root's rt_readback of frame k has returned (one barrier per frame).
  * The per-pixel sums (sum_rgb, PFM) of the root cover its own tiles only. */
+/* Dynamic sharding (a third split next to sample ranges and tiles): the GPUs of a node take the jobs of ONE frame
+ * -- (tile, sample layer) pairs, the unit the wavefront kernel's warps already fetch -- from one counter that lives in the root
+ * GPU's memory; every warp of every GPU advances it with a system-scope atomic over NVLink.  A GPU that is a few per cent slower
+ * (clocks, neighbours) simply takes fewer jobs, so all of them finish together: no rank skew in front of the combine.  Every rank
+ * renders into its own accumulation buffer (zeroed first: it holds only the jobs this rank took); the buffers are then combined
+ * like sample shards (rt_fold_slices + reduce, or the fused IPC resolve).
+ *   root:  rt_jobs_export(blob) once -> blob to every peer;   peer: rt_jobs_open(blob) once
+ *   every rank, every frame: rt_render(ALL samples, shared_jobs = number of GPUs), rt_fold_slices, combine
+ * All ranks must render the same frames in the same order (the counters are used round-robin by frame number, the root clears
+ * them four frames ahead) and stay within three frames of each other -- any per-frame combine guarantees that.
+ * RT_WAVEFRONT + RT_F32 only (the order of a pixel's samples is free there); scene and camera must be the same on all ranks.
+ * rt_jobs_share: the same for several contexts of ONE process (their devices must be able to reach the root's memory). */
+int rt_jobs_export(rt_ctx *ctx, void *handle);             /* RT_IPC_HANDLE_BYTES */
+int rt_jobs_open(rt_ctx *ctx, const void *handle);
+int rt_jobs_share(rt_ctx *ctx, rt_ctx *root);
+int rt_jobs_close(rt_ctx *ctx);
+
 int rt_frame_export(rt_ctx *ctx, void *handle);            /* RT_IPC_HANDLE_BYTES; re-export after the image size changes */
 int rt_frame_open(rt_ctx *ctx, const void *handle);
 int rt_frame_close(rt_ctx *ctx);

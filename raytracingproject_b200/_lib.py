@@ -43,7 +43,7 @@ class RenderOpts(C.Structure):
     _fields_ = [("abi", C.c_uint32), ("precision", C.c_int32), ("variant", C.c_int32),
                 ("sample_begin", C.c_int32), ("sample_count", C.c_int32), ("accumulate", C.c_int32),
                 ("seed", C.c_uint64), ("slices", C.c_int32), ("sched", C.c_int32),
-                ("tile_rank", C.c_int32), ("tile_world", C.c_int32), ("top_cap", C.c_int32), ("pad", C.c_int32)]
+                ("tile_rank", C.c_int32), ("tile_world", C.c_int32), ("top_cap", C.c_int32), ("shared_jobs", C.c_int32)]
 
 
 class Stats(C.Structure):
@@ -81,6 +81,10 @@ SYMBOLS = {
     "rt_ipc_export": (_I, [_VP, _VP]),
     "rt_ipc_open_peers": (_I, [_VP, _VP, _I]),
     "rt_ipc_close_peers": (_I, [_VP]),
+    "rt_jobs_export": (_I, [_VP, _VP]),
+    "rt_jobs_open": (_I, [_VP, _VP]),
+    "rt_jobs_share": (_I, [_VP, _VP]),
+    "rt_jobs_close": (_I, [_VP]),
     "rt_frame_export": (_I, [_VP, _VP]),
     "rt_frame_open": (_I, [_VP, _VP]),
     "rt_frame_close": (_I, [_VP]),

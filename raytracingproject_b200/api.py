@@ -130,9 +130,9 @@ class Context:
         self._ck(self._lib.rt_update_spheres(self._h, L.ptr(spheres), len(spheres), L.ptr(materials), len(materials)))
 
     def render(self, cam, precision=L.F32, seed=0, variant=L.WAVEFRONT, sample_begin=0, sample_count=0,
-               accumulate=False, slices=0, sched=0, tile_rank=0, tile_world=0, top_cap=0):
+               accumulate=False, slices=0, sched=0, tile_rank=0, tile_world=0, top_cap=0, shared_jobs=False):
         o = L.RenderOpts(L.ABI, precision, variant, sample_begin, sample_count, int(accumulate), seed, slices, sched,
-                         tile_rank, tile_world, top_cap, 0)
+                         tile_rank, tile_world, top_cap, int(shared_jobs))
         self._ck(self._lib.rt_render(self._h, C.byref(cam), C.byref(o)))
         w, h = C.c_int(), C.c_int()
         self._lib.rt_image_size(C.byref(cam), C.byref(w), C.byref(h))
@@ -228,6 +228,21 @@ class Context:
         self._ck(self._lib.rt_ipc_close_peers(self._h))
 
     # ---- tile-sharded frames: bytes written into the root's image over NVLink (rt_b200.h) ----
+    # dynamic sharding: one job counter per frame for all GPUs (rt_jobs_*)
+    def jobs_export(self):
+        buf = (C.c_ubyte * L.IPC_HANDLE_BYTES)()
+        self._ck(self._lib.rt_jobs_export(self._h, buf))
+        return bytes(buf)
+
+    def jobs_open(self, blob):
+        self._ck(self._lib.rt_jobs_open(self._h, blob))
+
+    def jobs_share(self, root):
+        self._ck(self._lib.rt_jobs_share(self._h, root._h))
+
+    def jobs_close(self):
+        self._ck(self._lib.rt_jobs_close(self._h))
+
     def frame_export(self):
         buf = (C.c_ubyte * L.IPC_HANDLE_BYTES)()
         self._ck(self._lib.rt_frame_export(self._h, buf))

@@ -24,6 +24,8 @@
 #include "rt_scene.h"
 #include "rt_static.h"
 
+#define RT_JOB_COUNTERS 8                // dynamic sharding: job counters used round-robin by frame number (the root clears them 4 frames ahead)
+
 using namespace rt;
 
 static_assert(sizeof(rt_sphere) == 64, "rt_sphere layout");
@@ -121,6 +123,13 @@ struct rt_ctx {
     void* frame_remote = nullptr;                         // peer: the root's image (rgb8 + counter), mapped through CUDA IPC
     int frame_remote_W = 0, frame_remote_H = 0;
     DevBuf<int> frame_timeout;                            // root: set by the wait kernel when the peers' tiles did not arrive
+
+    // dynamic sharding: the job counters of frames f % RT_JOB_COUNTERS, in the root's memory (own) or mapped from it
+    DevBuf<unsigned> jobs_own;
+    unsigned* jobs_ptr = nullptr;           // what the kernels advance (own.p on the root)
+    void* jobs_mapped = nullptr;            // peer: the CUDA IPC mapping to close
+    unsigned jobs_frame = 0;                // frames rendered with shared_jobs since the counters were set up
+    bool jobs_root = false;
 
     rt_stats stats = {};
 };
@@ -287,6 +296,7 @@ int rt_destroy(rt_ctx* ctx) {
     cudaStreamSynchronize(ctx->stream);
     rt_ipc_close_peers(ctx);
     rt_frame_close(ctx);
+    rt_jobs_close(ctx); ctx->jobs_own.release();
     ctx->nodes.release(); ctx->nodes4.release(); ctx->sa32.release(); ctx->sb32.release(); ctx->sc32.release();
     ctx->sa64.release(); ctx->sb64.release(); ctx->sc64.release();
     ctx->big_a.release(); ctx->big_b.release(); ctx->big_c.release(); ctx->meta.release(); ctx->big_meta.release();
@@ -673,6 +683,7 @@ int render_impl(rt_ctx* ctx, const rt_camera& cam, const rt_render_opts& o, int 
     for (int k = 0; k <= slices; ++k) p.slice_begin[k] = ctx->slice_begin[k];
     p.bulk_layers = std::min(slices, ctx->bulk_layers);
     p.job_group = 2;          // pairs: +0.3-1.5 % over single jobs; 3 and more lose to the tail (profiles/r1_job_group_sweep.txt)
+    if (const char* e = std::getenv("RT_JOB_GROUP")) p.job_group = std::max(1, std::atoi(e));      // (A/B knob)
     p.tiles_x = (ctx->W + 7) / 8; p.tiles_y = (ctx->H + 3) / 4;
     p.accumulate = o.accumulate;
     p.tile_rank = 0; p.tile_world = 1;
@@ -700,6 +711,19 @@ int render_impl(rt_ctx* ctx, const rt_camera& cam, const rt_render_opts& o, int 
     }
     ctx->stats.scene_in_smem = staged ? 1 : (p.scene.n_top > 0 ? 2 : 0);
     ctx->stats.top_nodes_in_smem = p.scene.n_top;
+    p.jobs_shared = 0;
+    p.job_stride = 1;
+    if (const char* e = std::getenv("RT_JOB_STRIDE")) p.job_stride = std::max(1, std::atoi(e));      // (diagnostic knob)
+    if (o.shared_jobs) {
+        // the frame's jobs come from the counter shared with the other GPUs; this rank's buffer holds only what it takes
+        p.jobs_shared = 1;
+        p.job_counter = ctx->jobs_ptr + (ctx->jobs_frame % RT_JOB_COUNTERS);
+        if (ctx->jobs_root)
+            CK(cudaMemsetAsync(ctx->jobs_ptr + ((ctx->jobs_frame + RT_JOB_COUNTERS / 2) % RT_JOB_COUNTERS), 0, sizeof(unsigned), ctx->stream));
+        // this rank's buffer holds only the jobs it takes: everything else must read zero in the combine
+        if (!o.accumulate) CK(cudaMemsetAsync(ctx->accum.p, 0, size_t(slices) * ctx->W * ctx->H * sizeof(Q), ctx->stream));
+        ++ctx->jobs_frame;
+    }
     CK(cudaMemsetAsync(ctx->job_counter.p, 0, sizeof(unsigned int), ctx->stream));
     CK(cudaMemsetAsync(ctx->ray_counter.p, 0, RT_DEBUG_WORDS * sizeof(unsigned long long), ctx->stream));
     CK(cudaEventRecord(ctx->ev[0], ctx->stream));
@@ -725,12 +749,18 @@ extern "C" int rt_render(rt_ctx* ctx, const rt_camera* cam, const rt_render_opts
     if (opts->precision != RT_F32 && opts->precision != RT_F64) return fail(ctx, RT_E_INVALID, "rt_render: bad precision");
     if (opts->variant != RT_MEGAKERNEL && opts->variant != RT_MEGA_LOCKSTEP && opts->variant != RT_WAVEFRONT) return fail(ctx, RT_E_INVALID, "rt_render: variant not built");
     if (opts->tile_world > 1 && (opts->tile_rank < 0 || opts->tile_rank >= opts->tile_world)) return fail(ctx, RT_E_INVALID, "rt_render: tile_rank out of range");
+    if (opts->shared_jobs) {
+        if (!ctx->jobs_ptr) return fail(ctx, RT_E_STATE, "rt_render: shared_jobs needs rt_jobs_export (root) or rt_jobs_open / rt_jobs_share (peers) first");
+        if (opts->variant != RT_WAVEFRONT || opts->precision != RT_F32 || opts->tile_world > 1)
+            return fail(ctx, RT_E_INVALID, "rt_render: shared_jobs is for the wavefront variant in fast mode (f32), without tile sharding");
+    }
     // the wavefront pool keeps a path's sample index in 14 bits and its remaining depth in 16: beyond that the
     // warp-scheduled megakernel (same arithmetic, same image) takes the call
     rt_render_opts eff = *opts;
     // (and a job's tile origin in 15 + 16 bits)
     if (eff.variant == RT_WAVEFRONT && (cam->max_depth > 65535 || cam->image_width > 32000 || image_height_of(*cam) > 32000 ||
         (eff.sample_count > 0 ? eff.sample_count : cam->samples_per_pixel) > 16383)) { eff.variant = RT_MEGAKERNEL; eff.sched = 0; }
+    if (eff.shared_jobs && eff.variant != RT_WAVEFRONT) return fail(ctx, RT_E_INVALID, "rt_render: shared_jobs needs the wavefront variant (and its 16-bit sample / depth limits)");
     if (eff.tile_world > 1 && eff.variant != RT_WAVEFRONT) return fail(ctx, RT_E_INVALID, "rt_render: tile-interleaved sharding needs the wavefront variant (and its 16-bit sample / depth limits)");
     opts = &eff;
     CK(cudaSetDevice(ctx->device));
@@ -751,7 +781,8 @@ extern "C" int rt_render(rt_ctx* ctx, const rt_camera* cam, const rt_render_opts
         tiles = (long long)((W + 15) / 16) * ((H + P / 16 - 1) / (P / 16));
         ctas_per_sm = 1;
     }
-    const long long resident_warps = (long long)ctx->sm_count * ctas_per_sm * (block / 32);
+    // (dynamic sharding: the frame's jobs are shared by opts->shared_jobs GPUs -- the plan is made for all their warps)
+    const long long resident_warps = (long long)ctx->sm_count * ctas_per_sm * (block / 32) * std::max(1, opts->shared_jobs);
     // Parity mode keeps ONE slice unless asked otherwise: the per-pixel sum is then formed sample by
     // sample in the reference's order (src/camera.h:41-44).  Any other order can differ in the last
     // bit, and this scene has sums that sit exactly on a byte boundary of write_color (albedo 0.5 x
@@ -766,7 +797,6 @@ extern "C" int rt_render(rt_ctx* ctx, const rt_camera* cam, const rt_render_opts
     if (slices <= 0) slices = int(std::min<long long>(64, (16 * resident_warps + tiles - 1) / tiles));
     slices = std::max(1, std::min(std::min(slices, RT_MAX_SLICES), std::max(1, sample_count)));
     const size_t elem = opts->precision == RT_F32 ? sizeof(float4) : sizeof(double4);
-
     // a progressive pass may use fewer slices than the buffer holds (it adds into the first ones; resolve sums all)
     if (opts->accumulate && opts->slices <= 0 && ctx->slices > 0) slices = std::min(slices, ctx->slices);
     const bool fits = ctx->W == W && ctx->H == H && ctx->precision == opts->precision && slices <= ctx->slices;
@@ -1066,6 +1096,64 @@ extern "C" int rt_ipc_open_peers(rt_ctx* ctx, const void* handles, int n_peers) 
 // ---- tile-sharded frames: the image hand-over (rt_b200.h) ----
 struct FrameBlob { cudaIpcMemHandle_t h; int32_t W, H, magic, pad; };
 static_assert(sizeof(FrameBlob) == RT_IPC_HANDLE_BYTES, "frame blob size");
+
+// ---- dynamic sharding: one job counter per frame for all GPUs of the node (include/rt_b200.h) ----
+struct JobsBlob { cudaIpcMemHandle_t h; int magic, n, pad0, pad1; };
+static_assert(sizeof(JobsBlob) == RT_IPC_HANDLE_BYTES, "jobs blob size");
+
+extern "C" int rt_jobs_close(rt_ctx* ctx) {
+    if (!ctx) return RT_E_INVALID;
+    if (ctx->jobs_mapped) { cudaIpcCloseMemHandle(ctx->jobs_mapped); ctx->jobs_mapped = nullptr; }
+    ctx->jobs_ptr = nullptr; ctx->jobs_root = false; ctx->jobs_frame = 0;
+    return RT_OK;
+}
+
+extern "C" int rt_jobs_export(rt_ctx* ctx, void* handle) {
+    if (!ctx || !handle) return RT_E_INVALID;
+    CK(cudaSetDevice(ctx->device));
+    rt_jobs_close(ctx);
+    // cudaMalloc'ed on purpose (not from the stream-ordered pool): the block is exported through CUDA IPC
+    CK(ctx->jobs_own.resize(256));
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemset(ctx->jobs_own.p, 0, 256 * sizeof(unsigned)));
+    JobsBlob b;
+    CK(cudaIpcGetMemHandle(&b.h, ctx->jobs_own.p));
+    b.magic = 0x52544a42; b.n = RT_JOB_COUNTERS; b.pad0 = b.pad1 = 0;
+    std::memcpy(handle, &b, sizeof b);
+    ctx->jobs_ptr = ctx->jobs_own.p; ctx->jobs_root = true; ctx->jobs_frame = 0;
+    return RT_OK;
+}
+
+extern "C" int rt_jobs_open(rt_ctx* ctx, const void* handle) {
+    if (!ctx || !handle) return RT_E_INVALID;
+    CK(cudaSetDevice(ctx->device));
+    JobsBlob b;
+    std::memcpy(&b, handle, sizeof b);
+    if (b.magic != 0x52544a42 || b.n != RT_JOB_COUNTERS) return fail(ctx, RT_E_INVALID, "rt_jobs_open: not a job-counter handle of this library version");
+    rt_jobs_close(ctx);
+    void* p = nullptr;
+    CK(cudaIpcOpenMemHandle(&p, b.h, cudaIpcMemLazyEnablePeerAccess));
+    ctx->jobs_mapped = p; ctx->jobs_ptr = static_cast<unsigned*>(p); ctx->jobs_root = false; ctx->jobs_frame = 0;
+    return RT_OK;
+}
+
+extern "C" int rt_jobs_share(rt_ctx* ctx, rt_ctx* root) {
+    if (!ctx || !root) return RT_E_INVALID;
+    if (!root->jobs_root || !root->jobs_own.p) return fail(ctx, RT_E_STATE, "rt_jobs_share: the root has not called rt_jobs_export");
+    if (ctx == root) return RT_OK;
+    CK(cudaSetDevice(ctx->device));
+    if (ctx->device != root->device) {
+        int can = 0;
+        CK(cudaDeviceCanAccessPeer(&can, ctx->device, root->device));
+        if (!can) return fail(ctx, RT_E_INVALID, "rt_jobs_share: this device cannot reach the root's memory");
+        cudaError_t e = cudaDeviceEnablePeerAccess(root->device, 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return cuda_fail(ctx, e, "cudaDeviceEnablePeerAccess");
+        cudaGetLastError();
+    }
+    rt_jobs_close(ctx);
+    ctx->jobs_ptr = root->jobs_own.p; ctx->jobs_root = false; ctx->jobs_frame = root->jobs_frame;
+    return RT_OK;
+}
 
 extern "C" int rt_frame_export(rt_ctx* ctx, void* handle) {
     if (!ctx || !handle) return RT_E_INVALID;

@@ -35,6 +35,8 @@ template <typename T> struct RenderParams {
     int accumulate;
     int tile_rank, tile_world;          // wavefront: tile-interleaved sharding -- this launch renders the tile groups g with g % tile_world == tile_rank
     int th_s, th_l, th_n;               // section thresholds of the warp schedulers (render_sched_kernel, render_pool_kernel)
+    int job_stride;                     // diagnostic (RT_JOB_STRIDE): a fetch advances the counter by job_group * job_stride -- this launch then renders every job_stride-th group only
+    int jobs_shared;                    // wavefront: job_counter is shared with other GPUs (it may live in a peer's memory): system-scope atomics
 };
 
 struct HitRec;

@@ -211,7 +211,7 @@ render_pool_kernel(const RenderParams<T> p) {
                     int job = 0;
                     if (pend_left > 0) { job = pend_next++; --pend_left; }
                     else {
-                        if (lane == 0) job = int(atomicAdd(p.job_counter, unsigned(group)));
+                        if (lane == 0) job = int(p.jobs_shared ? atomicAdd_system(p.job_counter, unsigned(group * p.job_stride)) : atomicAdd(p.job_counter, unsigned(group * p.job_stride)));
                         job = __shfl_sync(FULL, job, 0);
                         pend_next = job + 1; pend_left = group - 1;
                     }

@@ -73,6 +73,27 @@ def render_sharded(ctx, cam, rank, world, precision, seed=0, slices=0, variant=1
     return begin, count
 
 
+# ------------------------------------------------------------------------- dynamic sharding --
+# The third partition: the ranks take the (tile, sample layer) jobs of ONE frame from a counter in rank 0's memory, advanced
+# by every warp of every GPU with a system-scope atomic over NVLink (rt_jobs_*).  A slower GPU takes fewer jobs, all ranks
+# finish together; the partial buffers are combined like sample shards (fold + reduce).
+
+def setup_shared_jobs(ctx, rank, world, group=None):
+    """Once: rank 0 creates the frame counters and exports them, every other rank maps them."""
+    import torch.distributed as dist
+    blob = [ctx.jobs_export() if rank == 0 else None]
+    dist.broadcast_object_list(blob, src=0, group=group)
+    if rank != 0:
+        ctx.jobs_open(blob[0])
+    dist.barrier(group=group)
+
+
+def render_shared(ctx, cam, precision, world=1, seed=0):
+    """This rank's share of the frame's jobs -- whatever it gets -- of ALL samples (asynchronous).  world = how many GPUs share
+    the list (the frame is cut into jobs for all their warps)."""
+    ctx.render(cam, precision=precision, seed=seed, shared_jobs=max(1, int(world)))
+
+
 # ------------------------------------------------------------------ tile-interleaved sharding --
 # The alternative partition of SURVEY.md 8e: rank g renders ALL samples of the tile pairs whose index is g modulo the
 # world size (pairs of 16 x 8 pixel tiles, interleaved finely enough that sky and sphere rows balance out), so the combine

@@ -21,7 +21,7 @@ def test_fast_resolve_of_a_rendered_frame_equals_the_general_kernels(ctx_scene, 
     spp = 16
     cam = rt.camera_rtiow(333, spp, 12)                              # 333 x 187: the pixel count is not a multiple of 4
     ctx.render(cam, precision=rt.F32, seed=3, variant=rt.WAVEFRONT, slices=slices)
-    assert ctx.stats()["slices"] == slices
+    assert ctx.stats()["slices"] == slices and ctx.accum_buffer()[1] == slices * ctx.width * ctx.height * 4
     for total in (spp, 0):                                           # 0: divide by the samples in the buffer
         fast, fused, text, exact, sums = _both_ways(ctx, total)
         assert np.array_equal(fast, exact)
@@ -70,3 +70,4 @@ def test_fast_resolve_on_byte_boundaries(ctx_scene, rt, slices):
     # the boundary row itself: byte k exactly (int(256 * sqrt((k/256)^2)) = k), 255 from 0.999 on (src/color.h:31)
     assert np.array_equal(exact[0, :, 0], np.minimum(np.arange(256), 255).astype(np.uint8))
     assert good.sum() >= (H - 3) * W
+

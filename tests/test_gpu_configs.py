@@ -383,3 +383,41 @@ def test_refit_after_the_spheres_moved_matches_a_fresh_scene(ctx, rt, O, g, buil
         ctx.update_spheres(shrunk, m2)                                 # the ground would have to enter it
     ctx.render(cam, precision=rt.F64, seed=5)                          # a refused update leaves the scene as it was
     assert np.array_equal(ctx.readback(3)["rgb8"], ref["rgb8"])
+
+
+def test_shared_job_counter_two_contexts_of_one_process(rt, O, scene):
+    """dynamic sharding (rt_jobs_*), exercised on ONE GPU: two contexts share the frame counters; whichever renders first takes
+    every job, the other finds none -- the sum of the two buffers is the frame either way, frame after frame"""
+    import torch
+    from raytracingproject_b200 import sharding
+    s, m = scene
+    a, b = rt.Context(0), rt.Context(0)
+    try:
+        for c in (a, b):
+            c.upload_scene(s.view(rt.SPHERE), m.view(rt.MATERIAL))
+        cam = rt.camera_rtiow(240, 7, 50)
+        with pytest.raises(rt.RtError):
+            a.render(cam, precision=rt.F32, seed=2, shared_jobs=True)              # no counters yet
+        a.render(cam, precision=rt.F32, seed=2)
+        want = a.readback(7, want_sum=False)["rgb8"]; want_rays = a.stats()["rays"]
+        a.jobs_export()
+        with pytest.raises(rt.RtError):
+            b.jobs_share(b)                                                        # b is not a root
+        b.jobs_share(a)
+        with pytest.raises(rt.RtError):
+            a.render(cam, precision=rt.F64, seed=2, shared_jobs=True)              # parity mode keeps the sample order: refused
+        for frame, order in enumerate(((a, b), (b, a), (a, b), (b, a), (a, b), (a, b), (b, a), (a, b), (b, a), (a, b))):   # > RT_JOB_COUNTERS frames
+            for c in order:
+                c.render(cam, precision=rt.F32, seed=2, shared_jobs=True)
+                c.synchronize()
+            first, second = order
+            assert first.stats()["rays"] == want_rays and second.stats()["rays"] == 0, frame
+            for c in order:
+                c.fold_slices(); c.synchronize()
+            ta, tb = sharding.alias_accum_tensor(a, layers=1), sharding.alias_accum_tensor(b, layers=1)
+            assert float(sharding.alias_accum_tensor(second, layers=1).abs().sum()) == 0.0
+            ta.add_(tb); torch.cuda.synchronize()
+            d = np.abs(a.readback(7, want_sum=False)["rgb8"].astype(int) - want.astype(int))       # float sums in another order: a byte may move by one
+            assert d.max() <= 1 and (d > 0).any(-1).mean() < 2e-3, (frame, int(d.max()))
+    finally:
+        a.close(); b.close()

@@ -7,6 +7,8 @@ rank 0 alone and with the CPU oracle:
   samples+ipc    sample-range shards, fold, rank 0's resolve kernel reads the peer's buffer over NVLink (CUDA IPC)
   tiles          tile-interleaved shards: every rank renders all samples of its tiles, resolves them and writes the
                  bytes straight into rank 0's image over NVLink -- no arithmetic in the combine
+  jobs+nccl      dynamic shards (fast mode): both GPUs take the (tile, sample layer) jobs of the frame from one counter in
+                 rank 0's memory (system-scope atomics over NVLink), fold, NCCL reduce
 """
 import os
 import socket
@@ -84,6 +86,31 @@ def _worker(rank, world, port, q):
                 res[pname + "_tiles_ppm"] = res_tiles["ppm"]
                 res[pname + "_tiles_rays"] = res_tiles["rays"]
             dist.barrier()
+            # --- dynamic shards: one job counter for both GPUs (fast mode only), three frames in a row
+            if prec == rt.F32:
+                sharding.setup_shared_jobs(ctx, rank, world)
+                for frame in range(3):
+                    sharding.render_shared(ctx, cam, prec, world, seed=5)
+                    rays = torch.tensor([ctx.stats()["rays"]], dtype=torch.int64, device="cuda")
+                    ctx.fold_slices()
+                    acc = sharding.alias_accum_tensor(ctx, layers=1)
+                    with torch.cuda.stream(stream):
+                        sharding.reduce_partials(acc, dst=0)
+                    stream.synchronize()
+                    both = torch.tensor([1 if ctx.stats()["rays"] > 0 else 0], dtype=torch.int64, device="cuda")
+                    dist.all_reduce(rays); dist.all_reduce(both)
+                    if rank == 0:
+                        res[f"f32_jobs{frame}"] = ctx.readback(spp, want_sum=False)["rgb8"]
+                        res[f"f32_jobs{frame}_rays"] = int(rays.item())
+                        res[f"f32_jobs{frame}_ranks_with_work"] = int(both.item())
+                    dist.barrier()
+                ctx.jobs_close()
+                try:
+                    ctx.render(cam, precision=prec, seed=5, shared_jobs=True)      # counters closed: must be refused
+                    res["jobs_closed_refused"] = False
+                except rt.RtError:
+                    res["jobs_closed_refused"] = True
+                dist.barrier()
             # --- the same frame on rank 0 alone
             if rank == 0:
                 ctx.render(cam, precision=prec, seed=5)
@@ -141,6 +168,13 @@ def test_two_gpus_every_combine_gives_the_single_gpu_frame():
         else:
             assert abs(res["f32_rays"] - ref["rays"]) / ref["rays"] < 5e-3
             assert (np.abs(solo.astype(int) - ref["rgb8"].astype(int)).max(-1) <= 1).mean() >= 0.999
+        if pname == "f32":
+            assert res["jobs_closed_refused"]
+            for frame in range(3):
+                d = np.abs(res[f"f32_jobs{frame}"].astype(int) - solo.astype(int))
+                assert d.max() <= 1 and (d > 0).any(-1).mean() < 2e-3, ("jobs", frame, int(d.max()))
+                assert res[f"f32_jobs{frame}_rays"] == res["f32_solo_rays"]       # every job rendered exactly once, by one GPU or the other
+                assert res[f"f32_jobs{frame}_ranks_with_work"] >= 1                # (a frame this small may go to whichever GPU starts first)
         for mode in ("nccl", "ipc", "tiles"):
             d = np.abs(res[f"{pname}_{mode}"].astype(int) - solo.astype(int))
             # two partial sums re-associate the per-pixel sum (float: the last bits; double: 1e-16): a byte may move by one
