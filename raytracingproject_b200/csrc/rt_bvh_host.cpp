@@ -27,48 +27,68 @@ struct Box {
 
 struct TmpNode { Box box; int left = -1, right = -1; int first = 0, count = 0; };   // leaf iff left < 0
 
+// Top-down SAH builder over index arrays that are sorted ONCE per axis -- by (centroid, index), a total order -- and kept sorted
+// by stable partitions: a range [first, first + count) holds the same primitives in all three arrays, each in its axis' order,
+// so the exact sweep of a node is three linear passes and the whole build O(n log n).  (The first version re-sorted every
+// range four times per node: 0.6 ms for the 485 spheres of the final scene, on every rt_upload_scene.)  Same splits, same leaf
+// order -- a leaf's slots are in z order, as the last sweep of the old builder left them -- hence the same tree, bit for bit.
 struct Builder {
     const std::vector<HostBox>& boxes;
     int max_leaf;
-    std::vector<int> idx;
+    std::vector<int> idx;                 // out: slot -> primitive
+    std::vector<int> ord[3], tmp;
+    std::vector<unsigned char> right_side;
     std::vector<TmpNode> nodes;
     std::vector<float> cen[3];
     std::vector<double> suffix;
 
     Builder(const std::vector<HostBox>& b, int ml) : boxes(b), max_leaf(ml) {
-        idx.resize(b.size());
-        std::iota(idx.begin(), idx.end(), 0);
+        const size_t n = b.size();
+        idx.resize(n); tmp.resize(n); right_side.assign(n, 0);
         for (int a = 0; a < 3; ++a) {
-            cen[a].resize(b.size());
-            for (size_t i = 0; i < b.size(); ++i) cen[a][i] = 0.5f * (b[i].lo[a] + b[i].hi[a]);
+            cen[a].resize(n);
+            for (size_t i = 0; i < n; ++i) cen[a][i] = 0.5f * (b[i].lo[a] + b[i].hi[a]);
+            ord[a].resize(n);
+            std::iota(ord[a].begin(), ord[a].end(), 0);
+            const std::vector<float>& c = cen[a];
+            std::sort(ord[a].begin(), ord[a].end(), [&c](int x, int y) { return c[x] < c[y] || (c[x] == c[y] && x < y); });
         }
-        suffix.resize(b.size() + 1);
-        nodes.reserve(2 * b.size() + 1);
+        suffix.resize(n + 1);
+        nodes.reserve(2 * n + 1);
+    }
+
+    // the primitives with right_side == 0 to the front of every array's range, order kept
+    void split_ranges(int first, int count) {
+        for (int a = 0; a < 3; ++a) {
+            int* o = ord[a].data() + first;
+            int nl = 0, nr = 0;
+            for (int i = 0; i < count; ++i) { if (right_side[o[i]]) tmp[nr++] = o[i]; else o[nl++] = o[i]; }
+            std::memcpy(o + nl, tmp.data(), size_t(nr) * sizeof(int));
+        }
     }
 
     int build(int first, int count) {
         const int me = int(nodes.size());
         nodes.emplace_back();
         Box bb;
-        for (int i = first; i < first + count; ++i) bb.grow(boxes[idx[i]]);
+        for (int i = first; i < first + count; ++i) bb.grow(boxes[ord[0][i]]);
         nodes[me].box = bb;
         nodes[me].first = first; nodes[me].count = count;
-        if (count == 1) return me;
+        if (count == 1) { idx[first] = ord[0][first]; return me; }
 
         // exact SAH sweep on every axis for small ranges, 32-bin SAH above
         const double inv_area = 1.0 / std::max(bb.area(), 1e-300);
         double best_cost = std::numeric_limits<double>::infinity();
-        int best_axis = -1, best_split = -1;      // split = number of prims on the left after sorting by axis
+        int best_axis = -1, best_split = -1;      // split = number of prims on the left in the axis' order
         float best_plane = 0; bool binned = count > 4096;
         if (!binned) {
             for (int a = 0; a < 3; ++a) {
-                std::sort(idx.begin() + first, idx.begin() + first + count, [&](int x, int y) {
-                    return cen[a][x] < cen[a][y] || (cen[a][x] == cen[a][y] && x < y); });
+                const int* o = ord[a].data() + first;
                 Box r;
-                for (int i = count - 1; i >= 1; --i) { r.grow(boxes[idx[first + i]]); suffix[i] = r.area(); }
+                for (int i = count - 1; i >= 1; --i) { r.grow(boxes[o[i]]); suffix[i] = r.area(); }
                 Box l;
                 for (int i = 1; i < count; ++i) {
-                    l.grow(boxes[idx[first + i - 1]]);
+                    l.grow(boxes[o[i - 1]]);
                     const double cost = 1.0 + (l.area() * i + suffix[i] * (count - i)) * inv_area;
                     if (cost < best_cost) { best_cost = cost; best_axis = a; best_split = i; }
                 }
@@ -76,14 +96,14 @@ struct Builder {
         } else {
             const int NB = 32;
             for (int a = 0; a < 3; ++a) {
-                float cmin = INFINITY, cmax = -INFINITY;
-                for (int i = first; i < first + count; ++i) { cmin = std::min(cmin, cen[a][idx[i]]); cmax = std::max(cmax, cen[a][idx[i]]); }
+                const int* o = ord[a].data() + first;
+                const float cmin = cen[a][o[0]], cmax = cen[a][o[count - 1]];
                 if (!(cmax > cmin)) continue;
                 Box bin[NB]; int cnt[NB] = { 0 };
                 const float scale = NB / (cmax - cmin);
-                for (int i = first; i < first + count; ++i) {
-                    int k = std::min(NB - 1, std::max(0, int((cen[a][idx[i]] - cmin) * scale)));
-                    bin[k].grow(boxes[idx[i]]); cnt[k]++;
+                for (int i = 0; i < count; ++i) {
+                    int k = std::min(NB - 1, std::max(0, int((cen[a][o[i]] - cmin) * scale)));
+                    bin[k].grow(boxes[o[i]]); cnt[k]++;
                 }
                 double ra[NB]; int rc[NB];
                 Box r; int c = 0;
@@ -98,23 +118,22 @@ struct Builder {
             }
         }
         const double leaf_cost = double(count);
-        if (count <= max_leaf && (best_axis < 0 || leaf_cost <= best_cost)) return me;      // leaf
+        if (count <= max_leaf && (best_axis < 0 || leaf_cost <= best_cost)) {               // leaf: slots in z order
+            std::memcpy(idx.data() + first, ord[2].data() + first, size_t(count) * sizeof(int));
+            return me;
+        }
         if (best_axis < 0) {                                                                // all centroids equal
             best_axis = 0; best_split = count / 2; binned = false;
         }
-        if (!binned) {
-            if (best_axis != 2 || true)
-                std::sort(idx.begin() + first, idx.begin() + first + count, [&](int x, int y) {
-                    return cen[best_axis][x] < cen[best_axis][y] || (cen[best_axis][x] == cen[best_axis][y] && x < y); });
-        } else {
-            auto mid = std::partition(idx.begin() + first, idx.begin() + first + count, [&](int x) {
-                return cen[best_axis][x] < best_plane; });
-            best_split = int(mid - (idx.begin() + first));
-            if (best_split == 0 || best_split == count) {
-                std::sort(idx.begin() + first, idx.begin() + first + count, [&](int x, int y) { return cen[best_axis][x] < cen[best_axis][y]; });
-                best_split = count / 2;
-            }
+        const int* o = ord[best_axis].data() + first;
+        if (binned) {                       // left = centroids below the plane (they are a prefix of the axis' order)
+            int k = 0;
+            while (k < count && cen[best_axis][o[k]] < best_plane) ++k;
+            best_split = k;
+            if (best_split == 0 || best_split == count) best_split = count / 2;
         }
+        for (int i = 0; i < count; ++i) right_side[o[i]] = i >= best_split;
+        split_ranges(first, count);
         const int l = build(first, best_split);
         const int r = build(first + best_split, count - best_split);
         nodes[me].left = l; nodes[me].right = r;
