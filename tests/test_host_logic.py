@@ -90,6 +90,13 @@ def test_host_bvh_builder(rt):
         b = rt.build_bvh_host(small, max_leaf)
         _check_bvh(small, b)
         assert b["depth"] <= 64
+    # the tree of the final scene is pinned: the O(n log n) builder of round 2 (index arrays sorted once per axis) must keep
+    # producing, bit for bit, what the first builder (four sorts per node) produced -- records and slot order
+    import hashlib
+    b = rt.build_bvh_host(small, 4)
+    assert b["depth"] == 11
+    assert hashlib.sha256(np.ascontiguousarray(b["order"]).tobytes() + np.ascontiguousarray(b["nodes"]).tobytes()).hexdigest() == \
+        "eb3228add990607893fcea556ee31b23dd2e9908c3d1367a805d0c9670cfc51b"
     b = rt.build_bvh_host(s[:1])                    # single sphere: root is a leaf
     assert b["root_ref"] < 0 and len(b["nodes"]) == 0
     _check_bvh(s[:1], b)
