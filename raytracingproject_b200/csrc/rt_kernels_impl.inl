@@ -38,7 +38,7 @@ template <> cudaError_t launch_render_sched<RT_REAL>(const RenderParams<RT_REAL>
 
 template <bool STAGED, int P, int BLOCK, bool WIDE = false>
 static cudaError_t launch_pool_shape(const RenderParams<RT_REAL>& p, int sm_count, cudaStream_t st) {
-    static_assert(Pool<RT_REAL, P>::bytes == int(P * (11 * sizeof(RT_REAL) + 4 + 2 * 2 + 4) + ((RT_DYNAMIC_ITEMS != 0 && sizeof(RT_REAL) == 4) ? 80 : 16 * RT_RING)), "pool_warp_bytes mirrors Pool::bytes");
+    static_assert(Pool<RT_REAL, P>::bytes == int(P * (12 * sizeof(RT_REAL) + 2 * 2 + 4) + ((RT_DYNAMIC_ITEMS != 0 && sizeof(RT_REAL) == 4) ? 80 : 16 * RT_RING)), "pool_warp_bytes mirrors Pool::bytes");
     const size_t smem = (STAGED ? staged_bytes_aligned<RT_REAL>(p.scene.n_nodes, p.scene.n_slots) : (WIDE ? 0 : size_t(p.scene.n_top) * 64)) +
                         size_t(BLOCK / 32) * Pool<RT_REAL, P>::bytes;
     cudaError_t e = cudaFuncSetAttribute(render_pool_kernel<RT_REAL, STAGED, P, BLOCK, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));

@@ -66,7 +66,7 @@ inline void pool_shape(int shape, int* paths, int* block) {
 #define RT_DYNAMIC_ITEMS 1             // (rt_wavefront.cuh)
 #endif
 template <typename T> inline size_t pool_warp_bytes(int paths) {      // + the warp's job descriptors (dynamic mode, float: 4 entries of 32 bytes)
-    return size_t(paths) * (11 * sizeof(T) + 4 + 2 * 2 + 4) + ((RT_DYNAMIC_ITEMS != 0 && sizeof(T) == 4) ? 80 : 16 * RT_RING);
+    return size_t(paths) * (12 * sizeof(T) + 2 * 2 + 4) + ((RT_DYNAMIC_ITEMS != 0 && sizeof(T) == 4) ? 80 : 16 * RT_RING);      // three quads of T, two 16-bit words, four list bytes
 }
 #define RT_POOL_DEFAULT_SHAPE(T) (sizeof(T) == 4 ? 3 : 0)
 #define RT_POOL_UNSTAGED_SHAPE(T) (sizeof(T) == 4 ? 9 : 0)

@@ -58,14 +58,16 @@ namespace rt {
 #endif
 
 template <typename T, int P> struct Pool {
-    enum { OX, OY, OZ, TM, DX, DY, DZ, TR, TG, TB, TBEST, NF };        // T arrays [P]
-    enum { BEST, NI };                                                  // int arrays [P]
+    // three arrays [P] of 4 x T (one 128-bit -- 2 x 128-bit in parity mode -- load or store each): a path's origin + time, its
+    // direction + closest hit distance, its throughput + closest hit slot (an int carried in the bits of the fourth component).
+    // The first layout kept eleven scalar arrays: a shading batch then cost 12 loads and 9 stores per path instead of 3 and 3
+    enum { QO, QD, QT, NQ };
     enum { SAMPLE, DEPTH, NH };                                         // 16-bit arrays [P]: ring entry (top 1 or 2 bits) | next sample relative to the job's first (all ones: done with that job); bounces left
     enum { QUEUE, LOPAQUE, LPIXEL, LEND, NL };                          // byte lists [P]; LPIXEL (dynamic mode): the pixel of the tile a slot is working on
     // dynamic mode (fast mode only, see the END stage): slots take (pixel, sample) items of the open jobs instead of owning a pixel
     static constexpr bool dyn = RT_DYNAMIC_ITEMS != 0 && sizeof(T) == 4;
     static constexpr int ring = dyn ? 4 : RT_RING, ring_bytes = dyn ? 16 * ring + 16 : 16 * ring;   // job descriptors (int4) of the warp (+ counters), after the lists
-    static constexpr int bytes = NF * P * int(sizeof(T)) + NI * P * 4 + NH * P * 2 + NL * P + ring_bytes;
+    static constexpr int bytes = NQ * P * 4 * int(sizeof(T)) + NH * P * 2 + NL * P + ring_bytes;
     static constexpr int tile_w = 16, tile_h = P / 16;
     static_assert(P % 32 == 0 && P <= 128, "pool: path id is 7 bits, lists are filled 32 at a time");
 };
@@ -80,6 +82,13 @@ __device__ __forceinline__ void accum_add(double4* dst, const Vec<double>& c) {
     v.x += c.x; v.y += c.y; v.z += c.z;
     *dst = v;
 }
+
+// the closest-hit slot rides in the fourth component of the throughput quad, bit for bit (no arithmetic ever touches it)
+__device__ __forceinline__ float  slot_bits(int s, float)  { return __int_as_float(s); }
+__device__ __forceinline__ double slot_bits(int s, double) { return __longlong_as_double((long long)s); }
+__device__ __forceinline__ int bits_slot(float w)  { return __float_as_int(w); }
+__device__ __forceinline__ int bits_slot(double w) { return int(__double_as_longlong(w)); }
+template <typename Q, typename T> __device__ __forceinline__ Q quad(T x, T y, T z, T w) { Q q; q.x = x; q.y = y; q.z = z; q.w = w; return q; }
 
 template <typename T, bool STAGED, int P, int BLOCK, bool WIDE = false>
 __global__ void __launch_bounds__(BLOCK, 1)
@@ -104,9 +113,8 @@ render_pool_kernel(const RenderParams<T> p) {
     }
 
     unsigned char* wb = smem + (STAGED ? staged_bytes_aligned<T>(sv.n_nodes, sv.n_slots) : size_t(n_top) * 64) + size_t(warp) * L::bytes;
-    T* const F = reinterpret_cast<T*>(wb);
-    int* const I = reinterpret_cast<int*>(F + L::NF * P);
-    unsigned short* const S = reinterpret_cast<unsigned short*>(I + L::NI * P);
+    Q* const G = reinterpret_cast<Q*>(wb);                          // G[L::QO * P + pid] ...
+    unsigned short* const S = reinterpret_cast<unsigned short*>(G + L::NQ * P);
     unsigned char* const B = reinterpret_cast<unsigned char*>(S + L::NH * P);
 
     int4* const ring = reinterpret_cast<int4*>(B + L::NL * P);   // job descriptors: (bx | by << 16, s_begin, s_end, slice)
@@ -190,8 +198,8 @@ render_pool_kernel(const RenderParams<T> p) {
                             const int4 J = ring[jb];
                             const int pix = B[L::LPIXEL * P + pid];
                             const int i = (J.x & 0xffff) + (pix & 15), j = (J.x >> 16) + (pix >> 4);
-                            const Vec<T> d = mk<T>(F[L::DX * P + pid], F[L::DY * P + pid], F[L::DZ * P + pid]);
-                            const Vec<T> thr = mk<T>(F[L::TR * P + pid], F[L::TG * P + pid], F[L::TB * P + pid]);
+                            const Q qd = G[L::QD * P + pid], qt = G[L::QT * P + pid];
+                            const Vec<T> d = mk<T>(qd.x, qd.y, qd.z), thr = mk<T>(qt.x, qt.y, qt.z);
                             accum_add(p.accum + size_t(J.w) * layer + size_t(j) * size_t(W) + size_t(i), thr * sky<T>(d));
                         }
                     }
@@ -266,9 +274,9 @@ render_pool_kernel(const RenderParams<T> p) {
                             PhiloxT<RT_PHILOX_TABLE != 0> rng; if (RT_PHILOX_TABLE) rng.init(p.keys); else rng.init(p.seed);
                             rng.set(uint32_t(j) * uint32_t(W) + uint32_t(i), uint32_t(J.y + srel), 0u);
                             const Ray<T> ray = get_ray<T>(p.cam, i, j, rng);
-                            F[L::OX * P + pid] = ray.o.x; F[L::OY * P + pid] = ray.o.y; F[L::OZ * P + pid] = ray.o.z; F[L::TM * P + pid] = ray.tm;
-                            F[L::DX * P + pid] = ray.d.x; F[L::DY * P + pid] = ray.d.y; F[L::DZ * P + pid] = ray.d.z;
-                            F[L::TR * P + pid] = T(1); F[L::TG * P + pid] = T(1); F[L::TB * P + pid] = T(1);
+                            G[L::QO * P + pid] = quad<Q, T>(ray.o.x, ray.o.y, ray.o.z, ray.tm);
+                            G[L::QD * P + pid] = quad<Q, T>(ray.d.x, ray.d.y, ray.d.z, T(0));
+                            G[L::QT * P + pid] = quad<Q, T>(T(1), T(1), T(1), slot_bits(-1, T(0)));
                             S[L::SAMPLE * P + pid] = (unsigned short)((ent << 14) | srel); S[L::DEPTH * P + pid] = (unsigned short)p.max_depth;
                             B[L::LPIXEL * P + pid] = (unsigned char)pix;
                             push = true;
@@ -340,8 +348,8 @@ render_pool_kernel(const RenderParams<T> p) {
                     int4 J = ring[jb];
                     int i = (J.x & 0xffff) + (pid & 15), j = (J.x >> 16) + (pid >> 4);
                     if (!(e & 0x80)) {
-                        const Vec<T> d = mk<T>(F[L::DX * P + pid], F[L::DY * P + pid], F[L::DZ * P + pid]);
-                        const Vec<T> thr = mk<T>(F[L::TR * P + pid], F[L::TG * P + pid], F[L::TB * P + pid]);
+                        const Q qd = G[L::QD * P + pid], qt = G[L::QT * P + pid];
+                        const Vec<T> d = mk<T>(qd.x, qd.y, qd.z), thr = mk<T>(qt.x, qt.y, qt.z);
                         const Vec<T> c = thr * sky<T>(d);
                         Q* dst = p.accum + size_t(J.w) * layer + size_t(j) * size_t(W) + size_t(i);
                         accum_add(dst, c);
@@ -367,9 +375,9 @@ render_pool_kernel(const RenderParams<T> p) {
                         PhiloxT<RT_PHILOX_TABLE != 0> rng; if (RT_PHILOX_TABLE) rng.init(p.keys); else rng.init(p.seed);
                         rng.set(uint32_t(j) * uint32_t(W) + uint32_t(i), uint32_t(s), 0u);
                         const Ray<T> ray = get_ray<T>(p.cam, i, j, rng);
-                        F[L::OX * P + pid] = ray.o.x; F[L::OY * P + pid] = ray.o.y; F[L::OZ * P + pid] = ray.o.z; F[L::TM * P + pid] = ray.tm;
-                        F[L::DX * P + pid] = ray.d.x; F[L::DY * P + pid] = ray.d.y; F[L::DZ * P + pid] = ray.d.z;
-                        F[L::TR * P + pid] = T(1); F[L::TG * P + pid] = T(1); F[L::TB * P + pid] = T(1);
+                        G[L::QO * P + pid] = quad<Q, T>(ray.o.x, ray.o.y, ray.o.z, ray.tm);
+                        G[L::QD * P + pid] = quad<Q, T>(ray.d.x, ray.d.y, ray.d.z, T(0));
+                        G[L::QT * P + pid] = quad<Q, T>(T(1), T(1), T(1), slot_bits(-1, T(0)));
                         S[L::SAMPLE * P + pid] = (unsigned short)((jb << SH) | (sidx + 1)); S[L::DEPTH * P + pid] = (unsigned short)p.max_depth;
                         push = true;
                     } else {
@@ -407,12 +415,11 @@ render_pool_kernel(const RenderParams<T> p) {
                     if (idx < n_q) {
                         const int pid = B[L::QUEUE * P + idx];
                         Ray<T> ray;
-                        ray.o = mk<T>(F[L::OX * P + pid], F[L::OY * P + pid], F[L::OZ * P + pid]);
-                        ray.d = mk<T>(F[L::DX * P + pid], F[L::DY * P + pid], F[L::DZ * P + pid]);
-                        ray.tm = F[L::TM * P + pid];
+                        const Q qo = G[L::QO * P + pid], qd = G[L::QD * P + pid];
+                        ray.o = mk<T>(qo.x, qo.y, qo.z); ray.d = mk<T>(qd.x, qd.y, qd.z); ray.tm = qo.w;
                         T tb; int bslot;
                         trav_big<T>(sv, ray, T(0.001), T(INFINITY), tb, bslot);
-                        F[L::TBEST * P + pid] = tb; I[L::BEST * P + pid] = bslot;
+                        G[L::QD * P + pid].w = tb; G[L::QT * P + pid].w = slot_bits(bslot, T(0));
                     }
                 }
                 __syncwarp();
@@ -439,15 +446,14 @@ render_pool_kernel(const RenderParams<T> p) {
                         RT_STAT(5, 1); RT_STAT(6, min(nP, avail)); RT_STAT(7, nN + nL);
                         if (isP && rank < avail) {
                             pid = B[L::QUEUE * P + head + rank];
-                            ray.o = mk<T>(F[L::OX * P + pid], F[L::OY * P + pid], F[L::OZ * P + pid]);
-                            ray.d = mk<T>(F[L::DX * P + pid], F[L::DY * P + pid], F[L::DZ * P + pid]);
-                            ray.tm = F[L::TM * P + pid];
+                            const Q qo = G[L::QO * P + pid], qd = G[L::QD * P + pid];
+                            ray.o = mk<T>(qo.x, qo.y, qo.z); ray.d = mk<T>(qd.x, qd.y, qd.z); ray.tm = qo.w;
                             tv.tbest = T(INFINITY); tv.best_slot = -1;
                             if (sv.n_big > 0) {
-                                tv.tbest = F[L::TBEST * P + pid]; tv.best_slot = I[L::BEST * P + pid];
+                                tv.tbest = qd.w; tv.best_slot = bits_slot(G[L::QT * P + pid].w);
                             }
                             trav_setup<T>(sv, ray, tv);
-                            if (tv.cur == RT_SENTINEL) { F[L::TBEST * P + pid] = tv.tbest; I[L::BEST * P + pid] = tv.best_slot; }   // no tree
+                            if (tv.cur == RT_SENTINEL) { G[L::QD * P + pid].w = tv.tbest; G[L::QT * P + pid].w = slot_bits(tv.best_slot, T(0)); }   // no tree
                             ++my_rays;                                   // one ray_color entry with depth > 0
                         }
                         head += min(nP, avail);
@@ -455,7 +461,7 @@ render_pool_kernel(const RenderParams<T> p) {
                         RT_STAT(8, 1); RT_STAT(9, nL); RT_STAT(10, nN); RT_STAT(11, nP);
                         if (!isN && !isP) {
                             trav_leaf<T>(sv, st.sa, st.sb, st.meta, ray, T(0.001), tv, stack);
-                            if (tv.cur == RT_SENTINEL) { F[L::TBEST * P + pid] = tv.tbest; I[L::BEST * P + pid] = tv.best_slot; }
+                            if (tv.cur == RT_SENTINEL) { G[L::QD * P + pid].w = tv.tbest; G[L::QT * P + pid].w = slot_bits(tv.best_slot, T(0)); }
                         }
                     } else {
                         // node visits, RT_NODE_VISITS per head count, repeated while most of the lanes that started them
@@ -475,7 +481,7 @@ render_pool_kernel(const RenderParams<T> p) {
                             }
                             now = __popc(__ballot_sync(FULL, tv.cur >= 0));
                         } while (now > 0 && now * 8 >= nN * th_n);
-                        if (isN && tv.cur == RT_SENTINEL) { F[L::TBEST * P + pid] = tv.tbest; I[L::BEST * P + pid] = tv.best_slot; }
+                        if (isN && tv.cur == RT_SENTINEL) { G[L::QD * P + pid].w = tv.tbest; G[L::QT * P + pid].w = slot_bits(tv.best_slot, T(0)); }
                     }
                 }
             }
@@ -492,7 +498,7 @@ render_pool_kernel(const RenderParams<T> p) {
                 int key = -1, pid = 0;
                 if (idx < n_q) {
                     pid = B[L::QUEUE * P + idx];
-                    const int slot = I[L::BEST * P + pid];
+                    const int slot = bits_slot(G[L::QT * P + pid].w);
                     if (slot < 0) key = 2;
                     else {
                         const int m = slot < sv.n_slots ? st.meta[slot] : sv.big_meta[slot - sv.n_slots];
@@ -534,11 +540,10 @@ render_pool_kernel(const RenderParams<T> p) {
                         const int pix = L::dyn ? int(B[L::LPIXEL * P + pid]) : pid;            // dynamic mode: the slot's current pixel
                         const int i = (J.x & 0xffff) + (pix & 15), j = (J.x >> 16) + (pix >> 4);
                         Ray<T> ray;
-                        ray.o = mk<T>(F[L::OX * P + pid], F[L::OY * P + pid], F[L::OZ * P + pid]);
-                        ray.d = mk<T>(F[L::DX * P + pid], F[L::DY * P + pid], F[L::DZ * P + pid]);
-                        ray.tm = F[L::TM * P + pid];
-                        T t = F[L::TBEST * P + pid];
-                        const int slot = I[L::BEST * P + pid], s = J.y + (sw & DONE) + (L::dyn ? 1 : 0);   // (static mode keeps "next sample" here)
+                        const Q qo = G[L::QO * P + pid], qd = G[L::QD * P + pid], qt = G[L::QT * P + pid];
+                        ray.o = mk<T>(qo.x, qo.y, qo.z); ray.d = mk<T>(qd.x, qd.y, qd.z); ray.tm = qo.w;
+                        T t = qd.w;
+                        const int slot = bits_slot(qt.w), s = J.y + (sw & DONE) + (L::dyn ? 1 : 0);   // (static mode keeps "next sample" here)
                         int depth = S[L::DEPTH * P + pid];
                         const Surface<T> sf = surface_at<T>(sv, st.sa, st.sb, st.sc, st.meta, ray, t, slot);
                         PhiloxT<RT_PHILOX_TABLE != 0> rng; if (RT_PHILOX_TABLE) rng.init(p.keys); else rng.init(p.seed);
@@ -551,9 +556,9 @@ render_pool_kernel(const RenderParams<T> p) {
                         } else {
                             cont = true;
                             ray.o = sf.p; ray.d = dnew;                         // time is inherited (src/material.h:22)
-                            F[L::OX * P + pid] = ray.o.x; F[L::OY * P + pid] = ray.o.y; F[L::OZ * P + pid] = ray.o.z;
-                            F[L::DX * P + pid] = ray.d.x; F[L::DY * P + pid] = ray.d.y; F[L::DZ * P + pid] = ray.d.z;
-                            F[L::TR * P + pid] *= att.x; F[L::TG * P + pid] *= att.y; F[L::TB * P + pid] *= att.z;
+                            G[L::QO * P + pid] = quad<Q, T>(ray.o.x, ray.o.y, ray.o.z, ray.tm);
+                            G[L::QD * P + pid] = quad<Q, T>(ray.d.x, ray.d.y, ray.d.z, T(0));
+                            G[L::QT * P + pid] = quad<Q, T>(qt.x * att.x, qt.y * att.y, qt.z * att.z, qt.w);
                             S[L::DEPTH * P + pid] = (unsigned short)depth;
                         }
                     }
