@@ -24,11 +24,6 @@ def sample_shard(spp, rank, world):
     return begin, end - begin
 
 
-def row_shard(height, rank, world):
-    """Alternative tile sharding: rows j with j % world == rank (no arithmetic in the combine)."""
-    return np.arange(rank, height, world)
-
-
 class _CudaAlias:
     """Exposes a raw device pointer through __cuda_array_interface__ so torch can alias it."""
 

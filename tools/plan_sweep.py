@@ -4,10 +4,10 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import raytracingproject_b200 as rt
 s, m = rt.scene_rtiow()
 ctx = rt.Context(0); ctx.upload_scene(s, m)
-for spp in (500, 62):
+for spp in (500, 62, 250):
     cam = rt.camera_rtiow(1920, spp, 50)
     for rnd in range(2):
-        for jobs in (0, 10, 14, 20, 28, 40, 64):
+        for jobs in (20, 24, 28, 32, 40):
             ts = []
             for _ in range(3 if spp == 500 else 5):
                 ctx.render(cam, precision=rt.F32, seed=0, sched=jobs << 24); ctx.synchronize(); st = ctx.stats(); ts.append(st["render_ms"])
