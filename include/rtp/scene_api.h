@@ -151,6 +151,19 @@ class interval {
     double clamp(double x) const { return x < min ? min : (x > max ? max : x); }
     static const interval empty, universe;
 };
+
+// ---- src/color.h:9-35 ------------------------------------------------------------------------------
+// linear_to_gamma and write_color for CALLER code that formats a colour of its own (a legend, a test value).  The frame
+// itself never passes through them: B200Impl::Camera::render takes its bytes from the device (rt_readback: resolve + P3
+// encode kernels, byte-identical to this text); these two exist so that code written against the reference's color.h compiles.
+inline double linear_to_gamma(double linear_component) { return std::sqrt(linear_component); }
+inline void write_color(std::ostream& out, color pixel_color, int samples_per_pixel) {
+    const double scale = 1.0 / samples_per_pixel;                       // :20-23
+    const double r = linear_to_gamma(pixel_color.x() * scale), g = linear_to_gamma(pixel_color.y() * scale), b = linear_to_gamma(pixel_color.z() * scale);
+    static const interval intensity(0.000, 0.999);                      // :31
+    out << static_cast<int>(256 * intensity.clamp(r)) << ' ' << static_cast<int>(256 * intensity.clamp(g)) << ' '
+        << static_cast<int>(256 * intensity.clamp(b)) << '\n';          // :32-34
+}
 inline const interval interval::empty(+infinity, -infinity);
 inline const interval interval::universe(-infinity, +infinity);
 

@@ -50,6 +50,15 @@ TEST_F(DropInFixture, CentrePixelCalls) {
     EXPECT_TRUE(black.similar_to(color(0, 0, 0))) << black;
 }
 
+// src/color.h as callers see it: write_color's text for a colour of their own (the frame's bytes come from the device)
+TEST(ColorHeader, WriteColorFormatsLikeTheReference) {
+    std::ostringstream o;
+    write_color(o, color(0.5 * 8, 2.0 * 8, 0.0), 8);                  // sqrt(0.5) * 256 = 181.02; above 0.999 -> 255; 0
+    write_color(o, color(0.0625, 0.25, 1.0), 1);                      // 64, 128, 255 (exact roots on byte boundaries)
+    EXPECT_EQ(o.str(), std::string("181 255 0\n64 128 255\n"));
+    EXPECT_EQ(linear_to_gamma(0.25), 0.5);
+}
+
 // a world edited in place between two render() calls is rendered as it is NOW (same list object, same count)
 TEST_F(DropInFixture, EditedWorldIsRenderedAgain) {
     cam.image_width = 64; cam.samples_per_pixel = 2; cam.max_depth = 8;
