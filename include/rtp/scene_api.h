@@ -321,4 +321,26 @@ class hittable_list : public hittable {
     aabb bbox;
 };
 
+// ---- src/bvh.h ------------------------------------------------------------------------------------------------
+// The book's idiom `world = hittable_list(make_shared<bvh_node>(world));` keeps working: the node only remembers the objects
+// (in list order, the tie-break of the closest-hit search) and their box; the tree that is walked is the one rt_upload_scene
+// builds on the device side (the reference's constructor, src/bvh.h:12-14, is an empty stub).
+class bvh_node : public hittable {
+  public:
+    bvh_node(const hittable_list& list) : bvh_node(list.objects, 0, list.objects.size()) {}
+    bvh_node(const std::vector<shared_ptr<hittable>>& src_objects, size_t start, size_t end) {
+        if (start > end || end > src_objects.size()) throw std::out_of_range("bvh_node: object range outside the list");
+        for (size_t i = start; i < end; ++i) {
+            bbox = aabb(bbox, src_objects[i]->bounding_box());
+            members.push_back(src_objects[i]);
+        }
+    }
+    aabb bounding_box() const override { return bbox; }
+    void describe(rt_scene_builder& b) const override { for (const auto& o : members) o->describe(b); }
+
+  private:
+    std::vector<shared_ptr<hittable>> members;
+    aabb bbox;
+};
+
 #endif  // RTP_SCENE_API_H

@@ -8,6 +8,7 @@
 #include <cstdlib>
 #include <sstream>
 
+#include "bvh.h"
 #include "camera.h"
 #include "camera_b200.h"
 #include "hittable_list.h"
@@ -81,6 +82,34 @@ TEST_F(DropInFixture, EditedWorldIsRenderedAgain) {
     std::fwrite(first.str().data(), 1, first.str().size(), stdout);
     std::printf("second_ppm_bytes %zu\n", second.str().size());
     std::fwrite(second.str().data(), 1, second.str().size(), stdout);
+}
+
+// the book's `world = hittable_list(make_shared<bvh_node>(world))` (src/bvh.h:10): same spheres in the same order -> same image
+TEST_F(DropInFixture, WorldWrappedInABvhNodeRendersTheSameImage) {
+    cam.image_width = 64; cam.samples_per_pixel = 2; cam.max_depth = 8;
+    world.add(make_shared<sphere>(point3(0, -1000, 0), 1000, make_shared<lambertian>(color(0.5, 0.5, 0.5))));
+    world.add(make_shared<sphere>(point3(0, 1, 0), 1.0, make_shared<dielectric>(1.5)));
+    world.add(make_shared<sphere>(point3(-4, 1, 0), point3(-4, 1.5, 0), 1.0, make_shared<lambertian>(color(0.4, 0.2, 0.1))));
+    world.add(make_shared<sphere>(point3(4, 1, 0), 1.0, make_shared<metal>(color(0.7, 0.6, 0.5), 0.0)));
+    std::ostringstream plain, wrapped, part;
+    std::streambuf* old = std::cout.rdbuf(plain.rdbuf());
+    cam.render(world);
+    const auto node = make_shared<bvh_node>(world);
+    EXPECT_EQ(node->bounding_box().x.min, world.bounding_box().x.min);
+    EXPECT_EQ(node->bounding_box().y.max, world.bounding_box().y.max);
+    hittable_list tree(node);
+    std::cout.rdbuf(wrapped.rdbuf());
+    cam.render(tree);
+    hittable_list front(make_shared<bvh_node>(world.objects, 0, 2));      // the first two objects only
+    std::cout.rdbuf(part.rdbuf());
+    cam.render(front);
+    std::cout.rdbuf(old);
+    EXPECT_GT(plain.str().size(), size_t(64 * 36 * 6));
+    EXPECT_EQ(plain.str() == wrapped.str(), true);
+    EXPECT_NE(plain.str(), part.str());
+    bool refused = false;
+    try { bvh_node beyond(world.objects, 3, 9); } catch (const std::out_of_range&) { refused = true; }
+    EXPECT_TRUE(refused);
 }
 
 }  // namespace

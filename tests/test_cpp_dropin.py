@@ -156,6 +156,7 @@ def test_unit_test_call_sequence_matches_the_oracle(O, rt):
     r = subprocess.run([CALLS], capture_output=True)
     assert b"[       OK ] DropInFixture.CentrePixelCalls" in r.stderr, r.stderr[-2000:]
     assert b"[       OK ] ColorHeader.WriteColorFormatsLikeTheReference" in r.stderr, r.stderr[-2000:]      # src/color.h for caller code
+    assert b"[       OK ] DropInFixture.WorldWrappedInABvhNodeRendersTheSameImage" in r.stderr, r.stderr[-2000:]   # src/bvh.h
     v = _parse_values(r.stdout)
     ocam = O.camera_rtiow(400, 30, 50)
     ray, _ = O.get_rays(ocam, [200], [112], [0], seed=0)
