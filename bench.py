@@ -6,7 +6,9 @@
   step     one full frame: render (all 500 spp, sample-range sharded over the ranks) -> combine on
            rank 0 -> resolve to the 8-bit image, everything resident on the device (`value`);
            `e2e` = the same frame through the public API with HOST buffers: scene upload (H2D) +
-           render + resolve + P3 encode + read-back of rgb8 and the P3 text (D2H) every step.
+           render + resolve + P3 encode + read-back of rgb8 and the P3 text (D2H) every step, frames
+           back to back (the copies of a frame overlap the next frame's render; `one_frame_alone_ms`
+           is a frame on its own).
   N > 1    one process per GPU (torchrun), strong scaling of the one frame; partial accumulation
            buffers are combined by an NCCL reduce (default) or the fused IPC peer-reduce resolve.
 
@@ -322,8 +324,11 @@ def main():
     pin_rgb8 = torch.empty(W * H * 3, dtype=torch.uint8, pin_memory=True).numpy() if rank == 0 else None
     pin_ppm = torch.empty(W * H * 12 + 64, dtype=torch.uint8, pin_memory=True).numpy() if rank == 0 else None
 
-    def step(e2e):
-        """one frame; returns nothing, everything is enqueued on ctx's stream"""
+    in_flight = [False]                                              # a split read-back begun and not ended (rank 0)
+
+    def step(e2e, split=False):
+        """one frame; returns nothing, everything is enqueued on ctx's stream.  split: the frame's bytes leave through
+        rt_readback_begin (copies on the library's copy stream); the previous frame's rt_readback_end comes first"""
         if e2e:
             ctx.upload_scene(s, m, builder=builder_id)               # H2D: the world, every step (BVH build included)
         if jobs:
@@ -342,6 +347,11 @@ def main():
             else:
                 stream.synchronize(); dist.barrier()                 # peers' partials complete before rank 0 reads them
         if rank == 0:
+            if e2e and split:
+                n = ctx.readback_end() if in_flight[0] else None     # frame k - 1: its copies ran under this frame's render
+                ctx.readback_begin(args.spp, pin_rgb8, pin_ppm)      # waits for this frame, starts its copies, returns
+                in_flight[0] = True
+                return {"ppm_len": n}
             if e2e:
                 return {"ppm_len": ctx.readback_into(args.spp, pin_rgb8, pin_ppm)}
             return ctx.readback(args.spp, want_sum=False, want_rgb8=False)   # resolve on device, nothing copied
@@ -385,10 +395,42 @@ def main():
         clocks = sampler.stop() if rank == 0 else None
         return times, rays, kernel_ms, clocks, out
 
+    def timed_pipelined(steps, warmup):
+        """the end-to-end frame as a caller rendering frame after frame runs it: K frames back to back between two barriers, the
+        device-to-host copies of frame k (rt_readback_begin / _end) under the upload and render of frame k + 1.  Every frame's
+        upload, render, combine, resolve, P3 encode and both copies are inside the timed region, the last frame's copies included."""
+        def drain():
+            n = None
+            if rank == 0 and in_flight[0]:
+                n = ctx.readback_end(); in_flight[0] = False
+            return n
+        for _ in range(warmup):
+            step(True, split=True)
+        drain()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            with torch.cuda.stream(stream):
+                flush.fill_(1)                                       # evict L2 between frames, on the frames' own stream (~0.05 ms)
+            step(True, split=True)
+        n = drain()
+        barrier()
+        t = torch.tensor([(time.perf_counter() - t0) * 1e3 / steps], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item(), n
+
     times, rays, kernel_ms, clocks, _ = timed(False, args.steps, args.warmup)
     rank_kernels = [list(x) for x in rank_kernel_ms]
     e2e_times, _, _, _, e2e_out = timed(True, max(2, min(args.steps, 3)), 1)
     launches = ctx.stats()["kernel_launches"]
+    # frames in a row with the read-back split in two (not with tile or job sharding: there the peers write rank 0's image, and
+    # the hand-over of frame k + 1 may not start before rank 0 has frame k on the host -- one barrier per frame, nothing to overlap)
+    pipelined_ms = None
+    if not tiles and not jobs and (world == 1 or args.combine == "nccl") and not os.environ.get("RT_BENCH_NO_PIPELINE"):
+        pipelined_ms, n_text = timed_pipelined(max(3, min(args.steps, 5)), 1)
+        if rank == 0 and e2e_out and n_text != e2e_out["ppm_len"]:
+            raise SystemExit(f"bench: the split read-back delivered {n_text} bytes of P3 text, rt_readback {e2e_out['ppm_len']}")
 
     # untimed, N > 1: the COMBINED frame of the last end-to-end step (folded, reduced over NVLink, resolved on rank 0)
     # against the same frame rendered by rank 0 alone.  The float partial sums re-associate, nothing else may differ.
@@ -461,10 +503,19 @@ def main():
                          "note": f"algorithmic {f_ray:.0f} flop/ray x {rank_rays:.3e} rays per launch (SURVEY 8d); peak = 148 SMs x 128 "
                                  f"FP32 lanes x 2 x {sm_mhz:.0f} MHz observed under load (not in MEASURED_PEAKS.json); L2-side figure "
                                  f"{rank_rays * b_ray / (kms * 1e-3) / 1e9:.0f} GB/s algorithmic ({b_ray:.0f} B/ray)"},
-            "e2e": {"value": samples / e2e_ms / 1e3, "unit": "Msamples/s", "ms_per_step": e2e_ms,
-                    "h2d_bytes_per_step": int(s.nbytes + m.nbytes + 104),
-                    "d2h_bytes_per_step": int(W * H * 3 + (e2e_out["ppm_len"] if e2e_out else 0)),
-                    "api": "rt_upload_scene + rt_render + rt_readback(rgb8 + P3 text) per step; scene from pinned host arrays, results into pinned host buffers"},
+            # frames in a row (a caller's render loop): the copies of frame k overlap the render of frame k + 1; `one_frame_alone_ms`
+            # is the same frame with nothing before or after it (rt_readback, each step between two barriers)
+            "e2e": ({"value": samples / pipelined_ms / 1e3, "unit": "Msamples/s", "ms_per_step": pipelined_ms, "one_frame_alone_ms": e2e_ms,
+                     "h2d_bytes_per_step": int(s.nbytes + m.nbytes + 104),
+                     "d2h_bytes_per_step": int(W * H * 3 + (e2e_out["ppm_len"] if e2e_out else 0)),
+                     "api": "rt_upload_scene + rt_render + rt_readback_begin / rt_readback_end (rgb8 + P3 text) per step, frames back to back "
+                            "between two barriers: the device-to-host copies of a frame run under the next frame's render, the last frame's "
+                            "inside the timed region; scene from pinned host arrays, results into pinned host buffers"}
+                    if pipelined_ms else
+                    {"value": samples / e2e_ms / 1e3, "unit": "Msamples/s", "ms_per_step": e2e_ms,
+                     "h2d_bytes_per_step": int(s.nbytes + m.nbytes + 104),
+                     "d2h_bytes_per_step": int(W * H * 3 + (e2e_out["ppm_len"] if e2e_out else 0)),
+                     "api": "rt_upload_scene + rt_render + rt_readback(rgb8 + P3 text) per step; scene from pinned host arrays, results into pinned host buffers"}),
             "gpu_launches": int(launches) * args.steps, "clocks": clocks,
             # where a step's time goes (device-resident leg): rank 0's render kernel (CUDA events inside the library) and what
             # follows it until the frame is resolved on rank 0 -- tiles: wait for the peers' bytes + resolve of rank 0's tiles;

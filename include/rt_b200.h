@@ -171,6 +171,17 @@ int rt_render(rt_ctx *ctx, const rt_camera *cam, const rt_render_opts *opts);
  * spp_total = divisor used by write_color (0 = samples rendered into the buffer so far). */
 int rt_readback(rt_ctx *ctx, int spp_total, double *sum_rgb, uint8_t *rgb8, char *ppm, size_t *ppm_len);
 
+/* The same hand-over in two halves, for a caller that renders frame after frame (the loop around camera::render in a caller
+ * of its own; the reference prints one frame, src/main.cpp:70): rt_readback_begin resolves the frame and the P3 text on the
+ * device, waits for that, starts the device-to-host copies of rgb8 (H*W*3 bytes) and / or the text (ppm_capacity >= its
+ * length, at most H*W*12 + 64) on a copy stream of the context and returns; rt_readback_end waits for the copies and gives the
+ * text's length.  Between the two the caller may rt_upload_scene / rt_render the next frame -- the copies overlap its render --
+ * but must leave the host buffers alone; pinned host memory makes the copies asynchronous.  One split read-back at a time
+ * (RT_E_STATE otherwise); on a tile-sharded frame (rt_frame_export) the peers must not deliver the next frame before
+ * rt_readback_end has returned. */
+int rt_readback_begin(rt_ctx *ctx, int spp_total, uint8_t *rgb8, char *ppm, size_t ppm_capacity);
+int rt_readback_end(rt_ctx *ctx, size_t *ppm_len);
+
 /* ---- next row 8f-2: output formats next to P3, progressive preview ------------------------------ *
  * Progressive accumulation itself is rt_render with accumulate = 1 over further sample ranges
  * (sample_begin / sample_count): the streams are keyed by (pixel, sample), so any split of [0, spp)

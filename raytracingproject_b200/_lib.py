@@ -67,6 +67,8 @@ SYMBOLS = {
     "rt_update_spheres": (_I, [_VP, _VP, _SZ, _VP, _SZ]),
     "rt_render": (_I, [_VP, _VP, _VP]),
     "rt_readback": (_I, [_VP, _I, _VP, _VP, _VP, _VP]),
+    "rt_readback_begin": (_I, [_VP, _I, _VP, _VP, _SZ]),
+    "rt_readback_end": (_I, [_VP, _VP]),
     "rt_readback_image": (_I, [_VP, _I, _I, _VP, _VP]),
     "rt_preview": (_I, [_VP, _I, _VP, _VP]),
     "rt_image_size": (_I, [_VP, _VP, _VP]),

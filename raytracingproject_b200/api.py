@@ -159,6 +159,17 @@ class Context:
         self._ck(self._lib.rt_readback(self._h, spp_total, None, L.ptr(rgb8), L.ptr(ppm), C.byref(n) if ppm is not None else None))
         return n.value
 
+    def readback_begin(self, spp_total, rgb8=None, ppm=None):
+        """rt_readback_begin: resolve (+ P3 text) on the device, then start the copies into the caller's buffers (numpy uint8
+        arrays, pinned for a truly asynchronous copy) and return; render the next frame, then readback_end()."""
+        self._ck(self._lib.rt_readback_begin(self._h, spp_total, L.ptr(rgb8), L.ptr(ppm), ppm.nbytes if ppm is not None else 0))
+
+    def readback_end(self):
+        """rt_readback_end: wait for the copies begun by readback_begin; returns the length of the P3 text (0 if none)."""
+        n = C.c_size_t(0)
+        self._ck(self._lib.rt_readback_end(self._h, C.byref(n)))
+        return n.value
+
     def readback_image(self, fmt, spp_total=0):
         """The frame as file bytes: IMG_P3 (the reference's stdout), IMG_P6 or IMG_PFM (rt_readback_image)."""
         n = C.c_size_t(0)

@@ -111,6 +111,11 @@ struct rt_ctx {
     DevBuf<unsigned> enc_sums;
     DevBuf<unsigned long long> enc_offsets;   // [blocks] + total at the end
     bool render_timed = false;
+    // split read-back (rt_readback_begin / rt_readback_end): the frame's bytes travel on a stream of their own
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t copy_done = nullptr;
+    bool copy_pending = false;              // begun and not ended: rgb8 / text must not be overwritten before copy_done
+    size_t copy_text_len = 0;
 
     // peers (CUDA IPC)
     PeerList peers = {};
@@ -302,6 +307,8 @@ int rt_destroy(rt_ctx* ctx) {
     ctx->big_a.release(); ctx->big_b.release(); ctx->big_c.release(); ctx->meta.release(); ctx->big_meta.release();
     ctx->accum.release(); ctx->reduced.release(); ctx->job_counter.release(); ctx->ray_counter.release();
     ctx->rgb8.release(); ctx->sum.release(); ctx->text.release(); ctx->enc_sums.release(); ctx->enc_offsets.release();
+    if (ctx->copy_stream) { cudaStreamSynchronize(ctx->copy_stream); cudaStreamDestroy(ctx->copy_stream); }
+    if (ctx->copy_done) cudaEventDestroy(ctx->copy_done);
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -827,6 +834,11 @@ extern "C" int rt_render(rt_ctx* ctx, const rt_camera* cam, const rt_render_opts
     return RT_OK;
 }
 
+// a split read-back still copying out of rgb8 / text: whatever writes them next waits on the device (no host wait)
+static cudaError_t after_pending_copies(rt_ctx* ctx) {
+    return ctx->copy_pending ? cudaStreamWaitEvent(ctx->stream, ctx->copy_done, 0) : cudaSuccess;
+}
+
 extern "C" int rt_readback(rt_ctx* ctx, int spp_total, double* sum_rgb, uint8_t* rgb8, char* ppm, size_t* ppm_len) {
     NvtxRange nvtx_("rt_readback");
     if (!ctx) return RT_E_INVALID;
@@ -838,6 +850,7 @@ extern "C" int rt_readback(rt_ctx* ctx, int spp_total, double* sum_rgb, uint8_t*
     CK(ensure_rgb8(ctx, npix));
     if (sum_rgb) CK(ctx->sum.resize(npix * 3));
     const double scale = spp_total > 0 ? 1.0 / spp_total : 0.0;                 // src/color.h:20
+    CK(after_pending_copies(ctx));
     CK(cudaEventRecord(ctx->ev[2], ctx->stream));
     int launches = 1;
     const FrameViews no_views{nullptr, nullptr, 0, 0};
@@ -924,12 +937,50 @@ extern "C" int rt_readback(rt_ctx* ctx, int spp_total, double* sum_rgb, uint8_t*
     return RT_OK;
 }
 
+// Split read-back.  rt_readback_begin does what rt_readback does up to the frame's bytes being ready on the device (resolve, P3
+// text, its length -- that is rt_readback itself, asked for no copies), then starts the two bulk copies on the context's copy
+// stream and returns; rt_readback_end waits for them.  In between the caller may upload and rt_render the NEXT frame: a render
+// writes the accumulation layers only, and whatever resolves next waits for copy_done on the device (after_pending_copies).
+extern "C" int rt_readback_begin(rt_ctx* ctx, int spp_total, uint8_t* rgb8, char* ppm, size_t ppm_capacity) {
+    NvtxRange nvtx_("rt_readback_begin");
+    if (!ctx) return RT_E_INVALID;
+    if (ctx->copy_pending) return fail(ctx, RT_E_STATE, "rt_readback_begin: a split read-back is in flight (rt_readback_end first)");
+    if (!rgb8 && !ppm) return fail(ctx, RT_E_INVALID, "rt_readback_begin: neither rgb8 nor ppm wanted");
+    size_t text_len = 0;
+    const int rc = rt_readback(ctx, spp_total, nullptr, nullptr, nullptr, ppm ? &text_len : nullptr);   // synchronises the render stream
+    if (rc != RT_OK) return rc;
+    if (ppm && ppm_capacity < text_len) return fail(ctx, RT_E_INVALID, "rt_readback_begin: ppm buffer too small");
+    if (!ctx->copy_stream) {
+        CK(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&ctx->copy_done, cudaEventDisableTiming));
+    }
+    const size_t npix = size_t(ctx->W) * ctx->H;
+    if (rgb8) CK(cudaMemcpyAsync(rgb8, ctx->rgb8.p, npix * 3, cudaMemcpyDeviceToHost, ctx->copy_stream));
+    if (ppm) CK(cudaMemcpyAsync(ppm, ctx->text.p, text_len, cudaMemcpyDeviceToHost, ctx->copy_stream));
+    CK(cudaEventRecord(ctx->copy_done, ctx->copy_stream));
+    ctx->copy_pending = true;
+    ctx->copy_text_len = ppm ? text_len : 0;
+    return RT_OK;
+}
+
+extern "C" int rt_readback_end(rt_ctx* ctx, size_t* ppm_len) {
+    NvtxRange nvtx_("rt_readback_end");
+    if (!ctx) return RT_E_INVALID;
+    if (!ctx->copy_pending) return fail(ctx, RT_E_STATE, "rt_readback_end: no split read-back in flight");
+    CK(cudaSetDevice(ctx->device));
+    ctx->copy_pending = false;                                  // whatever the copies' fate, the hand-over is finished
+    CK(cudaEventSynchronize(ctx->copy_done));
+    if (ppm_len) *ppm_len = ctx->copy_text_len;
+    return RT_OK;
+}
+
 // ---------------------------------------------------------------- 8f-2: more output formats --
 static int resolve_views(rt_ctx* ctx, int spp_total, const FrameViews& v) {
     if (ctx->peers.n > 0 && !ctx->folded) return fail(ctx, RT_E_STATE, "resolve: peers are mapped; every rank must call rt_fold_slices before the fused resolve");
     const size_t npix = size_t(ctx->W) * ctx->H;
     CK(ensure_rgb8(ctx, npix));
     const double scale = spp_total > 0 ? 1.0 / spp_total : 0.0;
+    CK(after_pending_copies(ctx));
     if (ctx->precision == RT_F32)
         CK(launch_resolve<float4>(reinterpret_cast<const float4*>(ctx->accum.p), live_slices(ctx), live_peers(ctx), npix, scale,
                                   nullptr, ctx->rgb8.p, nullptr, ctx->stream, v, ctx->tiles));
