@@ -111,6 +111,7 @@ struct rt_ctx {
     DevBuf<unsigned> enc_sums;
     DevBuf<unsigned long long> enc_offsets;   // [blocks] + total at the end
     bool render_timed = false;
+    int* host_words = nullptr;              // 16 ints of pinned host memory the device can store to (small results without a device-to-host copy)
     // split read-back (rt_readback_begin / rt_readback_end): the frame's bytes travel on a stream of their own
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t copy_done = nullptr;
@@ -287,6 +288,9 @@ int rt_create(rt_ctx** out, int device) {
         }
         cudaGetLastError();
     }
+    if (cudaHostAlloc(reinterpret_cast<void**>(&ctx->host_words), 16 * sizeof(int), cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) {
+        ctx->host_words = nullptr; cudaGetLastError();      // (the copy path serves then)
+    }
     ctx->job_counter.resize(1);
     ctx->frame_timeout.resize(1);
     cudaMemset(ctx->frame_timeout.p, 0, sizeof(int));
@@ -308,6 +312,7 @@ int rt_destroy(rt_ctx* ctx) {
     ctx->accum.release(); ctx->reduced.release(); ctx->job_counter.release(); ctx->ray_counter.release();
     ctx->rgb8.release(); ctx->sum.release(); ctx->text.release(); ctx->enc_sums.release(); ctx->enc_offsets.release();
     if (ctx->copy_stream) { cudaStreamSynchronize(ctx->copy_stream); cudaStreamDestroy(ctx->copy_stream); }
+    if (ctx->host_words) cudaFreeHost(ctx->host_words);
     if (ctx->copy_done) cudaEventDestroy(ctx->copy_done);
     for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -442,7 +447,7 @@ extern "C" int rt_upload_scene(rt_ctx* ctx, const rt_sphere* spheres, size_t n_s
         CK(cudaMemcpyAsync(d_ids.p, tree_ids.data(), sizeof(int) * n_tree, cudaMemcpyHostToDevice, ctx->stream));
         cudaError_t e = launch_scene_boxes(d_sph.p, d_ids.p, n_tree, d_boxes.p, ctx->stream);
         int root = RT_SENTINEL, depth = 0;
-        if (e == cudaSuccess) e = build_lbvh_gpu(d_boxes.p, n_tree, lbvh_leaf, ctx->nodes.p, d_order.p, &root, &depth, ctx->stream);
+        if (e == cudaSuccess) e = build_lbvh_gpu(d_boxes.p, n_tree, lbvh_leaf, ctx->nodes.p, d_order.p, &root, &depth, ctx->stream, ctx->host_words);
         if (e == cudaSuccess) e = launch_scene_fill(d_sph.p, d_mat.p, d_ids.p, d_order.p, n_tree, ctx->sa32.p, ctx->sb32.p, ctx->sc32.p,
                                                     ctx->sa64.p, ctx->sb64.p, ctx->sc64.p, ctx->meta.p, ctx->stream, ctx->slot_sphere.p);
         if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);

@@ -174,7 +174,10 @@ __global__ void __launch_bounds__(256) lbvh_refit(const HostBox* __restrict__ bo
 
 }  // namespace
 
-cudaError_t build_lbvh_gpu(const HostBox* d_boxes, int n, int max_leaf, float4* d_nodes, int* d_order, int* root_ref, int* depth, cudaStream_t st) {
+__global__ void lbvh_publish(const int* __restrict__ root_depth, int* mapped_word) { *mapped_word = *root_depth; }
+
+cudaError_t build_lbvh_gpu(const HostBox* d_boxes, int n, int max_leaf, float4* d_nodes, int* d_order, int* root_ref, int* depth, cudaStream_t st,
+                           int* mapped_word) {
     if (n < 2) return cudaErrorInvalidValue;
     max_leaf = max_leaf < 1 ? 1 : (max_leaf > 8 ? 8 : max_leaf);
     int2* range = nullptr;
@@ -212,8 +215,15 @@ cudaError_t build_lbvh_gpu(const HostBox* d_boxes, int n, int max_leaf, float4* 
     lbvh_refit<<<nb, 256, 0, st>>>(d_boxes, vals_sorted, n, left, right, parent_inner, parent_leaf, range, max_leaf, flags, nbox, d_nodes, d_order, root_depth);
     LB(cudaGetLastError());
     int h_depth = 0;
-    LB(cudaMemcpyAsync(&h_depth, root_depth, sizeof(int), cudaMemcpyDeviceToHost, st));
-    LB(cudaStreamSynchronize(st));
+    if (mapped_word) {
+        lbvh_publish<<<1, 1, 0, st>>>(root_depth, mapped_word);
+        LB(cudaGetLastError());
+        LB(cudaStreamSynchronize(st));
+        h_depth = *static_cast<volatile int*>(mapped_word);
+    } else {
+        LB(cudaMemcpyAsync(&h_depth, root_depth, sizeof(int), cudaMemcpyDeviceToHost, st));
+        LB(cudaStreamSynchronize(st));
+    }
 #undef LB
     cleanup();
     if (root_ref) *root_ref = 0;

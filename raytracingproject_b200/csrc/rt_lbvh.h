@@ -15,8 +15,10 @@ namespace rt {
 // Builds the node records (rt_trace.cuh layout) on the device from device-resident boxes.
 // d_nodes: n-1 records of 16 floats; d_order: slot -> box index (leaf order); leaves hold 1..max_leaf
 // primitives (subtrees of that size are referred to as one leaf).  Returns the root ref and tree depth
-// through the pointers (host).
+// through the pointers (host).  mapped_word: one int of pinned host memory (device-addressable) or null -- with it the depth
+// reaches the host by a store from the device instead of a device-to-host copy, which would queue on the copy engine behind
+// whatever bulk copy another stream has in flight (the previous frame's read-back, rt_readback_begin).
 cudaError_t build_lbvh_gpu(const HostBox* d_boxes, int n, int max_leaf, float4* d_nodes, int* d_order,
-                           int* root_ref, int* depth, cudaStream_t st);
+                           int* root_ref, int* depth, cudaStream_t st, int* mapped_word = nullptr);
 
 }  // namespace rt
