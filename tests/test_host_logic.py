@@ -52,6 +52,9 @@ def test_image_size_and_camera(rt):
     assert list(c.lookfrom) == [13.0, 2.0, 3.0] and c.defocus_angle == 0.6 and c.focus_dist == 10.0
 
 
+PINNED_40K_TREE = "eed8616e6b27475864dd97048a1be93cf2c606cb52f846f53840bfde8b3dd146"   # scene_rtiow(100) without the ground, 4 per leaf
+
+
 def _check_bvh(spheres, b):
     """every sphere in exactly one leaf; every sphere inside the boxes of all its ancestors"""
     nodes, order, root = b["nodes"], b["order"], b["root_ref"]
@@ -107,6 +110,22 @@ def test_host_bvh_builder(rt):
     # identical centres (degenerate split) still terminate and cover everything
     same = np.repeat(s[5:6], 37)
     _check_bvh(same, rt.build_bvh_host(same, 2))
+
+
+def test_host_bvh_builder_threads_build_the_same_tree(rt, monkeypatch):
+    """scenes of >= 32768 spheres are built by several host threads (subtrees in parallel, centroids radix-sorted): the tree must
+    not depend on how many -- records and slot order bit for bit (RT_BVH_BUILD_THREADS is read at every build)"""
+    import hashlib
+    big, _ = rt.scene_rtiow(100)                    # ~40 k spheres
+    trees = []
+    for threads in ("1", "2", "5", "16"):
+        monkeypatch.setenv("RT_BVH_BUILD_THREADS", threads)
+        b = rt.build_bvh_host(big[1:], 4)
+        trees.append(hashlib.sha256(np.ascontiguousarray(b["order"]).tobytes() + np.ascontiguousarray(b["nodes"]).tobytes()).hexdigest())
+    assert len(set(trees)) == 1, trees
+    _check_bvh(big[1:], b)
+    # pinned against the single-threaded comparison-sort builder this one replaced (same scene, 4 spheres per leaf)
+    assert trees[0] == PINNED_40K_TREE
 
 
 def test_sample_shards_partition_the_samples():
